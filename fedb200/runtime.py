@@ -1,0 +1,401 @@
+"""Federated round loops: server (FedAvg) and serverless (gossip), sync and async.
+
+What the reference does (call stacks in SURVEY §3):
+
+* server mode — Flower ``Server.fit``: per round sample all clients, each ``fit``s from the global
+  parameters, ``aggregate_fit`` = weighted mean, then every client ``evaluate``s the new global
+  model and the metrics are example-weighted (src/Servercase/server_IID_IMDB.py:205-218);
+* serverless mode — a Python ``for`` over clients that train one after another on ONE shared model
+  object, snapshot their parameters, and an unweighted mean of the snapshots becomes the next
+  global model; global accuracy on a fresh random test subset; ``save_pretrained`` every round
+  (src/Serverlesscase/serverless_IID_IMDB.py:255-285).
+
+Here clients/peers are spread over ranks (one process per GPU), weights stay on the device in flat
+arenas, and aggregation / mixing / scoring / hashing are single fused kernels through ``Comm``.
+``serverless_semantics="handoff"`` reproduces the reference's sequential chain for comparison;
+the default ``"parallel"`` trains every peer from its own state concurrently (true gossip).
+"""
+from __future__ import annotations
+
+import os
+import time
+from dataclasses import asdict
+from typing import Dict, List, Optional
+
+import numpy as np
+import torch
+
+from .anomaly import AnomalyInjector, detect, score_updates
+from .config import FedConfig
+from .data.build import build_corpus, client_loaders, global_test_loader
+from .ledger import Ledger
+from .ledger.block import BROADCAST
+from .models.hf_io import load_state, save_pretrained
+from .p2p import AsyncGossipEngine, Topology, apply_mask, info_passing_time, mixing_matrix, optimise_route
+from .parallel import init_distributed, local_peer_ids, make_comm, peers_per_rank
+from .server.fedavg import FedAvg, weighted_average
+from .trainer.local import make_runner, resolve_device
+from .utils import MetricsLogger, OverheadMeter, PhaseTimer
+
+
+class FedRuntime:
+    def __init__(self, cfg: FedConfig, logger: Optional[MetricsLogger] = None, echo: bool = True):
+        self.cfg = cfg
+        dev = resolve_device(cfg)
+        self.rank, self.world, self.local_rank = init_distributed(dev)
+        self.device = torch.device("cuda", self.local_rank) if dev.type == "cuda" else dev
+        if self.device.type == "cuda":
+            torch.cuda.set_device(self.device)
+        self.overhead = OverheadMeter()                                   # before data/model load, like :59-63
+        self.log = logger or MetricsLogger(cfg.metrics_path, echo=echo, rank=self.rank)
+        self.comm = make_comm(cfg.comm, self.device, self.rank, self.world)
+        self.N = cfg.num_clients
+        self.local_ids = local_peer_ids(self.N, self.rank, self.world)
+        self.P = peers_per_rank(self.N, self.world)
+        cfg.data.max_seq_len = min(cfg.data.max_seq_len, cfg.model.max_position)
+        self.corpus = build_corpus(cfg.data, cfg.model, self.N, cfg.seed)
+        self.runner = make_runner(cfg, self.device, cfg.seed)
+        self.D = self.runner.flat.numel()
+        self.nbytes = self.D * 4
+        self.global_flat = self.comm.alloc("global", self.D)
+        self.global_flat.copy_(self.runner.flat)
+        self.slots = self.comm.alloc("slots", self.P * self.D).view(self.P, self.D)
+        self.acc = self.comm.alloc("acc", self.D)
+        self.timer = PhaseTimer(self.device.type == "cuda")
+        self.topo = Topology.from_name(cfg.topology, self.N, cfg.seed)
+        self.injector = AnomalyInjector(self.N, cfg.inject_anomalies, cfg.inject_kind, seed=cfg.seed)
+        self.ledger = Ledger(chunk_bytes=4096) if cfg.ledger else None
+        self.strategy = FedAvg(fraction_fit=1.0, fraction_evaluate=1.0,
+                               evaluate_metrics_aggregation_fn=weighted_average, seed=cfg.seed)
+        self.global_accuracies: List[float] = []
+        self.masked: List[int] = []
+        self.start_round = 0
+        self.peer_state = None
+        if cfg.mode == "serverless" and cfg.serverless_semantics == "parallel" and not self._full_uniform():
+            self.peer_state = self.comm.alloc("state", self.P * self.D).view(self.P, self.D)
+            for li in range(len(self.local_ids)):
+                self.peer_state[li].copy_(self.global_flat)
+        if cfg.resume and cfg.checkpoint_dir and os.path.exists(os.path.join(cfg.checkpoint_dir, "config.json")):
+            self._resume()
+        static = detect(self.topo, cfg.anomaly_detector) if cfg.anomaly_detector not in ("none", "cosine_pagerank") else []
+        self.static_masked = static
+        self.log.log("init", mode=cfg.mode, clients=self.N, world=self.world, device=str(self.device),
+                     backend=self.runner.backend, comm=self.comm.name, params=self.D, model=cfg.model.name,
+                     static_masked=static)
+
+    # ------------------------------------------------------------------------------------------
+    def _full_uniform(self) -> bool:
+        return self.cfg.topology == "full" and not self.cfg.asynchronous
+
+    def _resume(self) -> None:
+        import json
+        path = self.cfg.checkpoint_dir
+        state = load_state(path)
+        self.runner.load_state_dict(state)
+        self.runner.sync_shadow()
+        self.global_flat.copy_(self.runner.flat)
+        fs = os.path.join(path, "fed_state.json")
+        if os.path.exists(fs):
+            with open(fs) as fh:
+                meta = json.load(fh)
+            self.start_round = int(meta.get("round", -1)) + 1
+            self.global_accuracies = list(meta.get("global_accuracies", []))
+            lp = os.path.join(path, "ledger.json")
+            if self.ledger is not None and os.path.exists(lp):
+                self.ledger = Ledger.load(lp)
+                self.ledger.assert_valid()
+        self.log.log("resume", round=self.start_round, path=path)
+
+    def _checkpoint(self, rnd: int) -> Optional[float]:
+        cfg = self.cfg
+        if not cfg.checkpoint_dir or (rnd + 1) % max(cfg.checkpoint_every, 1) != 0:
+            return None
+        size = None
+        if self.rank == 0:
+            self.runner.load_flat(self.global_flat)
+            meta = {"round": rnd, "global_accuracies": self.global_accuracies, "mode": cfg.mode,
+                    "ledger_height": self.ledger.height if self.ledger else 0, "masked": self.masked}
+            size = save_pretrained(self.runner.state_dict(), cfg.model, cfg.checkpoint_dir, meta)
+            if self.ledger is not None:
+                self.ledger.save(os.path.join(cfg.checkpoint_dir, "ledger.json"))
+        self.comm.barrier()
+        return size
+
+    # ---- one client visit ----------------------------------------------------------------------
+    def _train_peer(self, li: int, k: int, rnd: int, start: torch.Tensor) -> Dict:
+        pin = self.device.type == "cuda"
+        tr, te = client_loaders(self.corpus, self.cfg.data, k, rnd, pin=pin)
+        with self.timer.phase("train"):
+            self.runner.load_flat(start)
+            self.runner.sync_shadow()
+            stats = self.runner.train_epochs(tr, self.cfg.local_epochs)
+        corrupted = self.injector.maybe_corrupt(k, self.runner.flat, start, rnd)
+        with self.timer.phase("publish"):
+            root = self._publish(li)
+        return {"peer": k, "batches": len(tr), "samples": tr.num_samples, "tokens": tr.num_tokens(),
+                "loss": stats["loss"], "root": root, "corrupted": corrupted, "testloader": te}
+
+    def _publish(self, li: int) -> Optional[bytes]:
+        """Copy the trained weights into the peer-visible slot; hash them on the way if the ledger
+        is on (fused ``sha256_copy`` kernel on a GPU)."""
+        src, dst = self.runner.flat, self.slots[li]
+        if self.ledger is None:
+            dst.copy_(src)
+            return None
+        if src.is_cuda:
+            from .ops import cuda_ops
+            self.comm.launches += 2
+            return cuda_ops.sha256_copy_root(src, dst, self.ledger.chunk_bytes)
+        dst.copy_(src)
+        from .ledger.merkle import merkle_root
+        return merkle_root(src.detach().numpy().tobytes(), self.ledger.chunk_bytes)
+
+    def _score(self, rnd: int) -> List[int]:
+        """On-line cosine/PageRank scoring of the published updates -> masked peer ids."""
+        if self.cfg.anomaly_detector != "cosine_pagerank":
+            return list(self.static_masked)
+        with self.timer.phase("score"):
+            L = len(self.local_ids)
+            deltas = (self.slots[:L] - self.global_flat.unsqueeze(0)).to(
+                torch.bfloat16 if self.device.type == "cuda" else torch.float32)
+            if L < self.P:
+                pad = torch.zeros(self.P - L, self.D, dtype=deltas.dtype, device=deltas.device)
+                deltas = torch.cat([deltas, pad], 0)
+            g = self.comm.gram(deltas, self.N).to(torch.float64).cpu().numpy()[: self.N, : self.N]
+            bad, ranks, band = score_updates(g)
+        self.log.log("score", round=rnd, masked=bad, ranks=[round(float(x), 6) for x in ranks], band=band)
+        return bad
+
+    def _ledger_append(self, rnd: int, infos: List[Dict], route_of=None) -> None:
+        if self.ledger is None:
+            return
+        with self.timer.phase("ledger"):
+            mine = [(i["peer"], i["root"].hex(), i["batches"]) for i in infos]
+            every = sorted(sum(self.comm.all_gather_object(mine), []))
+            for peer, root_hex, n in every:
+                route = route_of(peer) if route_of else []
+                self.ledger.append(rnd, peer, BROADCAST, bytes.fromhex(root_hex), self.nbytes, n, route,
+                                   timestamp_ns=rnd * 1_000_000 + peer)
+            if self.cfg.num_rounds <= 4 or rnd % 5 == 0:
+                self.ledger.assert_valid()
+
+    # ---- server mode -----------------------------------------------------------------------------
+    def round_server(self, rnd: int) -> Dict:
+        infos = [self._train_peer(li, k, rnd, self.global_flat) for li, k in enumerate(self.local_ids)]
+        self.masked = self._score(rnd)
+        with self.timer.phase("aggregate"):
+            ws = [0.0 if i["peer"] in self.masked else float(i["batches"]) for i in infos]   # n_k = len(trainloader)
+            self._local_weighted_sum(ws)
+            self.comm.weighted_mean(self.acc, sum(ws), self.global_flat)
+        self._ledger_append(rnd, infos)
+        with self.timer.phase("evaluate"):
+            ev = []
+            self.runner.load_flat(self.global_flat)
+            self.runner.sync_shadow()
+            for i in infos:
+                te = i["testloader"]
+                loss, acc = self.runner.evaluate(te)
+                ev.append((float(loss), len(te), {"accuracy": float(acc), "loss": float(loss)}))
+            ev = sum(self.comm.all_gather_object(ev), [])
+            loss, metrics = self.strategy.aggregate_evaluate(rnd, ev)
+        self.global_accuracies.append(metrics.get("accuracy", float("nan")))
+        return {"loss_distributed": loss, **metrics, "train_loss": float(np.mean([i["loss"] for i in infos])) if infos else None,
+                "samples": sum(i["samples"] for i in infos), "tokens": sum(i["tokens"] for i in infos)}
+
+    def _local_weighted_sum(self, ws: List[float]) -> None:
+        L = len(ws)
+        if self.acc.is_cuda:
+            from .ops import cuda_ops
+            srcs = [self.slots[i] for i in range(L) if ws[i] != 0.0]
+            if srcs:
+                cuda_ops.mix_n(srcs, [w for w in ws if w != 0.0], self.acc)
+                self.comm.launches += 1
+            else:
+                self.acc.zero_()
+        else:
+            self.acc.zero_()
+            for i in range(L):
+                if ws[i] != 0.0:
+                    self.acc.add_(self.slots[i], alpha=ws[i])
+
+    # ---- serverless mode ---------------------------------------------------------------------------
+    def round_serverless(self, rnd: int) -> Dict:
+        cfg = self.cfg
+        infos = []
+        if cfg.serverless_semantics == "handoff":
+            if self.world != 1:
+                raise ValueError("handoff (reference-compat) semantics is a single-process chain")
+            cur = self.global_flat.clone()
+            for li, k in enumerate(self.local_ids):
+                infos.append(self._train_peer(li, k, rnd, cur))
+                cur.copy_(self.runner.flat)                  # next client continues from these weights
+        else:
+            for li, k in enumerate(self.local_ids):
+                start = self.global_flat if self.peer_state is None else self.peer_state[li]
+                infos.append(self._train_peer(li, k, rnd, start))
+        local_acc = []
+        with self.timer.phase("evaluate_local"):
+            for li, i in enumerate(infos):                   # client.evaluate_model() after training (:264)
+                self.runner.load_flat(self.slots[li])
+                self.runner.sync_shadow()
+                local_acc.append(self.runner.evaluate(i["testloader"])[1])
+        self.masked = self._score(rnd)
+        with self.timer.phase("aggregate"):
+            ws = [0.0 if i["peer"] in self.masked else 1.0 for i in infos]          # unweighted mean (:269)
+            self._local_weighted_sum(ws)
+            self.comm.weighted_mean(self.acc, sum(ws), self.global_flat)             # consensus / global model
+            if self.peer_state is not None:
+                w = apply_mask(mixing_matrix(self.topo.adjacency(), "metropolis"), self.masked)
+                rows = w[self.local_ids[0]: self.local_ids[0] + self.P] if self.local_ids else w[:0]
+                if rows.shape[0] < self.P:
+                    rows = np.concatenate([rows, np.zeros((self.P - rows.shape[0], self.N))], 0)
+                self.comm.mix_rows(self.slots, rows, self.peer_state, self.N)
+        routes = {}
+        if cfg.route_optimizer and self.ledger is not None:
+            for i in infos:
+                routes[i["peer"]] = optimise_route(self.topo, self.nbytes, i["peer"], removed=self.masked)
+        self._ledger_append(rnd, infos, (lambda p: []) if not routes else
+                            (lambda p: routes[p].routes[max(routes[p].routes, key=lambda j: routes[p].latency[j])]
+                             if p in routes and routes[p].routes else []))
+        with self.timer.phase("evaluate_global"):
+            self.runner.load_flat(self.global_flat)
+            self.runner.sync_shadow()
+            te = global_test_loader(self.corpus, cfg.data, rnd, pin=self.device.type == "cuda")
+            gl, ga = self.runner.evaluate(te)
+        self.global_accuracies.append(float(ga))
+        locs = sum(self.comm.all_gather_object([float(a) for a in local_acc]), [])
+        return {"accuracy": float(ga), "loss": float(gl), "local_accuracy": locs,
+                "train_loss": float(np.mean([i["loss"] for i in infos])) if infos else None,
+                "samples": sum(i["samples"] for i in infos), "tokens": sum(i["tokens"] for i in infos)}
+
+    # ---- asynchronous serverless (virtual-time event engine) -------------------------------------------
+    def run_async(self) -> Dict:
+        if self.world != 1:
+            raise NotImplementedError("asynchronous gossip currently runs all peers in one process "
+                                      "(several peers per GPU); use sync rounds for multi-rank runs")
+        cfg = self.cfg
+        state = self.comm.alloc("async_state", self.N * self.D).view(self.N, self.D)
+        inbox = {}
+        for k in range(self.N):
+            state[k].copy_(self.global_flat)
+        epochs = np.zeros(self.N, dtype=np.int64)
+
+        def train_fn(k: int) -> float:
+            rnd = int(epochs[k])
+            tr, _ = client_loaders(self.corpus, cfg.data, k, rnd, pin=self.device.type == "cuda")
+            t0 = time.perf_counter()
+            with self.timer.phase("train"):
+                self.runner.load_flat(state[k])
+                self.runner.sync_shadow()
+                self.runner.train_epochs(tr, cfg.local_epochs)
+                self.injector.maybe_corrupt(k, self.runner.flat, state[k], rnd)
+                state[k].copy_(self.runner.flat)
+            epochs[k] += 1
+            if self.device.type == "cuda":
+                torch.cuda.synchronize()
+            return time.perf_counter() - t0
+
+        def publish_fn(src: int, dst: int) -> None:
+            with self.timer.phase("publish"):
+                buf = inbox.setdefault((dst, src), torch.empty_like(state[src]))
+                if self.ledger is not None and buf.is_cuda:
+                    from .ops import cuda_ops
+                    root = cuda_ops.sha256_copy_root(state[src], buf, self.ledger.chunk_bytes)
+                    self.comm.launches += 2
+                else:
+                    buf.copy_(state[src])
+                    root = None
+                    if self.ledger is not None:
+                        from .ledger.merkle import merkle_root
+                        root = merkle_root(buf.numpy().tobytes(), self.ledger.chunk_bytes)
+                if self.ledger is not None:
+                    self.ledger.append(int(epochs[src]), src, dst, root, self.nbytes, 0, [src, dst])
+
+        def mix_fn(k: int, srcs: List[int], ws: List[float], self_w: float) -> None:
+            if not srcs:
+                return
+            with self.timer.phase("aggregate"):
+                bufs = [state[k]] + [inbox[(k, s)] for s in srcs]
+                wts = [self_w] + list(ws)
+                if state.is_cuda:
+                    from .ops import cuda_ops
+                    cuda_ops.mix_n(bufs, wts, self.acc)
+                    self.comm.launches += 1
+                    state[k].copy_(self.acc)
+                else:
+                    self.acc.zero_()
+                    for b, w in zip(bufs, wts):
+                        self.acc.add_(b, alpha=float(w))
+                    state[k].copy_(self.acc)
+
+        masked = list(self.static_masked)
+        eng = AsyncGossipEngine(self.topo, self.nbytes, train_fn, mix_fn, publish_fn, cfg.staleness_decay,
+                                masked=masked, route_optimizer=cfg.route_optimizer)
+        res = eng.run(cfg.num_rounds)
+        keep = [k for k in range(self.N) if k not in masked]
+        self.global_flat.zero_()
+        for k in keep:
+            self.global_flat.add_(state[k], alpha=1.0 / len(keep))
+        self.runner.load_flat(self.global_flat)
+        self.runner.sync_shadow()
+        gl, ga = self.runner.evaluate(global_test_loader(self.corpus, cfg.data, cfg.num_rounds))
+        self.global_accuracies.append(float(ga))
+        res.update(accuracy=float(ga), loss=float(gl), masked=masked,
+                   info_passing=info_passing_time(self.topo, self.nbytes, 0, removed=masked))
+        self.async_engine = eng
+        self.log.log("async_done", **res)
+        return res
+
+    # ---- driver ----------------------------------------------------------------------------------------
+    def run(self) -> Dict:
+        cfg = self.cfg
+        if cfg.mode == "serverless" and cfg.asynchronous:
+            out = self.run_async()
+            return self._finish(out)
+        last = {}
+        for rnd in range(self.start_round, cfg.num_rounds):
+            t0 = time.perf_counter()
+            self.timer.reset()
+            last = self.round_server(rnd) if cfg.mode == "server" else self.round_serverless(rnd)
+            size = self._checkpoint(rnd)
+            dev = self.timer.device_ms()
+            wall = time.perf_counter() - t0
+            tot = self.comm.reduce_scalars([last.get("samples", 0), last.get("tokens", 0)], "sum")
+            mx = self.comm.reduce_scalars([wall], "max")[0]
+            self.log.log("round", round=rnd, wall_s=mx, samples_per_s=tot[0] / mx if mx else None,
+                         tokens_per_s=tot[1] / mx if mx else None, phases_ms=dev, model_size_gib=size,
+                         masked=self.masked, ledger_height=self.ledger.height if self.ledger else 0,
+                         **{k: v for k, v in last.items() if k not in ("samples", "tokens")})
+        return self._finish(last)
+
+    def _finish(self, last: Dict) -> Dict:
+        rep = self.overhead.report()
+        comm_model = info_passing_time(self.topo, self.nbytes, 0, removed=self.masked)
+        out = {"global_accuracies": self.global_accuracies, **rep, "info_passing_time": comm_model,
+               "ledger_height": self.ledger.height if self.ledger else 0, "last": last}
+        self.log.log("done", **out)
+        return out
+
+    def close(self) -> None:
+        self.log.close()
+        self.comm.close()
+
+
+def run_experiment(cfg: FedConfig, echo: bool = True) -> Dict:
+    rt = FedRuntime(cfg, echo=echo)
+    try:
+        return rt.run()
+    finally:
+        rt.close()
+
+
+def run_client_sweep(cfg: FedConfig, counts=(5, 10, 20), echo: bool = True) -> Dict[int, Dict]:
+    """Client-count sweep (C16): ``for NUM_CLIENTS in [5, 10, 20]`` re-running the experiment
+    (src/Serverlesscase/serverless_cancer_biobert_allclients.py:40-41)."""
+    import copy
+    out = {}
+    for n in counts:
+        c = copy.deepcopy(cfg)
+        c.num_clients = n
+        out[n] = run_experiment(c, echo=echo)
+    return out

@@ -1,0 +1,4 @@
+"""Instrumentation (C15): device/wall timers, psutil overhead, JSONL metrics."""
+from .timers import PhaseTimer, cuda_time_ms  # noqa: F401
+from .overhead import OverheadMeter  # noqa: F401
+from .log import MetricsLogger  # noqa: F401
