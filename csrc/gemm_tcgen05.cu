@@ -1,0 +1,335 @@
+// gemm_tcgen05 (K8): the encoder / pooler-free GEMMs of the local trainer on the 5th-gen tensor cores.
+//   D[M, N] = A[M, K] * B[N, K]^T   with bf16 operands, fp32 accumulation in TMEM, fused epilogues.
+// Replaces the cuBLAS calls behind nn.Linear in the reference's train loop
+// (src/Servercase/server_IID_IMDB.py:108-118; shapes in SURVEY §2.6).
+//
+// Structure (persistent, warp-specialised, one CTA per SM, 192 threads):
+//   warp 0  TMA producer   : cp.async.bulk.tensor tiles of A and B into a 4-deep 128B-swizzled smem ring
+//   warp 1  MMA issuer     : one elected thread issues tcgen05.mma (cta_group::1, M=128, N=BN, K=16),
+//                            accumulators double-buffered in TMEM (2 x BN columns), tcgen05.commit frees slots
+//   warps 2-5 epilogue     : tcgen05.ld 32 rows x 32 columns per warp, fused bias / dropout / residual /
+//                            GELU / GELU' / fp32 split-K reduction, direct 16-byte global stores
+// Operand layouts (selected per call, all fed by TMA, no transposes are ever materialised):
+//   forward  y = x W^T      A K-major  (x  [M, K]),        B K-major  (W [N, K], the HF Linear layout)
+//   dgrad    dx = dy W      A K-major  (dy [M, N']),       B MN-major (W [N', K'] read as [K = N', N = K'])
+//   wgrad    dW = dy^T x    A MN-major (dy [tokens, N']),  B MN-major (x [tokens, K']), split-K over tokens,
+//                           fp32 vector atomics into the gradient arena
+#include "common.cuh"
+#include "../include/fedb200.h"
+
+namespace fedb {
+
+constexpr int GM_BM = 128;
+constexpr int GM_BK = 64;
+constexpr int GM_STAGES = 4;
+constexpr int GM_THREADS = 192;
+constexpr int GM_A_BYTES = GM_BM * GM_BK * 2;     // 16 KB
+
+struct GemmParams {
+    int M, N, K;
+    int splits;             // split-K factor (EPI_ATOMIC only)
+    int epi;
+    void* out;              // bf16 [M, ldo] (fp32 for EPI_ATOMIC)
+    void* out2;             // bf16 [M, ldo]: GELU output for EPI_BIAS_GELU
+    int ldo;
+    const float* bias;      // [N] or null
+    const __nv_bfloat16* aux;   // residual / pre-activation, [M, ld_aux]
+    int ld_aux;
+    int act;                // 0 = erf GELU (BERT), 1 = tanh GELU (ALBERT gelu_new)
+    unsigned long long seed;
+    uint32_t keep_thresh;
+    float inv_keep;
+    int use_dropout;
+};
+
+__device__ __forceinline__ void store_bf16x32(__nv_bfloat16* dst, const float (&v)[32], int ncols_valid) {
+    // dst is 16-byte aligned (column offsets are multiples of 32, ldo multiple of 8)
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        if (q * 8 < ncols_valid) {
+            uint4 o;
+            o.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]); o.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
+            o.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]); o.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
+            *reinterpret_cast<uint4*>(dst + q * 8) = o;
+        }
+    }
+}
+__device__ __forceinline__ void load_bf16x32(const __nv_bfloat16* src, float (&v)[32], int ncols_valid) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        if (q * 8 < ncols_valid) {
+            const uint4 r = *reinterpret_cast<const uint4*>(src + q * 8);
+            const float2 a = unpack_bf16x2(r.x), b = unpack_bf16x2(r.y), c = unpack_bf16x2(r.z), d = unpack_bf16x2(r.w);
+            v[q * 8 + 0] = a.x; v[q * 8 + 1] = a.y; v[q * 8 + 2] = b.x; v[q * 8 + 3] = b.y;
+            v[q * 8 + 4] = c.x; v[q * 8 + 5] = c.y; v[q * 8 + 6] = d.x; v[q * 8 + 7] = d.y;
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[q * 8 + k] = 0.f;
+        }
+    }
+}
+
+template <int A_MN, int B_MN, int BN>
+__global__ void __launch_bounds__(GM_THREADS, 1) gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                     const __grid_constant__ CUtensorMap tmB,
+                                                                     const GemmParams p) {
+    constexpr int B_BYTES = BN * GM_BK * 2;
+    constexpr int STAGE_BYTES = GM_A_BYTES + B_BYTES;
+    constexpr uint32_t TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
+
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    __shared__ __align__(8) uint64_t full_bar[GM_STAGES];
+    __shared__ __align__(8) uint64_t empty_bar[GM_STAGES];
+    __shared__ __align__(8) uint64_t acc_full[2];
+    __shared__ __align__(8) uint64_t acc_empty[2];
+    __shared__ uint32_t tmem_base_slot;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m_tiles = (p.M + GM_BM - 1) / GM_BM, n_tiles = (p.N + BN - 1) / BN;
+    const int k_blocks = (p.K + GM_BK - 1) / GM_BK;
+    const int kb_per_split = (k_blocks + p.splits - 1) / p.splits;
+    const int total = m_tiles * n_tiles * p.splits;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+        for (int s = 0; s < GM_STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], 4); }
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc(&tmem_base_slot, TMEM_COLS);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = tmem_base_slot;
+
+    if (warp == 0) {
+        // =============================== TMA producer ===============================
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int w = blockIdx.x; w < total; w += gridDim.x) {
+                const int split = w % p.splits, tile = w / p.splits;
+                const int n_blk = tile % n_tiles, m_blk = tile / n_tiles;
+                const int kb0 = split * kb_per_split, kb1 = min(k_blocks, kb0 + kb_per_split);
+                for (int kb = kb0; kb < kb1; ++kb, ++it) {
+                    const int s = it % GM_STAGES;
+                    mbar_wait(&empty_bar[s], ((it / GM_STAGES) & 1u) ^ 1u);
+                    mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                    uint8_t* sa = smem + s * STAGE_BYTES;
+                    uint8_t* sb = sa + GM_A_BYTES;
+                    if (A_MN == 0) {
+                        tma_load_2d(sa, &tmA, &full_bar[s], kb * GM_BK, m_blk * GM_BM);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < GM_BM / 64; ++j)
+                            tma_load_2d(sa + j * 8192, &tmA, &full_bar[s], m_blk * GM_BM + j * 64, kb * GM_BK);
+                    }
+                    if (B_MN == 0) {
+                        tma_load_2d(sb, &tmB, &full_bar[s], kb * GM_BK, n_blk * BN);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j)
+                            tma_load_2d(sb + j * 8192, &tmB, &full_bar[s], n_blk * BN + j * 64, kb * GM_BK);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // =============================== MMA issuer ===============================
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(GM_BM, BN, A_MN, B_MN);
+            uint32_t it = 0, local = 0;
+            for (int w = blockIdx.x; w < total; w += gridDim.x, ++local) {
+                const int split = w % p.splits;
+                const int kb0 = split * kb_per_split, kb1 = min(k_blocks, kb0 + kb_per_split);
+                const uint32_t buf = local & 1u;
+                mbar_wait(&acc_empty[buf], ((local >> 1) & 1u) ^ 1u);
+                tc_fence_after_sync();
+                const uint32_t tmem_d = tmem_base + buf * BN;
+                for (int kb = kb0; kb < kb1; ++kb, ++it) {
+                    const int s = it % GM_STAGES;
+                    mbar_wait(&full_bar[s], (it / GM_STAGES) & 1u);
+                    tc_fence_after_sync();
+                    const uint32_t sa = smem_u32(smem + s * STAGE_BYTES), sb = sa + GM_A_BYTES;
+#pragma unroll
+                    for (int k = 0; k < GM_BK / 16; ++k) {
+                        const uint64_t da = A_MN ? umma_smem_desc(sa + k * 2048, 8192, 1024)
+                                                 : umma_smem_desc(sa + k * 32, 16, 1024);
+                        const uint64_t db = B_MN ? umma_smem_desc(sb + k * 2048, 8192, 1024)
+                                                 : umma_smem_desc(sb + k * 32, 16, 1024);
+                        umma_bf16(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit(&empty_bar[s]);
+                }
+                umma_commit(&acc_full[buf]);
+            }
+        }
+    } else {
+        // =============================== epilogue warps ===============================
+        const int quad = warp & 3;                       // TMEM lane quadrant this warp may read
+        uint32_t local = 0;
+        for (int w = blockIdx.x; w < total; w += gridDim.x, ++local) {
+            const int tile = w / p.splits;
+            const int n_blk = tile % n_tiles, m_blk = tile / n_tiles;
+            const uint32_t buf = local & 1u;
+            const int split = w % p.splits;
+            const bool has_k = split * kb_per_split < k_blocks;
+            mbar_wait(&acc_full[buf], (local >> 1) & 1u);
+            tc_fence_after_sync();
+            const int row = m_blk * GM_BM + quad * 32 + lane;
+            const bool row_ok = row < p.M;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                const int col0 = n_blk * BN + c * 32;
+                if (col0 >= p.N) break;                  // warp-uniform
+                uint32_t raw[32];
+                tmem_ld_32x32(tmem_base + ((uint32_t)(quad * 32) << 16) + buf * BN + c * 32, raw);
+                tmem_ld_wait();
+                const int nvalid = min(32, p.N - col0);
+                if (row_ok) {
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = has_k ? __uint_as_float(raw[j]) : 0.f;
+                    if (p.epi == FEDB200_EPI_ATOMIC_F32) {
+                        float* o = reinterpret_cast<float*>(p.out) + (size_t)row * p.ldo + col0;
+#pragma unroll
+                        for (int q = 0; q < 8; ++q)
+                            if (q * 4 < nvalid)
+                                atomicAdd(reinterpret_cast<float4*>(o + q * 4),
+                                          make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]));
+                    } else {
+                        if (p.bias != nullptr) {
+#pragma unroll
+                            for (int q = 0; q < 8; ++q) {
+                                if (q * 4 < nvalid) {
+                                    const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0) + q);
+                                    v[q * 4] += b4.x; v[q * 4 + 1] += b4.y; v[q * 4 + 2] += b4.z; v[q * 4 + 3] += b4.w;
+                                }
+                            }
+                        }
+                        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.ldo + col0;
+                        if (p.epi == FEDB200_EPI_BIAS) {
+                            store_bf16x32(o, v, nvalid);
+                        } else if (p.epi == FEDB200_EPI_BIAS_DROP_RES) {
+                            float r[32];
+                            load_bf16x32(p.aux + (size_t)row * p.ld_aux + col0, r, nvalid);
+                            if (p.use_dropout) {
+#pragma unroll
+                                for (int q = 0; q < 4; ++q)
+                                    dropout_apply8(v + q * 8, p.seed, (uint32_t)row, (uint32_t)(col0 + q * 8), p.keep_thresh, p.inv_keep);
+                            }
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) v[j] += r[j];
+                            store_bf16x32(o, v, nvalid);
+                        } else if (p.epi == FEDB200_EPI_BIAS_GELU) {
+                            store_bf16x32(o, v, nvalid);
+                            // activate the bf16-rounded pre-activation so backward (which re-reads it) is consistent
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) {
+                                const float u = __bfloat162float(__float2bfloat16_rn(v[j]));
+                                v[j] = p.act ? gelu_tanh(u) : gelu_erf(u);
+                            }
+                            store_bf16x32(reinterpret_cast<__nv_bfloat16*>(p.out2) + (size_t)row * p.ldo + col0, v, nvalid);
+                        } else if (p.epi == FEDB200_EPI_MUL_GELU_GRAD) {
+                            float u[32];
+                            load_bf16x32(p.aux + (size_t)row * p.ld_aux + col0, u, nvalid);
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) v[j] *= p.act ? gelu_tanh_grad(u[j]) : gelu_erf_grad(u[j]);
+                            store_bf16x32(o, v, nvalid);
+                        } else {    // FEDB200_EPI_ADD
+                            if (p.aux != nullptr) {
+                                float r[32];
+                                load_bf16x32(p.aux + (size_t)row * p.ld_aux + col0, r, nvalid);
+#pragma unroll
+                                for (int j = 0; j < 32; ++j) v[j] += r[j];
+                            }
+                            store_bf16x32(o, v, nvalid);
+                        }
+                    }
+                }
+                __syncwarp();
+            }
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[buf]);
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+template <int A_MN, int B_MN, int BN>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int max_ctas, cudaStream_t s) {
+    constexpr int STAGE_BYTES = GM_A_BYTES + BN * GM_BK * 2;
+    const size_t smem = (size_t)GM_STAGES * STAGE_BYTES + 1024;
+    auto kern = gemm_tcgen05_kernel<A_MN, B_MN, BN>;
+    static bool configured = false;
+    if (!configured) {
+        FEDB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    const int m_tiles = (p.M + GM_BM - 1) / GM_BM, n_tiles = (p.N + BN - 1) / BN;
+    int grid = m_tiles * n_tiles * p.splits;
+    int cap = sm_count();
+    if (max_ctas > 0 && cap > max_ctas) cap = max_ctas;
+    if (grid > cap) grid = cap;
+    kern<<<grid, GM_THREADS, smem, s>>>(ta, tb, p);
+    FEDB_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace fedb
+
+using namespace fedb;
+
+// layout: 0 = NT (A [M,K] K-major, B [N,K] K-major)           forward
+//         1 = NN (A [M,K] K-major, B [K,N] row-major)          dgrad
+//         2 = TN (A [K,M] row-major, B [K,N] row-major)        wgrad (use epi = ATOMIC_F32, splits >= 1)
+extern "C" int fedb200_gemm_bf16(int layout, const void* A, int lda, const void* B, int ldb, int M, int N, int K,
+                                 int epi, void* out, void* out2, int ldo, const float* bias, const void* aux,
+                                 int ld_aux, int act, unsigned long long seed, float dropout_p, int splits,
+                                 int max_ctas, void* stream) {
+    FEDB_REQUIRE(layout >= 0 && layout <= 2, "gemm: layout %d", layout);
+    FEDB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
+    FEDB_REQUIRE(N % 8 == 0 && ldo % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0, "gemm: N, ldo, lda, ldb must be multiples of 8");
+    FEDB_REQUIRE(epi >= 0 && epi <= FEDB200_EPI_ATOMIC_F32, "gemm: epilogue %d", epi);
+    FEDB_REQUIRE(((uintptr_t)out & 15) == 0 && ((uintptr_t)out2 & 15) == 0 && ((uintptr_t)aux & 15) == 0 && ld_aux % 8 == 0,
+                 "gemm: out/out2/aux must be 16-byte aligned");
+    if (epi == FEDB200_EPI_BIAS_DROP_RES || epi == FEDB200_EPI_MUL_GELU_GRAD) FEDB_REQUIRE(aux != nullptr, "gemm: epilogue needs aux");
+    if (epi == FEDB200_EPI_BIAS_GELU) FEDB_REQUIRE(out2 != nullptr, "gemm: GELU epilogue needs out2");
+    if (epi != FEDB200_EPI_ATOMIC_F32) splits = 1;
+    if (splits < 1) splits = 1;
+    const int k_blocks = (K + GM_BK - 1) / GM_BK;
+    if (splits > k_blocks) splits = k_blocks;
+    // make every split non-empty
+    while (splits > 1 && (splits - 1) * ((k_blocks + splits - 1) / splits) >= k_blocks) --splits;
+
+    const int BN = N >= 256 ? 256 : (N >= 128 ? 128 : 64);
+    const int a_mn = layout == 2, b_mn = layout != 0;
+    CUtensorMap ta, tb;
+    int e;
+    if (!a_mn) e = make_tmap_bf16_2d(&ta, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, GM_BM, GM_BK);
+    else       e = make_tmap_bf16_2d(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, GM_BK, 64);
+    if (e) return e;
+    if (!b_mn) e = make_tmap_bf16_2d(&tb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, (uint32_t)BN, GM_BK);
+    else       e = make_tmap_bf16_2d(&tb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, GM_BK, 64);
+    if (e) return e;
+
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K; p.splits = splits; p.epi = epi; p.out = out; p.out2 = out2; p.ldo = ldo;
+    p.bias = bias; p.aux = (const __nv_bfloat16*)aux; p.ld_aux = ld_aux; p.act = act; p.seed = seed;
+    p.keep_thresh = dropout_thresh16(dropout_p);
+    p.inv_keep = 1.0f / (1.0f - dropout_p);
+    p.use_dropout = dropout_p > 0.f;
+    cudaStream_t s = (cudaStream_t)stream;
+
+#define FEDB_GEMM_CASE(AM, BM, BNV) if (a_mn == AM && b_mn == BM && BN == BNV) return launch_gemm<AM, BM, BNV>(ta, tb, p, max_ctas, s);
+    FEDB_GEMM_CASE(0, 0, 256) FEDB_GEMM_CASE(0, 0, 128) FEDB_GEMM_CASE(0, 0, 64)
+    FEDB_GEMM_CASE(0, 1, 256) FEDB_GEMM_CASE(0, 1, 128) FEDB_GEMM_CASE(0, 1, 64)
+    FEDB_GEMM_CASE(1, 1, 256) FEDB_GEMM_CASE(1, 1, 128) FEDB_GEMM_CASE(1, 1, 64)
+#undef FEDB_GEMM_CASE
+    FEDB_REQUIRE(false, "gemm: no kernel for layout %d BN %d", layout, BN);
+    return 0;
+}

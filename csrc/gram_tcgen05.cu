@@ -1,0 +1,147 @@
+// cosine_gram (K4): G = Delta * Delta^T over the flattened client updates, on the 5th-gen tensor cores.
+//
+// Delta is [N, D] bf16 with N <= 128 clients and D ~ 1e8 — an extremely skinny GEMM whose cost is reading
+// N*D*2 bytes, so the kernel is a streaming reduction over K = D:
+//   * the reduction dimension is sharded over GPUs (rank r owns columns [k_begin, k_end)) and, inside a GPU,
+//     over persistent CTAs; the all-gathered [N, D] matrix is never materialised — each CTA pulls its K-slice
+//     of every rank's rows straight from that rank's (peer-mapped) buffer with TMA into one 128B-swizzled
+//     [rows x 64] shared tile;
+//   * one tcgen05.mma (M = 128, N = n_pad, K = 16, cta_group::1) per 16 columns uses the SAME tile as the A and
+//     the B operand (both K-major), accumulating the whole K-slice into a single [128 x n_pad] fp32 TMEM tile;
+//   * epilogue: tcgen05.ld -> fp32 atomics into the N x N result (zeroed by the caller); the cross-rank
+//     N x N sum is a few KB.
+// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer, all four warps drain TMEM at the end.
+// There is no reference counterpart (the reference scores a latency graph offline, All_graphs_IMDB_dataset
+// .ipynb:168-176); this is the north-star "anomaly scorer" of BASELINE.json.
+#include "common.cuh"
+#include "../include/fedb200.h"
+
+namespace fedb {
+
+constexpr int GR_STAGES = 8;
+constexpr int GR_TILE_BYTES = 128 * 128;          // 128 rows x 64 bf16
+constexpr int GR_THREADS = 128;
+
+struct GramMaps {
+    CUtensorMap map[FEDB200_MAX_RANKS];
+};
+
+__global__ void __launch_bounds__(GR_THREADS, 1) gram_tcgen05_kernel(const __grid_constant__ GramMaps maps, int n_ranks,
+                                                                     int rows_per_rank, int n_pad, int kb_begin,
+                                                                     int kb_end, float* __restrict__ out, int n_out) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    __shared__ __align__(8) uint64_t full_bar[GR_STAGES];
+    __shared__ __align__(8) uint64_t empty_bar[GR_STAGES];
+    __shared__ __align__(8) uint64_t done_bar;
+    __shared__ uint32_t tmem_base_slot;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rows_total = n_ranks * rows_per_rank;
+    const uint32_t tmem_cols = n_pad <= 32 ? 32u : (n_pad <= 64 ? 64u : 128u);
+
+    // rows >= rows_total are never written by TMA: clear the ring once so the unused A rows are finite
+    for (int i = threadIdx.x; i < GR_STAGES * GR_TILE_BYTES / 16; i += GR_THREADS)
+        reinterpret_cast<uint4*>(smem)[i] = make_uint4(0u, 0u, 0u, 0u);
+    fence_async_smem();
+
+    if (warp == 0 && lane == 0) {
+        for (int r = 0; r < n_ranks; ++r) tma_prefetch_desc(&maps.map[r]);
+        for (int s = 0; s < GR_STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        mbar_init(&done_bar, 1);
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc(&tmem_base_slot, tmem_cols);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_d = tmem_base_slot;
+
+    const int n_kb = (kb_end - kb_begin - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;   // this CTA's k-blocks
+    const uint32_t stage_tx = (uint32_t)rows_total * 128u;
+
+    if (warp == 0 && lane == 0) {
+        // ---------------- TMA producer ----------------
+        for (int it = 0; it < n_kb; ++it) {
+            const int s = it % GR_STAGES;
+            const uint32_t ph = (uint32_t)(it / GR_STAGES) & 1u;
+            mbar_wait(&empty_bar[s], ph ^ 1u);
+            mbar_expect_tx(&full_bar[s], stage_tx);
+            const int kcol = (kb_begin + (int)blockIdx.x + it * (int)gridDim.x) * 64;
+            for (int r = 0; r < n_ranks; ++r)
+                tma_load_2d(smem + s * GR_TILE_BYTES + r * rows_per_rank * 128, &maps.map[r], &full_bar[s], kcol, 0);
+        }
+    } else if (warp == 1 && lane == 0) {
+        // ---------------- MMA issuer ----------------
+        const uint32_t idesc = umma_idesc_bf16(128, n_pad, 0, 0);
+        for (int it = 0; it < n_kb; ++it) {
+            const int s = it % GR_STAGES;
+            const uint32_t ph = (uint32_t)(it / GR_STAGES) & 1u;
+            mbar_wait(&full_bar[s], ph);
+            tc_fence_after_sync();
+            const uint32_t base = smem_u32(smem + s * GR_TILE_BYTES);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint64_t d = umma_smem_desc(base + k * 32, 16, 1024);
+                umma_bf16(tmem_d, d, d, idesc, (it | k) != 0);
+            }
+            umma_commit(&empty_bar[s]);          // frees the slot once these MMAs have read it
+        }
+        umma_commit(&done_bar);
+    }
+    __syncwarp();
+
+    // ---------------- epilogue: all four warps ----------------
+    if (n_kb > 0) {
+        mbar_wait(&done_bar, 0);
+        tc_fence_after_sync();
+        const int row = warp * 32 + lane;
+        for (int c0 = 0; c0 < n_pad; c0 += 16) {
+            uint32_t v[16];
+            tmem_ld_32x16(tmem_d + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);
+            tmem_ld_wait();
+            if (row < n_out) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                    if (c0 + j < n_out) atomicAdd(out + (size_t)row * n_out + c0 + j, __uint_as_float(v[j]));
+            }
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_d, tmem_cols);
+}
+
+}  // namespace fedb
+
+using namespace fedb;
+
+// rows_ptrs[r]: base of rank r's [rows_per_rank, D] bf16 buffer (local or peer-mapped), row stride ld elements.
+// Accumulates G[i, j] (i, j < n_out = n_ranks * rows_per_rank) over columns [col_begin, col_end) into `out`
+// (fp32 [n_out, n_out], caller zeroes it).  col_begin must be a multiple of 64.
+extern "C" int fedb200_gram_bf16(const void* const* rows_ptrs, int n_ranks, int rows_per_rank, size_t D, size_t ld,
+                                 size_t col_begin, size_t col_end, float* out, int max_ctas, void* stream) {
+    FEDB_REQUIRE(n_ranks >= 1 && n_ranks <= FEDB200_MAX_RANKS, "gram: n_ranks=%d outside [1, %d]", n_ranks, FEDB200_MAX_RANKS);
+    const int rows_total = n_ranks * rows_per_rank;
+    FEDB_REQUIRE(rows_total >= 1 && rows_total <= 128, "gram: %d rows; at most 128 clients per launch", rows_total);
+    FEDB_REQUIRE(col_begin % 64 == 0 && col_end <= D && col_begin <= col_end, "gram: bad column range");
+    FEDB_REQUIRE(D % 8 == 0 && ld % 8 == 0, "gram: D and ld must be multiples of 8 (16-byte TMA strides)");
+    if (col_begin == col_end) return 0;
+    GramMaps maps;
+    for (int r = 0; r < n_ranks; ++r) {
+        int e = make_tmap_bf16_2d(&maps.map[r], rows_ptrs[r], (uint64_t)rows_per_rank, (uint64_t)D, (uint64_t)ld,
+                                  (uint32_t)rows_per_rank, 64);
+        if (e) return e;
+    }
+    const int n_pad = (rows_total + 15) / 16 * 16;
+    const int kb_begin = (int)(col_begin / 64), kb_end = (int)((col_end + 63) / 64);
+    int grid = sm_count();
+    if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
+    if (grid > kb_end - kb_begin) grid = kb_end - kb_begin;
+    const size_t smem = (size_t)GR_STAGES * GR_TILE_BYTES + 1024;
+    FEDB_CHECK(cudaFuncSetAttribute(gram_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    gram_tcgen05_kernel<<<grid, GR_THREADS, smem, (cudaStream_t)stream>>>(maps, n_ranks, rows_per_rank, n_pad, kb_begin,
+                                                                         kb_end, out, rows_total);
+    FEDB_LAUNCH_CHECK();
+    return 0;
+}

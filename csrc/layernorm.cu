@@ -1,0 +1,209 @@
+// LayerNorm forward / backward over bf16 activations (K10) with the reference's eps 1e-12
+// (BertLayerNorm, serverless_cancer_classification_with_BioBERT.ipynb:526-570).  One warp per row, rows held
+// in registers as 16-byte vectors (H % 8 == 0, H <= 1024).  The backward also emits, for free, everything
+// that is a column reduction of its own traffic: dgamma, dbeta and the bias gradient of the dense layer that
+// produced the pre-LN tensor (optionally through that layer's dropout mask, regenerated from the RNG counter).
+#include "common.cuh"
+#include "../include/fedb200.h"
+
+namespace fedb {
+
+constexpr int LN_MAXV = 4;          // vectors of 8 bf16 per lane -> H <= 1024
+constexpr int LN_WARPS = 8;
+
+struct RowVec {
+    float x[LN_MAXV][8];
+};
+
+__device__ __forceinline__ void load_row(const __nv_bfloat16* row, int nvec, int lane, RowVec& r) {
+#pragma unroll
+    for (int i = 0; i < LN_MAXV; ++i) {
+        const int v = lane + 32 * i;
+        if (v < nvec) {
+            const uint4 raw = *reinterpret_cast<const uint4*>(row + v * 8);
+            const float2 a = unpack_bf16x2(raw.x), b = unpack_bf16x2(raw.y), c = unpack_bf16x2(raw.z), d = unpack_bf16x2(raw.w);
+            r.x[i][0] = a.x; r.x[i][1] = a.y; r.x[i][2] = b.x; r.x[i][3] = b.y;
+            r.x[i][4] = c.x; r.x[i][5] = c.y; r.x[i][6] = d.x; r.x[i][7] = d.y;
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) r.x[i][k] = 0.f;
+        }
+    }
+}
+__device__ __forceinline__ void store_vec(__nv_bfloat16* row, int v, const float (&y)[8]) {
+    uint4 o;
+    o.x = pack_bf16x2(y[0], y[1]); o.y = pack_bf16x2(y[2], y[3]);
+    o.z = pack_bf16x2(y[4], y[5]); o.w = pack_bf16x2(y[6], y[7]);
+    *reinterpret_cast<uint4*>(row + v * 8) = o;
+}
+__device__ __forceinline__ void row_stats(const RowVec& r, int nvec, int lane, int H, float eps, float& mean, float& rstd) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < LN_MAXV; ++i)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) s += r.x[i][k];
+    mean = warp_sum(s) / (float)H;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < LN_MAXV; ++i) {
+        if (lane + 32 * i < nvec) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { const float d = r.x[i][k] - mean; q += d * d; }
+        }
+    }
+    rstd = rsqrtf(warp_sum(q) / (float)H + eps);
+}
+
+__global__ void __launch_bounds__(LN_WARPS * 32) ln_fwd_kernel(const __nv_bfloat16* __restrict__ z,
+                                                               const float* __restrict__ gamma,
+                                                               const float* __restrict__ beta,
+                                                               __nv_bfloat16* __restrict__ y, float* __restrict__ mean_out,
+                                                               float* __restrict__ rstd_out, int T, int H, float eps) {
+    const int lane = threadIdx.x & 31, nvec = H / 8;
+    const int warp = blockIdx.x * LN_WARPS + (threadIdx.x >> 5), nwarps = gridDim.x * LN_WARPS;
+    for (int row = warp; row < T; row += nwarps) {
+        RowVec r;
+        load_row(z + (size_t)row * H, nvec, lane, r);
+        float mean, rstd;
+        row_stats(r, nvec, lane, H, eps, mean, rstd);
+#pragma unroll
+        for (int i = 0; i < LN_MAXV; ++i) {
+            const int v = lane + 32 * i;
+            if (v < nvec) {
+                float o[8];
+                const float4 g0 = *reinterpret_cast<const float4*>(gamma + v * 8), g1 = *reinterpret_cast<const float4*>(gamma + v * 8 + 4);
+                const float4 b0 = *reinterpret_cast<const float4*>(beta + v * 8), b1 = *reinterpret_cast<const float4*>(beta + v * 8 + 4);
+                const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+                const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+                for (int k = 0; k < 8; ++k) o[k] = (r.x[i][k] - mean) * rstd * gg[k] + bb[k];
+                store_vec(y + (size_t)row * H, v, o);
+            }
+        }
+        if (lane == 0) { mean_out[row] = mean; rstd_out[row] = rstd; }
+    }
+}
+
+// dz = LN'(dy);   df = dz * dropmask (optional);   dgamma += sum dy*xhat;  dbeta += sum dy;  dbias += sum df
+__global__ void __launch_bounds__(LN_WARPS * 32) ln_bwd_kernel(
+    const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ z, const float* __restrict__ mean_in,
+    const float* __restrict__ rstd_in, const float* __restrict__ gamma, __nv_bfloat16* __restrict__ dz,
+    __nv_bfloat16* __restrict__ df, float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dbias,
+    int T, int H, uint64_t seed, uint32_t keep_thresh, float inv_keep) {
+    extern __shared__ float red[];        // [LN_WARPS][H]
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, nvec = H / 8;
+    const int warp = blockIdx.x * LN_WARPS + wib, nwarps = gridDim.x * LN_WARPS;
+    float ag[LN_MAXV][8], ab[LN_MAXV][8], as[LN_MAXV][8];
+#pragma unroll
+    for (int i = 0; i < LN_MAXV; ++i)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) ag[i][k] = ab[i][k] = as[i][k] = 0.f;
+    float gg[LN_MAXV][8];
+#pragma unroll
+    for (int i = 0; i < LN_MAXV; ++i) {
+        const int v = lane + 32 * i;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) gg[i][k] = v < nvec ? gamma[v * 8 + k] : 0.f;
+    }
+    for (int row = warp; row < T; row += nwarps) {
+        RowVec x, g;
+        load_row(z + (size_t)row * H, nvec, lane, x);
+        load_row(dy + (size_t)row * H, nvec, lane, g);
+        const float mean = mean_in[row], rstd = rstd_in[row];
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < LN_MAXV; ++i) {
+            if (lane + 32 * i < nvec) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const float xh = (x.x[i][k] - mean) * rstd;
+                    const float dxh = g.x[i][k] * gg[i][k];
+                    x.x[i][k] = xh;
+                    ag[i][k] += g.x[i][k] * xh;
+                    ab[i][k] += g.x[i][k];
+                    g.x[i][k] = dxh;
+                    s1 += dxh; s2 += dxh * xh;
+                }
+            }
+        }
+        const float c1 = warp_sum(s1) / (float)H, c2 = warp_sum(s2) / (float)H;
+#pragma unroll
+        for (int i = 0; i < LN_MAXV; ++i) {
+            const int v = lane + 32 * i;
+            if (v < nvec) {
+                float o[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) o[k] = rstd * (g.x[i][k] - c1 - x.x[i][k] * c2);
+                store_vec(dz + (size_t)row * H, v, o);
+                if (df != nullptr) {
+                    dropout_apply8(o, seed, (uint32_t)row, (uint32_t)(v * 8), keep_thresh, inv_keep);
+                    store_vec(df + (size_t)row * H, v, o);
+                }
+                if (dbias != nullptr) {
+                    // accumulate the bf16-rounded value the downstream GEMMs will actually consume
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) as[i][k] += __bfloat162float(__float2bfloat16_rn(o[k]));
+                }
+            }
+        }
+    }
+    // block reduction of the three column accumulators, one quantity at a time
+    float* outs[3] = {dgamma, dbeta, dbias};
+    for (int q = 0; q < 3; ++q) {
+        if (outs[q] == nullptr) continue;
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < LN_MAXV; ++i) {
+            const int v = lane + 32 * i;
+            if (v < nvec) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) red[wib * H + v * 8 + k] = q == 0 ? ag[i][k] : (q == 1 ? ab[i][k] : as[i][k]);
+            }
+        }
+        __syncthreads();
+        for (int c = threadIdx.x; c < H; c += LN_WARPS * 32) {
+            float s = 0.f;
+#pragma unroll
+            for (int w = 0; w < LN_WARPS; ++w) s += red[w * H + c];
+            atomicAdd(outs[q] + c, s);
+        }
+    }
+}
+
+}  // namespace fedb
+
+using namespace fedb;
+
+static int ln_grid(int T) {
+    int blocks = (T + LN_WARPS - 1) / LN_WARPS;
+    const int cap = sm_count() * 4;
+    return blocks < 1 ? 1 : (blocks > cap ? cap : blocks);
+}
+
+extern "C" int fedb200_layernorm_fwd(const void* z, const float* gamma, const float* beta, void* y, float* mean,
+                                     float* rstd, int T, int H, float eps, void* stream) {
+    FEDB_REQUIRE(H % 8 == 0 && H <= 8 * 32 * LN_MAXV, "layernorm: H=%d must be a multiple of 8 and <= 1024", H);
+    if (T <= 0) return 0;
+    ln_fwd_kernel<<<ln_grid(T), LN_WARPS * 32, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)z, gamma, beta, (__nv_bfloat16*)y, mean, rstd, T, H, eps);
+    FEDB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int fedb200_layernorm_bwd(const void* dy, const void* z, const float* mean, const float* rstd,
+                                     const float* gamma, void* dz, void* df, float* dgamma, float* dbeta,
+                                     float* dbias, int T, int H, unsigned long long seed, float dropout_p,
+                                     void* stream) {
+    FEDB_REQUIRE(H % 8 == 0 && H <= 8 * 32 * LN_MAXV, "layernorm: H=%d must be a multiple of 8 and <= 1024", H);
+    if (T <= 0) return 0;
+    const float keep = 1.0f - dropout_p;
+    const uint32_t thresh = dropout_thresh16(dropout_p);
+    if (dropout_p <= 0.f) df = nullptr;
+    int blocks = ln_grid(T);
+    if (blocks > sm_count() * 2) blocks = sm_count() * 2;
+    ln_bwd_kernel<<<blocks, LN_WARPS * 32, LN_WARPS * H * sizeof(float), (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)z, mean, rstd, gamma, (__nv_bfloat16*)dz, (__nv_bfloat16*)df,
+        dgamma, dbeta, dbias, T, H, seed, thresh, 1.0f / keep);
+    FEDB_LAUNCH_CHECK();
+    return 0;
+}

@@ -1,0 +1,90 @@
+"""ctypes loader for ``fedb200/lib/libfedb200.so`` (built in-tree by ``build.py`` with nvcc for sm_100a).
+
+The library is a plain C ABI (``include/fedb200.h``): kernels take raw device pointers and a stream, so
+there is no libtorch dependency and the build takes seconds.  On a machine with a GPU a missing or
+unloadable library is an error — there is no silent PyTorch fallback for the fused paths.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+_LIB: Optional[C.CDLL] = None
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "lib", "libfedb200.so")
+
+vp, i32, u32, u64, f32, f64, sz = C.c_void_p, C.c_int, C.c_uint, C.c_ulonglong, C.c_float, C.c_double, C.c_size_t
+
+_PROTOS = {
+    "fedb200_last_error": (C.c_char_p, []),
+    "fedb200_abi_version": (i32, []),
+    "fedb200_sm_count": (i32, []),
+    "fedb200_adamw_flat": (i32, [vp, vp, vp, vp, vp, sz, i32, f32, f32, f32, f32, f32, f32, i32, vp]),
+    "fedb200_mix_n": (i32, [vp, vp, i32, vp, vp, sz, vp]),
+    "fedb200_colsum_bf16": (i32, [vp, vp, i32, i32, i32, vp]),
+    "fedb200_cast_f32_bf16": (i32, [vp, vp, sz, vp]),
+    "fedb200_delta_bf16": (i32, [vp, vp, vp, sz, vp]),
+    "fedb200_gemm_bf16": (i32, [i32, vp, i32, vp, i32, i32, i32, i32, i32, vp, vp, i32, vp, vp, i32, i32, u64, f32,
+                                i32, i32, vp]),
+    "fedb200_layernorm_fwd": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, f32, vp]),
+    "fedb200_layernorm_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, u64, f32, vp]),
+    "fedb200_embed_fwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, f32, u64, f32, vp]),
+    "fedb200_embed_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, u64, f32, vp]),
+    "fedb200_head_fwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, f32, u64, f32, vp]),
+    "fedb200_head_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, u64, f32, vp]),
+    "fedb200_attn_fwd": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, f32, u64, f32, vp]),
+    "fedb200_attn_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, u64, f32, vp]),
+    "fedb200_gram_bf16": (i32, [vp, i32, i32, sz, sz, sz, sz, vp, i32, vp]),
+    "fedb200_pagerank": (i32, [vp, i32, i32, f64, f64, i32, f64, i32, vp, vp, vp, vp]),
+    "fedb200_sha256_leaves": (i32, [vp, vp, sz, u32, vp, vp]),
+    "fedb200_merkle_root": (i32, [vp, vp, u32, vp, vp]),
+    "fedb200_block_validate": (i32, [vp, vp, u32, vp, vp, vp]),
+    "fedb200_peer_alloc": (i32, [sz, vp, vp]),
+    "fedb200_peer_open": (i32, [vp, vp]),
+    "fedb200_peer_close": (i32, [vp]),
+    "fedb200_peer_free": (i32, [vp]),
+    "fedb200_fedavg_reduce": (i32, [vp, vp, vp, vp, i32, i32, sz, f32, u32, i32, vp]),
+    "fedb200_peer_barrier": (i32, [vp, i32, i32, u32, i32, vp]),
+}
+
+
+class KernelError(RuntimeError):
+    pass
+
+
+def available() -> bool:
+    return os.path.exists(LIB_PATH)
+
+
+def lib() -> C.CDLL:
+    global _LIB
+    if _LIB is None:
+        path = os.path.abspath(LIB_PATH)
+        if not os.path.exists(path):
+            raise KernelError(f"{path} is missing — run `python build.py` (nvcc, sm_100a) before using the fused ops")
+        l = C.CDLL(path)
+        for name, (res, args) in _PROTOS.items():
+            if hasattr(l, name):
+                fn = getattr(l, name)
+                fn.restype, fn.argtypes = res, args
+        _LIB = l
+    return _LIB
+
+
+def call(name: str, *args) -> None:
+    l = lib()
+    fn = getattr(l, name, None)
+    if fn is None:
+        raise KernelError(f"{name} is not exported by libfedb200.so (stale build?)")
+    rc = fn(*args)
+    if rc != 0:
+        raise KernelError(f"{name} failed (cuda error {rc}): {l.fedb200_last_error().decode()}")
+
+
+# number of kernel launches issued through this module (the bench reports it as gpu_launches)
+LAUNCHES = 0
+
+
+def count(n: int = 1) -> None:
+    global LAUNCHES
+    LAUNCHES += n

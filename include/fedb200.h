@@ -1,0 +1,120 @@
+/* fedb200 — C ABI of the hand-written sm_100a kernels (libfedb200.so).
+ *
+ * Conventions: every function returns 0 on success or a cudaError_t value; fedb200_last_error() gives the
+ * message.  Pointers are device pointers unless noted.  `stream` is a cudaStream_t passed as void*.  Nothing
+ * here allocates device memory unless its comment says so: callers own all buffers (PyTorch tensors in the
+ * Python package).  "Reference" citations point into the research repository this framework re-implements
+ * (paths relative to its root); most kernels have no counterpart there because it ships no native code.
+ */
+#ifndef FEDB200_H
+#define FEDB200_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FEDB200_ABI_VERSION 1
+#define FEDB200_MAX_MIX_SOURCES 64
+#define FEDB200_MAX_RANKS 8
+
+/* GEMM epilogues */
+#define FEDB200_EPI_BIAS 0          /* out = acc + bias                                  (QKV projection)        */
+#define FEDB200_EPI_BIAS_DROP_RES 1 /* out = dropout(acc + bias) + aux                   (attn-out, FFN-down)    */
+#define FEDB200_EPI_BIAS_GELU 2     /* out = acc + bias ; out2 = gelu(out)               (FFN-up)                */
+#define FEDB200_EPI_MUL_GELU_GRAD 3 /* out = acc * gelu'(aux)                            (dgrad through GELU)    */
+#define FEDB200_EPI_ADD 4           /* out = acc (+ aux)                                 (dgrad + residual grad) */
+#define FEDB200_EPI_ATOMIC_F32 5    /* out_f32 += acc (split-K)                          (wgrad)                 */
+
+const char* fedb200_last_error(void);
+int fedb200_abi_version(void);
+int fedb200_sm_count(void);
+
+/* ---- flat-arena kernels ------------------------------------------------------------------------------------ */
+/* K13. One pass of HF-semantics AdamW over the whole flat arena (reference: transformers.AdamW python loop,
+ * src/Servercase/server_IID_IMDB.py:109,117): p/m/v update, optional bf16 shadow write, optional grad zeroing. */
+int fedb200_adamw_flat(float* p, float* g, float* m, float* v, void* shadow_bf16, size_t n, int step, float lr,
+                       float beta1, float beta2, float eps, float weight_decay, float grad_scale, int zero_grad,
+                       void* stream);
+/* K1 (local stage) / K2 / K3 combine: out = sum_j weights[j] * srcs[j]; srcs may be peer-mapped pointers.
+ * `srcs` and `weights` are HOST arrays.  Reference: `sum(param)/len(param)`,
+ * src/Serverlesscase/serverless_IID_IMDB.py:269, and Flower's FedAvg aggregate (server_IID_IMDB.py:205-209). */
+int fedb200_mix_n(const float* const* srcs, const float* weights, int n_src, float* out, void* shadow_bf16, size_t n,
+                  void* stream);
+int fedb200_colsum_bf16(const void* x, float* out, int M, int N, int ld, void* stream);
+int fedb200_cast_f32_bf16(const float* in, void* out, size_t n, void* stream);
+int fedb200_delta_bf16(const float* a, const float* b, void* out, size_t n, void* stream);
+
+/* ---- local-trainer kernels ----------------------------------------------------------------------------------- */
+/* K8. bf16 GEMM on tcgen05/TMEM fed by TMA. layout 0: A[M,K] B[N,K]; 1: A[M,K] B[K,N]; 2: A[K,M] B[K,N]. */
+int fedb200_gemm_bf16(int layout, const void* A, int lda, const void* B, int ldb, int M, int N, int K, int epi,
+                      void* out, void* out2, int ldo, const float* bias, const void* aux, int ld_aux, int act,
+                      unsigned long long seed, float dropout_p, int splits, int max_ctas, void* stream);
+/* K10. LayerNorm over bf16 rows (eps 1e-12 in BERT). bwd also emits dgamma/dbeta and the producing layer's dbias. */
+int fedb200_layernorm_fwd(const void* z, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
+                          int T, int H, float eps, void* stream);
+int fedb200_layernorm_bwd(const void* dy, const void* z, const float* mean, const float* rstd, const float* gamma,
+                          void* dz, void* df, float* dgamma, float* dbeta, float* dbias, int T, int H,
+                          unsigned long long seed, float dropout_p, void* stream);
+/* K11. word + position + token-type gather, LayerNorm, dropout; and the scatter backward. */
+int fedb200_embed_fwd(const int* ids, const int* pos, const int* tt, const float* word, const float* posw,
+                      const float* typew, const float* gamma, const float* beta, void* out, float* mean, float* rstd,
+                      int T, int H, float eps, unsigned long long seed, float dropout_p, void* stream);
+int fedb200_embed_bwd(const void* dx, const int* ids, const int* pos, const int* tt, const float* word,
+                      const float* posw, const float* typew, const float* gamma, const float* mean, const float* rstd,
+                      float* gword, float* gpos, float* gtype, float* dgamma, float* dbeta, int T, int H,
+                      int type_vocab, unsigned long long seed, float dropout_p, void* stream);
+/* K12. pooler + dropout + classifier + softmax cross-entropy, forward and backward. */
+int fedb200_head_fwd(const void* x, const int* first_tok, const float* Wp, const float* bp, const float* Wc,
+                     const float* bc, const int* labels, float* pooled, float* pooled_drop, float* logits,
+                     float* loss, int* pred, float* dlogits, int B, int H, int C, float grad_scale,
+                     unsigned long long seed, float dropout_p, void* stream);
+int fedb200_head_bwd(const void* x, const int* first_tok, const float* Wp, const float* Wc, const float* pooled,
+                     const float* pooled_drop, const float* dlogits, float* dpre, float* gWp, float* gbp, float* gWc,
+                     float* gbc, void* dx, int B, int H, int C, unsigned long long seed, float dropout_p,
+                     void* stream);
+/* K9. fused masked-softmax attention over packed variable-length sequences (head_dim 64), tcgen05 + TMA.
+ * qkv is [T, 3H] bf16 (Q | K | V), ctx/dctx [T, H], lse [heads, T] fp32; cu_seqlens is int32 [B+1] on device. */
+int fedb200_attn_fwd(const void* qkv, void* ctx, float* lse, const int* cu_seqlens, int B, int T, int heads,
+                     int max_seqlen, float scale, unsigned long long seed, float dropout_p, void* stream);
+int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dctx, const float* lse, float* delta, void* dqkv,
+                     float* dq_accum, const int* cu_seqlens, int B, int T, int heads, int max_seqlen, float scale,
+                     unsigned long long seed, float dropout_p, void* stream);
+
+/* ---- federated kernels --------------------------------------------------------------------------------------- */
+/* K4. Gram matrix of client updates over a column slice, tcgen05 + TMA straight from (peer) buffers. */
+int fedb200_gram_bf16(const void* const* rows_ptrs, int n_ranks, int rows_per_rank, size_t D, size_t ld,
+                      size_t col_begin, size_t col_end, float* out, int max_ctas, void* stream);
+/* K5. PageRank power iteration + mean±k·sigma mask (reference: All_graphs_IMDB_dataset.ipynb:168-176). */
+int fedb200_pagerank(const float* mat, int n, int mode, double alpha, double tol, int max_iter, double k_sigma,
+                     int low_only, double* ranks, int* mask, double* info, void* stream);
+/* K6. SHA-256 leaves of `src` in chunk_bytes pieces while copying it to `dst` (dst may be NULL or peer memory). */
+int fedb200_sha256_leaves(const void* src, void* dst, size_t nbytes, unsigned int chunk_bytes, void* leaves,
+                          void* stream);
+/* Merkle reduction of n 32-byte nodes (clobbers `nodes`; `scratch` >= ceil(n/2)*32 bytes) -> 32-byte root. */
+int fedb200_merkle_root(void* nodes, void* scratch, unsigned int n, void* root_out, void* stream);
+/* K7. Re-hash n 128-byte block headers and check index / prev-hash links; first_bad = 0xFFFFFFFF if intact. */
+int fedb200_block_validate(const void* headers, const void* recorded_hashes, unsigned int n, void* hashes_out,
+                           unsigned int* first_bad, void* stream);
+
+/* ---- peer-memory runtime (NVLink / NVSwitch) ------------------------------------------------------------------- */
+/* Symmetric allocation: cudaMalloc + CUDA IPC export; the 64-byte handle goes to every peer through the host. */
+int fedb200_peer_alloc(size_t bytes, void** dev_ptr, void* ipc_handle_out64);
+int fedb200_peer_open(const void* ipc_handle64, void** mapped_ptr);
+int fedb200_peer_close(void* mapped_ptr);
+int fedb200_peer_free(void* dev_ptr);
+/* K1. Two-shot fused FedAvg: rank r reduces slice r of every rank's `acc` buffer, scales by 1/sum(weights)
+ * and writes the result to every rank's `out` buffer (and optional bf16 shadow); barriers are flag words in peer
+ * memory.  acc_ptrs / out_ptrs / flag_ptrs: HOST arrays of `world` peer-mapped device pointers (own rank included). */
+int fedb200_fedavg_reduce(const float* const* acc_ptrs, float* const* out_ptrs, void* const* shadow_ptrs,
+                          unsigned int* const* flag_ptrs, int rank, int world, size_t n, float inv_total_weight,
+                          unsigned int epoch, int timeout_ms, void* stream);
+/* Device-side barrier across ranks (flag words in peer memory), usable between any two kernels. */
+int fedb200_peer_barrier(unsigned int* const* flag_ptrs, int rank, int world, unsigned int epoch, int timeout_ms,
+                         void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FEDB200_H */

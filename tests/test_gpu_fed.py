@@ -1,0 +1,94 @@
+"""Federated kernels (SHA-256 / Merkle / block validation / PageRank / cosine Gram) vs host oracles."""
+import hashlib
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _ops():
+    from fedb200.ops import cuda_ops
+    return cuda_ops
+
+
+@pytest.mark.parametrize("nfloats,chunk", [(16, 64), (1024 * 50 + 4, 4096), (3_000_001 * 1, 4096), (4096 * 3, 4096), (1021, 256)])
+def test_sha256_leaves_and_root_bit_exact(cuda_lib, nfloats, chunk):
+    from fedb200.ledger.merkle import leaf_digests, merkle_root
+    ops = _ops()
+    x = torch.randn(nfloats, device="cuda")
+    dst = torch.zeros_like(x)
+    leaves = ops.sha256_leaves(x, dst, chunk)
+    raw = x.cpu().numpy().tobytes()
+    want = leaf_digests(raw, chunk)
+    got = leaves.cpu().numpy()
+    assert got.shape[0] == len(want)
+    for i in (0, len(want) // 2, len(want) - 1):
+        assert bytes(got[i]) == want[i], f"leaf {i} differs"
+    assert all(bytes(g) == w for g, w in zip(got, want))
+    assert torch.equal(dst, x), "fused copy differs from the source"
+    root = ops.merkle_root(leaves.clone())
+    assert bytes(root.cpu().numpy()) == merkle_root(raw, chunk)
+    assert ops.sha256_copy_root(x, None, chunk) == merkle_root(raw, chunk)
+
+
+def test_block_validate_on_device(cuda_lib):
+    from fedb200.ledger import Ledger
+    ops = _ops()
+    led = Ledger(chunk_bytes=256)
+    rng = np.random.default_rng(0)
+    for i in range(300):
+        led.record_update(i // 10, i % 10, (i + 1) % 10, rng.standard_normal(64).astype(np.float32).tobytes(), 5, [i % 10, 3],
+                          timestamp_ns=i)
+    hdr = torch.from_numpy(led.headers_array()).cuda()
+    rec = torch.from_numpy(np.frombuffer(b"".join(led.hashes), dtype=np.uint8).reshape(-1, 32).copy()).cuda()
+    bad, hashes = ops.block_validate(hdr, rec)
+    assert bad == -1
+    assert bytes(hashes[17].cpu().numpy()) == led.hashes[17] == hashlib.sha256(led.blocks[17].pack()).digest()
+    hdr2 = hdr.clone(); hdr2[123, 60] ^= 1            # flip one bit inside block 123's prev_hash
+    assert ops.block_validate(hdr2, rec)[0] == 123
+    hdr3 = hdr.clone(); hdr3[200, 20] ^= 1            # tamper with a payload field: hash 200 changes
+    assert ops.block_validate(hdr3, rec)[0] == 200
+    assert ops.block_validate(hdr3, None)[0] == 201   # without recorded hashes the next link breaks
+
+
+def test_pagerank_matches_notebook_vector(cuda_lib):
+    from fedb200.anomaly import pagerank_anomalies
+    from fedb200.p2p import Topology
+    ops = _ops()
+    w = Topology.reference10().edge_weights()
+    ranks, mask, info = ops.pagerank(torch.tensor(w, dtype=torch.float32, device="cuda"))
+    want_bad, want_r, (lo, hi) = pagerank_anomalies(w)
+    np.testing.assert_allclose(ranks.cpu().numpy(), want_r, rtol=0, atol=2e-7)
+    assert sorted(np.flatnonzero(mask.cpu().numpy()).tolist()) == want_bad == [0, 4, 7, 9]
+    assert abs(info[1].item() - lo) < 1e-6 and abs(info[2].item() - hi) < 1e-6
+
+
+@pytest.mark.parametrize("N,D", [(8, 64 * 200), (10, 100_000), (64, 1_000_000), (128, 64 * 40 + 8)])
+def test_gram_tcgen05(cuda_lib, N, D):
+    ops = _ops()
+    torch.manual_seed(0)
+    d = (torch.randn(N, D, device="cuda") * 0.1).bfloat16()
+    g = ops.gram(d)
+    ref = d.float() @ d.float().T
+    torch.cuda.synchronize()
+    err = (g - ref).abs().max().item()
+    assert err <= 2e-3 * ref.abs().max().item() + 1e-3, f"gram max err {err}"
+
+
+def test_gram_pagerank_flags_poisoned_update(cuda_lib):
+    from fedb200.anomaly import score_updates
+    ops = _ops()
+    torch.manual_seed(1)
+    N, D = 8, 200_000
+    common = torch.randn(D, device="cuda")
+    deltas = torch.stack([common + 0.5 * torch.randn(D, device="cuda") for _ in range(N)])
+    deltas[3] = -4.0 * deltas[3]
+    deltas[6] = torch.randn(D, device="cuda") * 3
+    g = ops.gram(deltas.bfloat16())
+    ranks, mask, info = ops.pagerank(g, mode=1, low_only=True)
+    bad_host, r_host, _ = score_updates(g.double().cpu().numpy())
+    assert sorted(np.flatnonzero(mask.cpu().numpy()).tolist()) == bad_host
+    assert 3 in bad_host and 6 in bad_host
+    np.testing.assert_allclose(ranks.cpu().numpy(), r_host, atol=1e-6)

@@ -1,0 +1,236 @@
+"""sm_100a trainer kernels vs plain PyTorch fp32 references of the same op."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _ops():
+    from fedb200.ops import cuda_ops
+    return cuda_ops
+
+
+def test_adamw_flat_matches_hf_semantics(cuda_lib):
+    from fedb200.trainer.adamw import hf_adamw_reference_step
+    ops = _ops()
+    torch.manual_seed(0)
+    n = 1_000_003
+    p = torch.randn(n, device="cuda"); g = torch.randn(n, device="cuda") * 1e-2
+    m = torch.zeros(n, device="cuda"); v = torch.zeros(n, device="cuda")
+    pr, mr, vr = p.clone(), m.clone(), v.clone()
+    # 16-byte alignment is required: slice from an aligned base
+    shadow = torch.empty(n, dtype=torch.bfloat16, device="cuda")
+    for step in (1, 2, 3):
+        gk = g.clone()
+        ops.adamw_flat(p, gk, m, v, shadow, step, 5e-5, 0.9, 0.999, 1e-6, 0.0, 1.0, True)
+        hf_adamw_reference_step(pr, g, mr, vr, step, 5e-5, 0.9, 0.999, 1e-6, 0.0)
+        assert torch.count_nonzero(gk) == 0
+    torch.testing.assert_close(p, pr, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(m, mr, rtol=1e-5, atol=1e-7)
+    torch.testing.assert_close(v, vr, rtol=1e-5, atol=1e-9)
+    torch.testing.assert_close(shadow.float(), pr.bfloat16().float(), rtol=0, atol=1e-2)
+
+
+def test_mix_n_weighted_sum(cuda_lib):
+    ops = _ops()
+    torch.manual_seed(1)
+    n = 300_001
+    srcs = [torch.randn(n, device="cuda") for _ in range(7)]
+    ws = [0.1 * (i + 1) for i in range(7)]
+    out = torch.empty(n, device="cuda")
+    sh = torch.empty(n, dtype=torch.bfloat16, device="cuda")
+    ops.mix_n(srcs, ws, out, sh)
+    ref = sum(w * s for w, s in zip(ws, srcs))
+    torch.testing.assert_close(out, ref, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(sh.float(), ref.bfloat16().float(), rtol=0, atol=3e-2)
+
+
+def test_colsum(cuda_lib):
+    ops = _ops()
+    x = torch.randn(1000, 192, device="cuda").bfloat16()
+    out = torch.ones(192, device="cuda")
+    ops.colsum_bf16(x, out)
+    torch.testing.assert_close(out, 1.0 + x.float().sum(0), rtol=1e-4, atol=1e-3)
+
+
+@pytest.mark.parametrize("T,H", [(37, 64), (1000, 768), (513, 1024)])
+def test_layernorm_fwd_bwd(cuda_lib, T, H):
+    ops = _ops()
+    torch.manual_seed(2)
+    z = (torch.randn(T, H, device="cuda") * 2 + 0.5).bfloat16()
+    gamma = torch.rand(H, device="cuda") + 0.5
+    beta = torch.randn(H, device="cuda")
+    y = torch.empty_like(z); mean = torch.empty(T, device="cuda"); rstd = torch.empty(T, device="cuda")
+    ops.layernorm_fwd(z, gamma, beta, y, mean, rstd, 1e-12)
+    zr = z.float().requires_grad_(True)
+    gr = gamma.clone().requires_grad_(True); br = beta.clone().requires_grad_(True)
+    yr = torch.nn.functional.layer_norm(zr, (H,), gr, br, 1e-12)
+    torch.testing.assert_close(y.float(), yr, rtol=2e-2, atol=2e-2)
+    dy = torch.randn(T, H, device="cuda").bfloat16()
+    yr.backward(dy.float())
+    dz = torch.empty_like(z)
+    dg = torch.zeros(H, device="cuda"); db = torch.zeros(H, device="cuda"); dbias = torch.zeros(H, device="cuda")
+    ops.layernorm_bwd(dy, z, mean, rstd, gamma, dz, None, dg, db, dbias)
+    torch.testing.assert_close(dz.float(), zr.grad, rtol=3e-2, atol=3e-2)
+    torch.testing.assert_close(dg, gr.grad, rtol=2e-2, atol=2e-1)
+    torch.testing.assert_close(db, br.grad, rtol=2e-2, atol=2e-1)
+    torch.testing.assert_close(dbias, dz.float().sum(0), rtol=2e-2, atol=2e-1)
+
+
+def test_layernorm_bwd_dropout_mask_is_consistent(cuda_lib):
+    """df = dz * mask with keep-rate ~ 0.9 and survivors scaled by 1/0.9."""
+    ops = _ops()
+    T, H = 512, 768
+    z = torch.randn(T, H, device="cuda").bfloat16()
+    gamma = torch.ones(H, device="cuda"); beta = torch.zeros(H, device="cuda")
+    y = torch.empty_like(z); mean = torch.empty(T, device="cuda"); rstd = torch.empty(T, device="cuda")
+    ops.layernorm_fwd(z, gamma, beta, y, mean, rstd)
+    dy = torch.randn(T, H, device="cuda").bfloat16()
+    dz = torch.empty_like(z); df = torch.empty_like(z)
+    dg = torch.zeros(H, device="cuda"); db = torch.zeros(H, device="cuda"); dbias = torch.zeros(H, device="cuda")
+    ops.layernorm_bwd(dy, z, mean, rstd, gamma, dz, df, dg, db, dbias, seed=1234, dropout_p=0.1)
+    keep = (df != 0).float().mean().item()
+    assert 0.88 < keep < 0.92
+    nz = df != 0
+    torch.testing.assert_close(df.float()[nz], (dz.float() / 0.9)[nz], rtol=2e-2, atol=1e-2)
+
+
+def _gemm_ref(layout, A, B):
+    a, b = A.float(), B.float()
+    if layout == 0:
+        return a @ b.T
+    if layout == 1:
+        return a @ b
+    return a.T @ b
+
+
+@pytest.mark.parametrize("layout", [0, 1, 2])
+@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (256, 128, 128), (304, 768, 768), (1000, 64, 192), (4096, 3072, 768)])
+def test_gemm_layouts_plain(cuda_lib, layout, M, N, K):
+    ops = _ops()
+    torch.manual_seed(3)
+    if layout == 0:
+        A = torch.randn(M, K, device="cuda").bfloat16(); B = torch.randn(N, K, device="cuda").bfloat16()
+    elif layout == 1:
+        A = torch.randn(M, K, device="cuda").bfloat16(); B = torch.randn(K, N, device="cuda").bfloat16()
+    else:
+        A = torch.randn(K, M, device="cuda").bfloat16(); B = torch.randn(K, N, device="cuda").bfloat16()
+    ref = _gemm_ref(layout, A, B)
+    if layout == 2:
+        out = torch.zeros(M, N, device="cuda")
+        ops.gemm(layout, A, B, out, M, N, K, epi=ops.EPI_ATOMIC_F32, splits=4)
+        got = out
+    else:
+        out = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+        ops.gemm(layout, A, B, out, M, N, K, epi=ops.EPI_ADD)
+        got = out.float()
+    torch.cuda.synchronize()
+    err = (got - ref).abs().max().item()
+    scale = ref.abs().max().item()
+    assert err <= 2e-2 * scale + 1e-2, f"layout {layout} {M}x{N}x{K}: max err {err} (ref max {scale})"
+
+
+def test_gemm_epilogues(cuda_lib):
+    ops = _ops()
+    torch.manual_seed(4)
+    M, N, K = 520, 768, 256
+    A = (torch.randn(M, K, device="cuda") * 0.5).bfloat16()
+    W = (torch.randn(N, K, device="cuda") * 0.1).bfloat16()
+    bias = torch.randn(N, device="cuda")
+    res = torch.randn(M, N, device="cuda").bfloat16()
+    base = A.float() @ W.float().T + bias
+    out = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    ops.gemm(0, A, W, out, M, N, K, epi=ops.EPI_BIAS, bias=bias)
+    torch.testing.assert_close(out.float(), base, rtol=2e-2, atol=3e-2)
+    ops.gemm(0, A, W, out, M, N, K, epi=ops.EPI_BIAS_DROP_RES, bias=bias, aux=res)
+    torch.testing.assert_close(out.float(), base + res.float(), rtol=2e-2, atol=5e-2)
+    out2 = torch.empty_like(out)
+    ops.gemm(0, A, W, out, M, N, K, epi=ops.EPI_BIAS_GELU, bias=bias, out2=out2)
+    torch.testing.assert_close(out.float(), base, rtol=2e-2, atol=3e-2)
+    torch.testing.assert_close(out2.float(), torch.nn.functional.gelu(out.float()), rtol=2e-2, atol=2e-2)
+    ops.gemm(0, A, W, out, M, N, K, epi=ops.EPI_BIAS_GELU, bias=bias, out2=out2, act=1)
+    torch.testing.assert_close(out2.float(), torch.nn.functional.gelu(out.float(), approximate="tanh"), rtol=2e-2, atol=2e-2)
+    u = torch.randn(M, N, device="cuda").bfloat16()
+    ops.gemm(0, A, W, out, M, N, K, epi=ops.EPI_MUL_GELU_GRAD, aux=u)
+    uf = u.float().requires_grad_(True)
+    torch.nn.functional.gelu(uf).sum().backward()
+    torch.testing.assert_close(out.float(), (A.float() @ W.float().T) * uf.grad, rtol=3e-2, atol=3e-2)
+    # dropout epilogue: same mask as the LN backward regenerates
+    ops.gemm(0, A, W, out, M, N, K, epi=ops.EPI_BIAS_DROP_RES, bias=bias, aux=torch.zeros_like(res), seed=77, dropout_p=0.1)
+    keep = (out != 0).float().mean().item()
+    assert 0.88 < keep < 0.92
+    H = N
+    z = torch.randn(M, H, device="cuda").bfloat16()
+    g1 = torch.ones(H, device="cuda")
+    y = torch.empty_like(z); mean = torch.empty(M, device="cuda"); rstd = torch.empty(M, device="cuda")
+    ops.layernorm_fwd(z, g1, torch.zeros(H, device="cuda"), y, mean, rstd)
+    dz = torch.empty_like(z); df = torch.empty_like(z)
+    dg = torch.zeros(H, device="cuda"); db = torch.zeros(H, device="cuda")
+    ops.layernorm_bwd(torch.randn(M, H, device="cuda").bfloat16(), z, mean, rstd, g1, dz, df, dg, db, None, seed=77, dropout_p=0.1)
+    big = dz.float().abs() > 1e-3
+    assert torch.equal((out != 0)[big], (df != 0)[big]), "GEMM epilogue and LN backward disagree on the dropout mask"
+
+
+def test_embed_fwd_bwd(cuda_lib):
+    ops = _ops()
+    torch.manual_seed(5)
+    T, H, V = 777, 768, 1000
+    word = torch.randn(V, H, device="cuda") * 0.02; posw = torch.randn(512, H, device="cuda") * 0.02
+    typew = torch.randn(2, H, device="cuda") * 0.02
+    gamma = torch.rand(H, device="cuda") + 0.5; beta = torch.randn(H, device="cuda") * 0.1
+    ids = torch.randint(0, V, (T,), device="cuda", dtype=torch.int32)
+    pos = torch.randint(0, 512, (T,), device="cuda", dtype=torch.int32)
+    tt = torch.randint(0, 2, (T,), device="cuda", dtype=torch.int32)
+    out = torch.empty(T, H, dtype=torch.bfloat16, device="cuda")
+    mean = torch.empty(T, device="cuda"); rstd = torch.empty(T, device="cuda")
+    ops.embed_fwd(ids, pos, tt, word, posw, typew, gamma, beta, out, mean, rstd)
+    wr, pr, tr = (t.clone().requires_grad_(True) for t in (word, posw, typew))
+    gr, br = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    ref = torch.nn.functional.layer_norm(wr[ids.long()] + pr[pos.long()] + tr[tt.long()], (H,), gr, br, 1e-12)
+    torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=2e-2)
+    dx = torch.randn(T, H, device="cuda").bfloat16()
+    ref.backward(dx.float())
+    gw, gp, gt = torch.zeros_like(word), torch.zeros_like(posw), torch.zeros_like(typew)
+    dg, db = torch.zeros(H, device="cuda"), torch.zeros(H, device="cuda")
+    ops.embed_bwd(dx, ids, pos, tt, word, posw, typew, gamma, mean, rstd, gw, gp, gt, dg, db)
+    torch.testing.assert_close(gw, wr.grad, rtol=1e-3, atol=1e-3)
+    torch.testing.assert_close(gp, pr.grad, rtol=1e-3, atol=1e-3)
+    torch.testing.assert_close(gt, tr.grad, rtol=1e-3, atol=5e-2)
+    torch.testing.assert_close(dg, gr.grad, rtol=1e-3, atol=5e-2)
+    torch.testing.assert_close(db, br.grad, rtol=1e-3, atol=5e-2)
+
+
+@pytest.mark.parametrize("C", [2, 41])
+def test_head_fwd_bwd(cuda_lib, C):
+    ops = _ops()
+    torch.manual_seed(6)
+    B, H, T = 32, 768, 4000
+    x = torch.randn(T, H, device="cuda").bfloat16()
+    first = torch.arange(B, device="cuda", dtype=torch.int32) * 100
+    Wp = torch.randn(H, H, device="cuda") * 0.03; bp = torch.randn(H, device="cuda") * 0.1
+    Wc = torch.randn(C, H, device="cuda") * 0.05; bc = torch.randn(C, device="cuda") * 0.1
+    labels = torch.randint(0, C, (B,), device="cuda", dtype=torch.int32)
+    pooled = torch.empty(B, H, device="cuda"); pd = torch.empty(B, H, device="cuda")
+    logits = torch.empty(B, C, device="cuda"); loss = torch.empty(B, device="cuda")
+    pred = torch.empty(B, dtype=torch.int32, device="cuda"); dlog = torch.empty(B, C, device="cuda")
+    ops.head_fwd(x, first, Wp, bp, Wc, bc, labels, pooled, pd, logits, loss, pred, dlog, 1.0 / B)
+    h0 = x[first.long()].float().requires_grad_(True)
+    Wpr, bpr, Wcr, bcr = (t.clone().requires_grad_(True) for t in (Wp, bp, Wc, bc))
+    lr_ = torch.tanh(h0 @ Wpr.T + bpr) @ Wcr.T + bcr
+    ref_loss = torch.nn.functional.cross_entropy(lr_, labels.long())
+    torch.testing.assert_close(logits, lr_, rtol=1e-3, atol=1e-3)
+    torch.testing.assert_close(loss.mean(), ref_loss, rtol=1e-4, atol=1e-4)
+    assert torch.equal(pred.long(), lr_.argmax(-1))
+    ref_loss.backward()
+    gWp, gbp, gWc, gbc = torch.zeros_like(Wp), torch.zeros_like(bp), torch.zeros_like(Wc), torch.zeros_like(bc)
+    dpre = torch.empty(B, H, device="cuda")
+    dx = torch.zeros(T, H, dtype=torch.bfloat16, device="cuda")
+    ops.head_bwd(x, first, Wp, Wc, pooled, pd, dlog, dpre, gWp, gbp, gWc, gbc, dx)
+    torch.testing.assert_close(gWc, Wcr.grad, rtol=1e-3, atol=1e-4)
+    torch.testing.assert_close(gbc, bcr.grad, rtol=1e-3, atol=1e-4)
+    torch.testing.assert_close(gWp, Wpr.grad, rtol=1e-3, atol=1e-4)
+    torch.testing.assert_close(gbp, bpr.grad, rtol=1e-3, atol=1e-4)
+    torch.testing.assert_close(dx[first.long()].float(), h0.grad, rtol=2e-2, atol=1e-4)
+    assert torch.count_nonzero(dx) <= B * H
