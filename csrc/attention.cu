@@ -1,0 +1,497 @@
+// Fused masked-softmax attention, forward and backward (K9), on tcgen05 / TMEM with TMA-fed operands.
+// Replaces HF BertSelfAttention (QK^T/sqrt(d) + padding mask -> softmax -> dropout -> PV; module dump at
+// serverless_cancer_classification_with_BioBERT.ipynb:537-545).  Sequences are PACKED (no pad tokens):
+// qkv is [T, 3H] bf16 (Q | K | V column blocks, head h at columns h*64), cu_seqlens gives each sequence's
+// token range, so the padding mask of the reference becomes "kv index < sequence length".
+//
+// forward, one CTA per (128-row q tile, head, sequence); 192 threads:
+//   warp 0 TMA   : Q tile once, then K_j / V_j tiles (2-deep ring)
+//   warp 1 MMA   : S = Q K_j^T  (M128 N128 K64, both K-major) -> TMEM;  O_j = P_j V_j (A = P from smem,
+//                  B = V tile read MN-major, so V is never transposed)
+//   warps 2-5    : one thread per q row: two passes over S in TMEM (row max, then exp2 / row sum / dropout),
+//                  P written as bf16 into the 128B-swizzled K-major layout, running O kept in registers
+// backward, one CTA per (128-row kv tile, head, sequence), looping over q tiles:
+//   S^T = K Q_i^T and dP^T = V dO_i^T land in TMEM with the kv index on the lanes, so the thread that owns a kv
+//   row produces its rows of P^T and dS^T directly in the A-operand layout; the same dS^T buffer is read
+//   K-major for dK += dS^T Q_i and MN-major for dQ_i = dS K (no transposes anywhere).  dV/dK accumulate in
+//   TMEM across the q loop; dQ tiles are reduced across kv CTAs with fp32 vector atomics into `dq_accum`
+//   (scratch, [T, H] fp32, must be zero on entry; the finishing kernel converts it to bf16 and re-zeroes it).
+// Dropout uses the library-wide counter RNG: row = head * T + q token, col = kv position in the sequence.
+// lse is stored in base-2 units of the scaled scores: lse2 = max2 + log2(sum), p = exp2(s*scale*log2e - lse2).
+#include "common.cuh"
+#include "../include/fedb200.h"
+
+namespace fedb {
+
+constexpr int AT_THREADS = 192;
+constexpr int AT_TILE = 128 * 64 * 2;        // 16 KB: [128 rows x 64 bf16]
+constexpr float LOG2E = 1.4426950408889634f;
+
+// write 8 consecutive bf16 (one 16-byte chunk `cc` of the 128-byte row `r`) into a 128B-swizzled tile
+__device__ __forceinline__ void st_swizzled_chunk(uint8_t* tile, int r, int cc, const float* v) {
+    uint4 o;
+    o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
+    o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
+    *reinterpret_cast<uint4*>(tile + r * 128 + ((cc ^ (r & 7)) << 4)) = o;
+}
+
+__device__ __forceinline__ uint64_t desc_kmajor(uint32_t tile_addr, int kstep) {     // 16 k-elements per step
+    return umma_smem_desc(tile_addr + kstep * 32, 16, 1024);
+}
+__device__ __forceinline__ uint64_t desc_mnmajor(uint32_t tile_addr, int kstep, uint32_t lbo) {   // 16 k-rows per step
+    return umma_smem_desc(tile_addr + kstep * 2048, lbo, 1024);
+}
+
+// =================================================================================================
+// forward
+// =================================================================================================
+__global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv,
+                                                                 __nv_bfloat16* __restrict__ ctx, float* __restrict__ lse,
+                                                                 const int* __restrict__ cu_seqlens, int T, int H,
+                                                                 float scale_log2, uint64_t seed, uint32_t keep_thresh,
+                                                                 float inv_keep, int use_dropout) {
+    const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * 128;
+    const int tok0 = cu_seqlens[b], len = cu_seqlens[b + 1] - tok0;
+    if (q0 >= len) return;
+    const int n_kv = (len + 127) / 128;
+
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* sQ = smem;
+    uint8_t* sK = sQ + AT_TILE;              // 2 stages
+    uint8_t* sV = sK + 2 * AT_TILE;          // 2 stages
+    uint8_t* sP = sV + 2 * AT_TILE;          // 2 tiles (kv 0-63 | 64-127)
+    __shared__ __align__(8) uint64_t q_full, k_full[2], v_full[2], k_empty[2], v_empty[2], s_full, p_ready, o_full;
+    __shared__ uint32_t tmem_slot;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tm_qkv);
+        mbar_init(&q_full, 1);
+        for (int s = 0; s < 2; ++s) { mbar_init(&k_full[s], 1); mbar_init(&v_full[s], 1); mbar_init(&k_empty[s], 1); mbar_init(&v_empty[s], 1); }
+        mbar_init(&s_full, 1); mbar_init(&p_ready, 128); mbar_init(&o_full, 1);
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc(&tmem_slot, 256);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_s = tmem_slot, tmem_o = tmem_slot + 128;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_expect_tx(&q_full, AT_TILE);
+            tma_load_2d(sQ, &tm_qkv, &q_full, h * 64, tok0 + q0);
+            for (int j = 0; j < n_kv; ++j) {
+                const int s = j & 1;
+                const uint32_t ph = ((uint32_t)(j >> 1) & 1u) ^ 1u;
+                mbar_wait(&k_empty[s], ph);
+                mbar_expect_tx(&k_full[s], AT_TILE);
+                tma_load_2d(sK + s * AT_TILE, &tm_qkv, &k_full[s], H + h * 64, tok0 + j * 128);
+                mbar_wait(&v_empty[s], ph);
+                mbar_expect_tx(&v_full[s], AT_TILE);
+                tma_load_2d(sV + s * AT_TILE, &tm_qkv, &v_full[s], 2 * H + h * 64, tok0 + j * 128);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
+            constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
+            const uint32_t aQ = smem_u32(sQ), aP = smem_u32(sP);
+            mbar_wait(&q_full, 0);
+            mbar_wait(&k_full[0], 0);
+            tc_fence_after_sync();
+#pragma unroll
+            for (int k = 0; k < 4; ++k) umma_bf16(tmem_s, desc_kmajor(aQ, k), desc_kmajor(smem_u32(sK), k), idesc_s, k > 0);
+            umma_commit(&s_full);
+            umma_commit(&k_empty[0]);
+            for (int j = 0; j < n_kv; ++j) {
+                const int s = j & 1;
+                mbar_wait(&p_ready, (uint32_t)j & 1u);
+                mbar_wait(&v_full[s], (uint32_t)(j >> 1) & 1u);
+                tc_fence_after_sync();
+                const uint32_t aV = smem_u32(sV + s * AT_TILE);
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    umma_bf16(tmem_o, desc_kmajor(aP + (k >> 2) * AT_TILE, k & 3), desc_mnmajor(aV, k, 8192), idesc_o, k > 0);
+                umma_commit(&o_full);
+                umma_commit(&v_empty[s]);
+                if (j + 1 < n_kv) {
+                    const int s1 = (j + 1) & 1;
+                    mbar_wait(&k_full[s1], (uint32_t)((j + 1) >> 1) & 1u);
+                    tc_fence_after_sync();
+                    const uint32_t aK = smem_u32(sK + s1 * AT_TILE);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) umma_bf16(tmem_s, desc_kmajor(aQ, k), desc_kmajor(aK, k), idesc_s, k > 0);
+                    umma_commit(&s_full);
+                    umma_commit(&k_empty[s1]);
+                }
+            }
+        }
+    } else {
+        // ---------------- softmax / output warps: one thread per q row ----------------
+        const int quad = warp & 3;
+        const int r = quad * 32 + lane;                       // row within the q tile == TMEM lane
+        const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+        const int q_tok = tok0 + q0 + r;
+        const bool q_ok = q0 + r < len;
+        const uint32_t drop_row = (uint32_t)(h * T + q_tok);
+        float o[64];
+#pragma unroll
+        for (int d = 0; d < 64; ++d) o[d] = 0.f;
+        float m_run = -INFINITY, l_run = 0.f;
+        for (int j = 0; j < n_kv; ++j) {
+            mbar_wait(&s_full, (uint32_t)j & 1u);
+            tc_fence_after_sync();
+            const int kv_valid = min(128, len - j * 128);
+            // pass 1: row max
+            float mx = -INFINITY;
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                uint32_t raw[32];
+                tmem_ld_32x32(tmem_s + lane_addr + c * 32, raw);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                    if (c * 32 + i < kv_valid) mx = fmaxf(mx, __uint_as_float(raw[i]));
+            }
+            const float m_new = fmaxf(m_run, mx * scale_log2);
+            const float alpha = exp2f(m_run - m_new);
+            l_run *= alpha;
+            // pass 2: probabilities -> smem (bf16, swizzled K-major), row sum
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                uint32_t raw[32];
+                tmem_ld_32x32(tmem_s + lane_addr + c * 32, raw);
+                tmem_ld_wait();
+                float p[32];
+                float rs = 0.f;
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    p[i] = (c * 32 + i < kv_valid) ? exp2f(__uint_as_float(raw[i]) * scale_log2 - m_new) : 0.f;
+                    rs += p[i];
+                }
+                l_run += rs;
+                if (use_dropout) {
+#pragma unroll
+                    for (int g = 0; g < 4; ++g)
+                        dropout_apply8(p + g * 8, seed, drop_row, (uint32_t)(j * 128 + c * 32 + g * 8), keep_thresh, inv_keep);
+                }
+                uint8_t* tile = sP + (c >> 1) * AT_TILE;
+#pragma unroll
+                for (int g = 0; g < 4; ++g) st_swizzled_chunk(tile, r, (c & 1) * 4 + g, p + g * 8);
+            }
+            fence_async_smem();
+            tc_fence_before_sync();
+            mbar_arrive(&p_ready);
+            m_run = m_new;
+            // fold this block's P V into the running output
+            mbar_wait(&o_full, (uint32_t)j & 1u);
+            tc_fence_after_sync();
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                uint32_t raw[32];
+                tmem_ld_32x32(tmem_o + lane_addr + c * 32, raw);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) o[c * 32 + i] = o[c * 32 + i] * alpha + __uint_as_float(raw[i]);
+            }
+            tc_fence_before_sync();
+        }
+        if (q_ok) {
+            const float inv = 1.f / l_run;
+            __nv_bfloat16* dst = ctx + (size_t)q_tok * H + h * 64;
+#pragma unroll
+            for (int g = 0; g < 8; ++g) {
+                uint4 pk;
+                pk.x = pack_bf16x2(o[g * 8 + 0] * inv, o[g * 8 + 1] * inv); pk.y = pack_bf16x2(o[g * 8 + 2] * inv, o[g * 8 + 3] * inv);
+                pk.z = pack_bf16x2(o[g * 8 + 4] * inv, o[g * 8 + 5] * inv); pk.w = pack_bf16x2(o[g * 8 + 6] * inv, o[g * 8 + 7] * inv);
+                *reinterpret_cast<uint4*>(dst + g * 8) = pk;
+            }
+            lse[(size_t)h * T + q_tok] = m_run + log2f(l_run);
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_slot, 256);
+}
+
+// =================================================================================================
+// backward
+// =================================================================================================
+// delta[h*T + tok] = sum_d dctx[tok, h*64 + d] * ctx[tok, h*64 + d]
+__global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __restrict__ ctx, const __nv_bfloat16* __restrict__ dctx,
+                                                         float* __restrict__ delta, int T, int heads) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= T * heads) return;
+    const int tok = idx / heads, h = idx % heads;
+    const size_t off = (size_t)tok * heads * 64 + h * 64;
+    float s = 0.f;
+#pragma unroll
+    for (int g = 0; g < 8; ++g) {
+        const uint4 a = *reinterpret_cast<const uint4*>(ctx + off + g * 8);
+        const uint4 b = *reinterpret_cast<const uint4*>(dctx + off + g * 8);
+        const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), a2 = unpack_bf16x2(a.z), a3 = unpack_bf16x2(a.w);
+        const float2 b0 = unpack_bf16x2(b.x), b1 = unpack_bf16x2(b.y), b2 = unpack_bf16x2(b.z), b3 = unpack_bf16x2(b.w);
+        s += a0.x * b0.x + a0.y * b0.y + a1.x * b1.x + a1.y * b1.y + a2.x * b2.x + a2.y * b2.y + a3.x * b3.x + a3.y * b3.y;
+    }
+    delta[(size_t)h * T + tok] = s;
+}
+
+// dqkv[:, 0:H] = bf16(dq_accum); dq_accum = 0 (ready for the next call)
+__global__ void __launch_bounds__(256) attn_dq_finish_kernel(float* __restrict__ dq_accum, __nv_bfloat16* __restrict__ dqkv,
+                                                             int T, int H) {
+    const size_t n4 = (size_t)T * H / 4, stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        const float4 v = reinterpret_cast<float4*>(dq_accum)[i];
+        reinterpret_cast<float4*>(dq_accum)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        const size_t e = i * 4, tok = e / H, col = e % H;
+        uint2 pk;
+        pk.x = pack_bf16x2(v.x, v.y); pk.y = pack_bf16x2(v.z, v.w);
+        *reinterpret_cast<uint2*>(dqkv + tok * 3 * (size_t)H + col) = pk;
+    }
+}
+
+__global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv,
+                                                                 const __grid_constant__ CUtensorMap tm_do,
+                                                                 const float* __restrict__ lse, const float* __restrict__ delta,
+                                                                 __nv_bfloat16* __restrict__ dqkv, float* __restrict__ dq_accum,
+                                                                 const int* __restrict__ cu_seqlens, int T, int H,
+                                                                 float scale, float scale_log2, uint64_t seed,
+                                                                 uint32_t keep_thresh, float inv_keep, int use_dropout) {
+    const int b = blockIdx.z, h = blockIdx.y, kv0 = blockIdx.x * 128;
+    const int tok0 = cu_seqlens[b], len = cu_seqlens[b + 1] - tok0;
+    if (kv0 >= len) return;
+    const int n_q = (len + 127) / 128;
+
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* sK = smem;
+    uint8_t* sV = sK + AT_TILE;
+    uint8_t* sQ = sV + AT_TILE;              // 2 stages
+    uint8_t* sdO = sQ + 2 * AT_TILE;         // 2 stages
+    uint8_t* sP = sdO + 2 * AT_TILE;         // Pd^T : 2 tiles (q 0-63 | 64-127), rows = kv
+    uint8_t* sdS = sP + 2 * AT_TILE;         // dS^T : 2 tiles
+    __shared__ __align__(8) uint64_t kv_full, qdo_full[2], qdo_empty[2], sdp_full, pds_ready, dq_full, dq_empty, dkv_full;
+    __shared__ uint32_t tmem_slot;
+    __shared__ float s_lse[2][128], s_delta[2][128];
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tm_qkv);
+        tma_prefetch_desc(&tm_do);
+        mbar_init(&kv_full, 1);
+        for (int s = 0; s < 2; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_empty[s], 1); }
+        mbar_init(&sdp_full, 1); mbar_init(&pds_ready, 128); mbar_init(&dq_full, 1); mbar_init(&dq_empty, 128);
+        mbar_init(&dkv_full, 1);
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc(&tmem_slot, 512);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tm_st = tmem_slot, tm_dpt = tmem_slot + 128, tm_dv = tmem_slot + 256, tm_dk = tmem_slot + 320,
+                   tm_dq = tmem_slot + 384;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_expect_tx(&kv_full, 2 * AT_TILE);
+            tma_load_2d(sK, &tm_qkv, &kv_full, H + h * 64, tok0 + kv0);
+            tma_load_2d(sV, &tm_qkv, &kv_full, 2 * H + h * 64, tok0 + kv0);
+            for (int i = 0; i < n_q; ++i) {
+                const int s = i & 1;
+                mbar_wait(&qdo_empty[s], ((uint32_t)(i >> 1) & 1u) ^ 1u);
+                mbar_expect_tx(&qdo_full[s], 2 * AT_TILE);
+                tma_load_2d(sQ + s * AT_TILE, &tm_qkv, &qdo_full[s], h * 64, tok0 + i * 128);
+                tma_load_2d(sdO + s * AT_TILE, &tm_do, &qdo_full[s], h * 64, tok0 + i * 128);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc_nn = umma_idesc_bf16(128, 128, 0, 0);     // S^T, dP^T
+            constexpr uint32_t idesc_kmn = umma_idesc_bf16(128, 64, 0, 1);     // dV, dK
+            constexpr uint32_t idesc_mnmn = umma_idesc_bf16(128, 64, 1, 1);    // dQ
+            const uint32_t aK = smem_u32(sK), aV = smem_u32(sV), aP = smem_u32(sP), aS = smem_u32(sdS);
+            mbar_wait(&kv_full, 0);
+            for (int i = 0; i < n_q; ++i) {
+                const int s = i & 1;
+                const uint32_t aQ = smem_u32(sQ + s * AT_TILE), aO = smem_u32(sdO + s * AT_TILE);
+                mbar_wait(&qdo_full[s], (uint32_t)(i >> 1) & 1u);
+                tc_fence_after_sync();
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_bf16(tm_st, desc_kmajor(aK, k), desc_kmajor(aQ, k), idesc_nn, k > 0);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_bf16(tm_dpt, desc_kmajor(aV, k), desc_kmajor(aO, k), idesc_nn, k > 0);
+                umma_commit(&sdp_full);
+                mbar_wait(&pds_ready, (uint32_t)i & 1u);
+                tc_fence_after_sync();
+#pragma unroll
+                for (int k = 0; k < 8; ++k)      // dV += Pd^T dO_i   (reduction over q)
+                    umma_bf16(tm_dv, desc_kmajor(aP + (k >> 2) * AT_TILE, k & 3), desc_mnmajor(aO, k, 8192), idesc_kmn, (i | k) != 0);
+#pragma unroll
+                for (int k = 0; k < 8; ++k)      // dK += dS^T Q_i
+                    umma_bf16(tm_dk, desc_kmajor(aS + (k >> 2) * AT_TILE, k & 3), desc_mnmajor(aQ, k, 8192), idesc_kmn, (i | k) != 0);
+                mbar_wait(&dq_empty, ((uint32_t)i & 1u) ^ 1u);
+                tc_fence_after_sync();
+#pragma unroll
+                for (int k = 0; k < 8; ++k)      // dQ_i = dS K   (A = dS^T buffer read MN-major, reduction over kv)
+                    umma_bf16(tm_dq, desc_mnmajor(aS, k, AT_TILE), desc_mnmajor(aK, k, 8192), idesc_mnmn, k > 0);
+                umma_commit(&dq_full);
+                umma_commit(&qdo_empty[s]);
+            }
+            umma_commit(&dkv_full);
+        }
+    } else {
+        const int quad = warp & 3;
+        const int r = quad * 32 + lane;                       // kv row for S^T/dP^T/dK/dV, q row for dQ
+        const int t128 = (warp - 2) * 32 + lane;              // 0..127 linear id among the compute threads
+        const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+        const int kv = kv0 + r;
+        const bool kv_ok = kv < len;
+        for (int i = 0; i < n_q; ++i) {
+            const int qb = i * 128, sl = i & 1;
+            {   // stage lse / delta of this q tile (double-buffered by i parity; published by the named barrier)
+                const int q = qb + t128;
+                s_lse[sl][t128] = q < len ? lse[(size_t)h * T + tok0 + q] : 0.f;
+                s_delta[sl][t128] = q < len ? delta[(size_t)h * T + tok0 + q] : 0.f;
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            mbar_wait(&sdp_full, (uint32_t)i & 1u);
+            tc_fence_after_sync();
+            if (i > 0) {
+                // the previous iteration's dV/dK/dQ MMAs read sP/sdS: they are complete once dq_full(i-1) fired,
+                // which this thread already waited on below before looping.
+            }
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                uint32_t rs[32], rp[32];
+                tmem_ld_32x32(tm_st + lane_addr + c * 32, rs);
+                tmem_ld_32x32(tm_dpt + lane_addr + c * 32, rp);
+                tmem_ld_wait();
+                float pd[32], ds[32];
+#pragma unroll
+                for (int jq = 0; jq < 32; ++jq) {
+                    const int ql = c * 32 + jq, q = qb + ql;
+                    const bool ok = kv_ok && q < len;
+                    const float p = ok ? exp2f(__uint_as_float(rs[jq]) * scale_log2 - s_lse[sl][ql]) : 0.f;
+                    float mk = 1.f;
+                    if (use_dropout)
+                        mk = dropout_scale(seed, (uint32_t)(h * T + tok0 + q), (uint32_t)kv, keep_thresh, inv_keep);
+                    pd[jq] = p * mk;
+                    ds[jq] = p * (__uint_as_float(rp[jq]) * mk - s_delta[sl][ql]) * scale;
+                }
+                uint8_t* tp = sP + (c >> 1) * AT_TILE;
+                uint8_t* td = sdS + (c >> 1) * AT_TILE;
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    st_swizzled_chunk(tp, r, (c & 1) * 4 + g, pd + g * 8);
+                    st_swizzled_chunk(td, r, (c & 1) * 4 + g, ds + g * 8);
+                }
+            }
+            fence_async_smem();
+            tc_fence_before_sync();
+            mbar_arrive(&pds_ready);
+            // dQ tile: lanes are q rows now
+            mbar_wait(&dq_full, (uint32_t)i & 1u);
+            tc_fence_after_sync();
+            const int q = qb + r;
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                uint32_t raw[32];
+                tmem_ld_32x32(tm_dq + lane_addr + c * 32, raw);
+                tmem_ld_wait();
+                if (q < len) {
+                    float* dst = dq_accum + (size_t)(tok0 + q) * H + h * 64 + c * 32;
+#pragma unroll
+                    for (int g = 0; g < 8; ++g)
+                        atomicAdd(reinterpret_cast<float4*>(dst + g * 4),
+                                  make_float4(__uint_as_float(raw[g * 4]), __uint_as_float(raw[g * 4 + 1]),
+                                              __uint_as_float(raw[g * 4 + 2]), __uint_as_float(raw[g * 4 + 3])));
+                }
+            }
+            tc_fence_before_sync();
+            mbar_arrive(&dq_empty);
+        }
+        mbar_wait(&dkv_full, 0);
+        tc_fence_after_sync();
+#pragma unroll
+        for (int which = 0; which < 2; ++which) {            // 0: dK -> K block, 1: dV -> V block
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                uint32_t raw[32];
+                tmem_ld_32x32((which ? tm_dv : tm_dk) + lane_addr + c * 32, raw);
+                tmem_ld_wait();
+                if (kv_ok) {
+                    __nv_bfloat16* dst = dqkv + (size_t)(tok0 + kv) * 3 * H + (which ? 2 * H : H) + h * 64 + c * 32;
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        uint4 pk;
+                        pk.x = pack_bf16x2(__uint_as_float(raw[g * 8 + 0]), __uint_as_float(raw[g * 8 + 1]));
+                        pk.y = pack_bf16x2(__uint_as_float(raw[g * 8 + 2]), __uint_as_float(raw[g * 8 + 3]));
+                        pk.z = pack_bf16x2(__uint_as_float(raw[g * 8 + 4]), __uint_as_float(raw[g * 8 + 5]));
+                        pk.w = pack_bf16x2(__uint_as_float(raw[g * 8 + 6]), __uint_as_float(raw[g * 8 + 7]));
+                        *reinterpret_cast<uint4*>(dst + g * 8) = pk;
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_slot, 512);
+}
+
+}  // namespace fedb
+
+using namespace fedb;
+
+extern "C" int fedb200_attn_fwd(const void* qkv, void* ctx, float* lse, const int* cu_seqlens, int B, int T, int heads,
+                                int max_seqlen, float scale, unsigned long long seed, float dropout_p, void* stream) {
+    FEDB_REQUIRE(B > 0 && T > 0 && heads > 0 && max_seqlen > 0, "attn_fwd: empty problem");
+    const int H = heads * 64;
+    CUtensorMap tm;
+    int e = make_tmap_bf16_2d(&tm, qkv, (uint64_t)T, (uint64_t)3 * H, (uint64_t)3 * H, 128, 64);
+    if (e) return e;
+    const size_t smem = 7 * AT_TILE + 1024;
+    static bool configured = false;
+    if (!configured) {
+        FEDB_CHECK(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    dim3 grid((max_seqlen + 127) / 128, heads, B);
+    attn_fwd_kernel<<<grid, AT_THREADS, smem, (cudaStream_t)stream>>>(
+        tm, (__nv_bfloat16*)ctx, lse, cu_seqlens, T, H, scale * LOG2E, seed, dropout_thresh16(dropout_p),
+        1.0f / (1.0f - dropout_p), dropout_p > 0.f);
+    FEDB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dctx, const float* lse, float* delta,
+                                void* dqkv, float* dq_accum, const int* cu_seqlens, int B, int T, int heads,
+                                int max_seqlen, float scale, unsigned long long seed, float dropout_p, void* stream) {
+    FEDB_REQUIRE(B > 0 && T > 0 && heads > 0 && max_seqlen > 0, "attn_bwd: empty problem");
+    const int H = heads * 64;
+    cudaStream_t s = (cudaStream_t)stream;
+    CUtensorMap tm, tmdo;
+    int e = make_tmap_bf16_2d(&tm, qkv, (uint64_t)T, (uint64_t)3 * H, (uint64_t)3 * H, 128, 64);
+    if (e) return e;
+    e = make_tmap_bf16_2d(&tmdo, dctx, (uint64_t)T, (uint64_t)H, (uint64_t)H, 128, 64);
+    if (e) return e;
+    attn_delta_kernel<<<(T * heads + 255) / 256, 256, 0, s>>>((const __nv_bfloat16*)ctx, (const __nv_bfloat16*)dctx, delta, T, heads);
+    FEDB_LAUNCH_CHECK();
+    const size_t smem = 10 * AT_TILE + 1024;
+    static bool configured = false;
+    if (!configured) {
+        FEDB_CHECK(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    dim3 grid((max_seqlen + 127) / 128, heads, B);
+    attn_bwd_kernel<<<grid, AT_THREADS, smem, s>>>(tm, tmdo, lse, delta, (__nv_bfloat16*)dqkv, dq_accum, cu_seqlens, T, H,
+                                                   scale, scale * LOG2E, seed, dropout_thresh16(dropout_p),
+                                                   1.0f / (1.0f - dropout_p), dropout_p > 0.f);
+    FEDB_LAUNCH_CHECK();
+    int blocks = sm_count() * 8;
+    attn_dq_finish_kernel<<<blocks, 256, 0, s>>>(dq_accum, (__nv_bfloat16*)dqkv, T, H);
+    FEDB_LAUNCH_CHECK();
+    return 0;
+}
