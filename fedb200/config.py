@@ -25,6 +25,9 @@ MODEL_PRESETS = {
                        intermediate_size=4096),
     "albert-base-v2": dict(arch="albert", vocab_size=30000, hidden_size=768, num_layers=12, num_heads=12,
                            intermediate_size=3072, embedding_size=128),
+    # small head_dim-64 shape for GPU tests of the fused trainer
+    "bert-mini": dict(arch="bert", vocab_size=2048, hidden_size=128, num_layers=2, num_heads=2,
+                      intermediate_size=256, max_position=512),
     # tiny shapes for CPU tests
     "bert-tiny": dict(arch="bert", vocab_size=512, hidden_size=64, num_layers=2, num_heads=2,
                       intermediate_size=128, max_position=128),

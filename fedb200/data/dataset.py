@@ -70,6 +70,29 @@ def collate_padded(ds: TokenDataset, idx: np.ndarray, pin: bool = False) -> Dict
     return out
 
 
+def collate_packed(ds: TokenDataset, idx: np.ndarray, pin: bool = False) -> Dict[str, torch.Tensor]:
+    """Packed (pad-free) collation for the fused trainer: ``ids/pos/tt`` are ``[T]`` int32 with the
+    sequences laid end to end, ``cu_seqlens`` is ``[B+1]``.  Same samples as :func:`collate_padded`, none
+    of the pad tokens."""
+    lens = (ds.offsets[idx + 1] - ds.offsets[idx]).astype(np.int64)
+    B, T = len(idx), int(lens.sum())
+    cu = np.zeros(B + 1, dtype=np.int32)
+    np.cumsum(lens, out=cu[1:])
+    ids = np.empty(T, dtype=np.int32)
+    pos = np.empty(T, dtype=np.int32)
+    for r, i in enumerate(idx):
+        n = int(lens[r])
+        ids[cu[r]:cu[r] + n] = ds.tokens[ds.offsets[i]:ds.offsets[i] + n]
+        pos[cu[r]:cu[r] + n] = np.arange(n, dtype=np.int32)
+    out = {"ids": torch.from_numpy(ids), "pos": torch.from_numpy(pos), "tt": torch.zeros(T, dtype=torch.int32),
+           "cu_seqlens": torch.from_numpy(cu), "labels": torch.from_numpy(ds.labels[idx].astype(np.int32))}
+    if pin and torch.cuda.is_available():
+        out = {k: v.pin_memory() for k, v in out.items()}
+    out["max_len"] = int(lens.max()) if B else 0
+    out["num_tokens"] = T
+    return out
+
+
 class BatchLoader:
     """Minimal ``DataLoader`` replacement: batch 32, optional shuffle, padded collation.
 
@@ -96,6 +119,10 @@ class BatchLoader:
     def __iter__(self) -> Iterator[Dict[str, torch.Tensor]]:
         for idx in self.batch_indices():
             yield collate_padded(self.dataset, idx, pin=self.pin)
+
+    def packed(self) -> Iterator[Dict[str, torch.Tensor]]:
+        for idx in self.batch_indices():
+            yield collate_packed(self.dataset, idx, pin=self.pin)
 
     @property
     def num_samples(self) -> int:

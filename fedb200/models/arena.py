@@ -30,8 +30,12 @@ def param_layout(shapes: "OrderedDict[str, Tuple[int, ...]]") -> Tuple["OrderedD
 
 class FlatArena:
     def __init__(self, shapes: "OrderedDict[str, Tuple[int, ...]]", dtype=torch.float32, device="cpu",
-                 buffer: torch.Tensor | None = None):
+                 buffer: torch.Tensor | None = None, key_order: Iterable[str] | None = None):
+        """``shapes`` order is the memory layout; ``key_order`` (default: same) is the order in which
+        ``state_dict()`` lists the tensors — the HF key order, whatever the layout."""
         self.shapes = OrderedDict((k, tuple(v)) for k, v in shapes.items())
+        self.key_order = list(key_order) if key_order is not None else list(self.shapes)
+        assert sorted(self.key_order) == sorted(self.shapes)
         self.layout, self.numel = param_layout(self.shapes)
         if buffer is None:
             buffer = torch.zeros(self.numel, dtype=dtype, device=device)
@@ -41,7 +45,7 @@ class FlatArena:
             (k, self.flat[o:o + n].view(self.shapes[k])) for k, (o, n) in self.layout.items())
 
     def like(self, dtype=None, device=None) -> "FlatArena":
-        return FlatArena(self.shapes, dtype or self.flat.dtype, device or self.flat.device)
+        return FlatArena(self.shapes, dtype or self.flat.dtype, device or self.flat.device, key_order=self.key_order)
 
     def payload_numel(self) -> int:
         return sum(n for _, n in self.layout.values())
@@ -51,7 +55,7 @@ class FlatArena:
             v.copy_(state[k].to(v.dtype))
 
     def state_dict(self) -> "OrderedDict[str, torch.Tensor]":
-        return OrderedDict(self.views)
+        return OrderedDict((k, self.views[k]) for k in self.key_order)
 
     @staticmethod
     def adopt(module: torch.nn.Module, device=None) -> "FlatArena":

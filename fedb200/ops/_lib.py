@@ -43,7 +43,7 @@ _PROTOS = {
     "fedb200_peer_open": (i32, [vp, vp]),
     "fedb200_peer_close": (i32, [vp]),
     "fedb200_peer_free": (i32, [vp]),
-    "fedb200_fedavg_reduce": (i32, [vp, vp, vp, vp, i32, i32, sz, f32, u32, i32, vp]),
+    "fedb200_fedavg_reduce": (i32, [vp, vp, vp, vp, i32, i32, sz, f32, f32, u32, i32, vp]),
     "fedb200_peer_barrier": (i32, [vp, i32, i32, u32, i32, vp]),
 }
 

@@ -1,0 +1,45 @@
+"""Host replica of the library-wide counter RNG used for dropout (``csrc/common.cuh``).
+
+One 64-bit murmur-style hash of ``(seed, row, col // 4)`` yields four 16-bit lanes; element
+``(row, col)`` is kept iff lane ``col % 4`` is below ``round((1 - p) * 65536)``.  Tests use this to
+build the exact mask a kernel applied, so dropout paths are checked against an fp32 reference instead
+of only statistically."""
+from __future__ import annotations
+
+import numpy as np
+
+_M1 = np.uint64(0xFF51AFD7ED558CCD)
+_M2 = np.uint64(0xC4CEB9FE1A85EC53)
+
+
+def mix_hash64(x: np.ndarray) -> np.ndarray:
+    x = x.astype(np.uint64)
+    with np.errstate(over="ignore"):
+        x ^= x >> np.uint64(33)
+        x *= _M1
+        x ^= x >> np.uint64(33)
+        x *= _M2
+        x ^= x >> np.uint64(33)
+    return x
+
+
+def thresh16(p: float) -> int:
+    keep = np.float32(1.0) - np.float32(p)
+    return 65536 if keep >= 1.0 else int(np.float32(keep * np.float32(65536.0) + np.float32(0.5)))
+
+
+def dropout_keep(seed: int, rows: np.ndarray, cols: np.ndarray, p: float) -> np.ndarray:
+    """Boolean keep-mask for the broadcast of ``rows`` x ``cols`` (uint32 indices)."""
+    r = np.asarray(rows, dtype=np.uint64)
+    c = np.asarray(cols, dtype=np.uint64)
+    word = mix_hash64(np.uint64(seed) ^ ((r << np.uint64(32)) | (c >> np.uint64(2))))
+    lane = (word >> (np.uint64(16) * (c & np.uint64(3)))) & np.uint64(0xFFFF)
+    return lane < np.uint64(thresh16(p))
+
+
+def dropout_scale(seed: int, n_rows: int, n_cols: int, p: float, row0: int = 0, col0: int = 0) -> np.ndarray:
+    """``[n_rows, n_cols]`` float32 multiplier matrix (0 or 1/(1-p))."""
+    rows = (np.arange(n_rows, dtype=np.uint64) + np.uint64(row0))[:, None]
+    cols = (np.arange(n_cols, dtype=np.uint64) + np.uint64(col0))[None, :]
+    keep = dropout_keep(seed, rows, cols, p)
+    return keep.astype(np.float32) / np.float32(1.0 - p)

@@ -62,8 +62,9 @@ class Comm:
         return [float(v) for v in values]
 
     # -- collectives over flat arenas -----------------------------------------------------------
-    def weighted_mean(self, acc: torch.Tensor, weight: float, out: torch.Tensor) -> None:
-        """``out = sum_r acc_r / sum_r weight_r`` on every rank (``acc_r`` = local sum n_k w_k)."""
+    def weighted_mean(self, acc: torch.Tensor, weight: float, out: torch.Tensor, shadow=None) -> None:
+        """``out = sum_r acc_r / sum_r weight_r`` on every rank (``acc_r`` = local sum n_k w_k);
+        ``shadow`` optionally receives the bf16 copy in the same pass."""
         raise NotImplementedError
 
     def mix_rows(self, slots: torch.Tensor, w_rows: np.ndarray, out: torch.Tensor, num_peers: int) -> None:
@@ -84,13 +85,15 @@ class LoopbackComm(Comm):
     buffers live on a GPU, plain torch on the CPU."""
     name = "loopback"
 
-    def weighted_mean(self, acc, weight, out):
+    def weighted_mean(self, acc, weight, out, shadow=None):
         if acc.is_cuda:
             from ..ops import cuda_ops
-            cuda_ops.mix_n([acc], [1.0 / float(weight)], out)
+            cuda_ops.mix_n([acc], [1.0 / float(weight)], out, shadow)
             self.launches += 1
         else:
             torch.mul(acc, 1.0 / float(weight), out=out)
+            if shadow is not None:
+                shadow.copy_(out)
 
     def mix_rows(self, slots, w_rows, out, num_peers):
         P = slots.shape[0]
@@ -137,13 +140,15 @@ class TorchDistComm(Comm):
         dist.all_reduce(t, op=dist.ReduceOp.SUM if op == "sum" else dist.ReduceOp.MAX)
         return t.tolist()
 
-    def weighted_mean(self, acc, weight, out):
+    def weighted_mean(self, acc, weight, out, shadow=None):
         w = torch.tensor([float(weight)], dtype=torch.float64, device=self.device)
         dist.all_reduce(w)
         if out.data_ptr() != acc.data_ptr():
             out.copy_(acc)
         dist.all_reduce(out)
         out.mul_(1.0 / float(w.item()))
+        if shadow is not None:
+            shadow.copy_(out)
 
     def mix_rows(self, slots, w_rows, out, num_peers):
         ppr = peers_per_rank(num_peers, self.world)

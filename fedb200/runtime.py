@@ -61,6 +61,7 @@ class FedRuntime:
         self.global_flat.copy_(self.runner.flat)
         self.slots = self.comm.alloc("slots", self.P * self.D).view(self.P, self.D)
         self.acc = self.comm.alloc("acc", self.D)
+        self.deltas = None
         self.timer = PhaseTimer(self.device.type == "cuda")
         self.topo = Topology.from_name(cfg.topology, self.N, cfg.seed)
         self.injector = AnomalyInjector(self.N, cfg.inject_anomalies, cfg.inject_kind, seed=cfg.seed)
@@ -156,13 +157,27 @@ class FedRuntime:
             return list(self.static_masked)
         with self.timer.phase("score"):
             L = len(self.local_ids)
-            deltas = (self.slots[:L] - self.global_flat.unsqueeze(0)).to(
-                torch.bfloat16 if self.device.type == "cuda" else torch.float32)
-            if L < self.P:
-                pad = torch.zeros(self.P - L, self.D, dtype=deltas.dtype, device=deltas.device)
-                deltas = torch.cat([deltas, pad], 0)
-            g = self.comm.gram(deltas, self.N).to(torch.float64).cpu().numpy()[: self.N, : self.N]
-            bad, ranks, band = score_updates(g)
+            on_gpu = self.device.type == "cuda"
+            if self.deltas is None:
+                self.deltas = self.comm.alloc("deltas", self.P * self.D, torch.bfloat16 if on_gpu else torch.float32
+                                              ).view(self.P, self.D)
+            for li in range(L):
+                if on_gpu:
+                    from .ops import cuda_ops
+                    cuda_ops.delta_bf16(self.slots[li], self.global_flat, self.deltas[li])
+                    self.comm.launches += 1
+                else:
+                    torch.sub(self.slots[li], self.global_flat, out=self.deltas[li])
+            g = self.comm.gram(self.deltas, self.N)
+            if on_gpu and self.N <= 128:
+                from .ops import cuda_ops
+                ranks_d, mask_d, info_d = cuda_ops.pagerank(g[: self.N, : self.N].contiguous(), mode=1, low_only=True)
+                self.comm.launches += 1
+                ranks = ranks_d.cpu().numpy()
+                bad = [int(i) for i in np.flatnonzero(mask_d.cpu().numpy())]
+                band = (float(info_d[1]), float(info_d[2]))
+            else:
+                bad, ranks, band = score_updates(g.to(torch.float64).cpu().numpy()[: self.N, : self.N])
         self.log.log("score", round=rnd, masked=bad, ranks=[round(float(x), 6) for x in ranks], band=band)
         return bad
 
@@ -242,8 +257,12 @@ class FedRuntime:
         self.masked = self._score(rnd)
         with self.timer.phase("aggregate"):
             ws = [0.0 if i["peer"] in self.masked else 1.0 for i in infos]          # unweighted mean (:269)
-            self._local_weighted_sum(ws)
-            self.comm.weighted_mean(self.acc, sum(ws), self.global_flat)             # consensus / global model
+            if len(ws) == 1 and self.P == 1:
+                # one peer per GPU: its slot IS the rank's accumulator (a masked peer contributes weight 0)
+                self.comm.weighted_mean(self.slots[0], ws[0], self.global_flat)
+            else:
+                self._local_weighted_sum(ws)
+                self.comm.weighted_mean(self.acc, sum(ws), self.global_flat)         # consensus / global model
             if self.peer_state is not None:
                 w = apply_mask(mixing_matrix(self.topo.adjacency(), "metropolis"), self.masked)
                 rows = w[self.local_ids[0]: self.local_ids[0] + self.P] if self.local_ids else w[:0]

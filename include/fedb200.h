@@ -104,12 +104,14 @@ int fedb200_peer_alloc(size_t bytes, void** dev_ptr, void* ipc_handle_out64);
 int fedb200_peer_open(const void* ipc_handle64, void** mapped_ptr);
 int fedb200_peer_close(void* mapped_ptr);
 int fedb200_peer_free(void* dev_ptr);
-/* K1. Two-shot fused FedAvg: rank r reduces slice r of every rank's `acc` buffer, scales by 1/sum(weights)
- * and writes the result to every rank's `out` buffer (and optional bf16 shadow); barriers are flag words in peer
- * memory.  acc_ptrs / out_ptrs / flag_ptrs: HOST arrays of `world` peer-mapped device pointers (own rank included). */
+/* K1. Two-shot fused FedAvg: rank r reduces slice r of every rank's `acc` buffer (acc_r = sum of n_k * w_k over
+ * its clients), scales by 1 / sum over ranks of `my_weight` (exchanged through the flag words; pass
+ * inv_total_weight > 0 to override) and writes the result to every rank's `out` buffer (and optional bf16
+ * shadow); start/end barriers are flag words in peer memory.  acc_ptrs / out_ptrs / flag_ptrs: HOST arrays of
+ * `world` peer-mapped device pointers (own rank included); flag buffers need >= 64 zero-initialised words. */
 int fedb200_fedavg_reduce(const float* const* acc_ptrs, float* const* out_ptrs, void* const* shadow_ptrs,
-                          unsigned int* const* flag_ptrs, int rank, int world, size_t n, float inv_total_weight,
-                          unsigned int epoch, int timeout_ms, void* stream);
+                          unsigned int* const* flag_ptrs, int rank, int world, size_t n, float my_weight,
+                          float inv_total_weight, unsigned int epoch, int timeout_ms, void* stream);
 /* Device-side barrier across ranks (flag words in peer memory), usable between any two kernels. */
 int fedb200_peer_barrier(unsigned int* const* flag_ptrs, int rank, int world, unsigned int epoch, int timeout_ms,
                          void* stream);

@@ -1,0 +1,167 @@
+"""Fused attention and the fused BERT trainer vs fp32 PyTorch references (GPU)."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _ops():
+    from fedb200.ops import cuda_ops
+    return cuda_ops
+
+
+def _ref_attention(qkv, cu, heads, scale, drop=None):
+    """fp32 reference over packed sequences; ``drop``: optional per-(head, q_tok) x kv multiplier fn."""
+    T, H3 = qkv.shape
+    H = H3 // 3
+    out = torch.zeros(T, H, dtype=qkv.dtype, device=qkv.device)
+    for b in range(len(cu) - 1):
+        s, e = int(cu[b]), int(cu[b + 1])
+        for h in range(heads):
+            q = qkv[s:e, h * 64:(h + 1) * 64]
+            k = qkv[s:e, H + h * 64:H + (h + 1) * 64]
+            v = qkv[s:e, 2 * H + h * 64:2 * H + (h + 1) * 64]
+            p = torch.softmax(q @ k.T * scale, dim=-1)
+            if drop is not None:
+                p = p * drop(h, s, e)
+            out[s:e, h * 64:(h + 1) * 64] = p @ v
+    return out
+
+
+@pytest.mark.parametrize("lens,heads", [([5, 128, 77], 2), ([300, 129, 1, 512, 256], 3), ([512] * 4, 12)])
+def test_attention_fwd_bwd_no_dropout(cuda_lib, lens, heads):
+    ops = _ops()
+    torch.manual_seed(0)
+    H, T, B = heads * 64, sum(lens), len(lens)
+    cu = torch.tensor([0] + list(np.cumsum(lens)), dtype=torch.int32, device="cuda")
+    qkv = (torch.randn(T, 3 * H, device="cuda") * 0.8).bfloat16()
+    ctx = torch.zeros(T, H, dtype=torch.bfloat16, device="cuda")
+    lse = torch.zeros(heads * T, device="cuda")
+    scale = 1.0 / 8.0
+    ops.attn_fwd(qkv, ctx, lse, cu, B, heads, max(lens), scale)
+    qr = qkv.float().requires_grad_(True)
+    ref = _ref_attention(qr, cu.tolist(), heads, scale)
+    torch.cuda.synchronize()
+    err = (ctx.float() - ref).abs().max().item()
+    assert err < 3e-2, f"attention forward max err {err}"
+    dctx = (torch.randn(T, H, device="cuda") * 0.5).bfloat16()
+    ref.backward(dctx.float())
+    dqkv = torch.zeros(T, 3 * H, dtype=torch.bfloat16, device="cuda")
+    dq_acc = torch.zeros(T, H, device="cuda")
+    delta = torch.zeros(heads * T, device="cuda")
+    ops.attn_bwd(qkv, ctx, dctx, lse, delta, dqkv, dq_acc, cu, B, heads, max(lens), scale)
+    torch.cuda.synchronize()
+    g = qr.grad
+    for name, sl in (("dQ", slice(0, H)), ("dK", slice(H, 2 * H)), ("dV", slice(2 * H, 3 * H))):
+        e = (dqkv[:, sl].float() - g[:, sl]).abs().max().item()
+        scale_ref = g[:, sl].abs().max().item()
+        assert e < 3e-2 * max(scale_ref, 1.0) + 2e-2, f"{name} max err {e} (ref max {scale_ref})"
+    assert torch.count_nonzero(dq_acc) == 0, "dq_accum scratch must be left zeroed"
+
+
+def test_attention_dropout_exact_mask(cuda_lib):
+    from fedb200.ops.rng import dropout_scale
+    ops = _ops()
+    torch.manual_seed(1)
+    lens, heads, p, seed = [200, 70, 333], 2, 0.1, 4242
+    H, T, B = heads * 64, sum(lens), len(lens)
+    cu = torch.tensor([0] + list(np.cumsum(lens)), dtype=torch.int32, device="cuda")
+    qkv = (torch.randn(T, 3 * H, device="cuda") * 0.8).bfloat16()
+    ctx = torch.zeros(T, H, dtype=torch.bfloat16, device="cuda")
+    lse = torch.zeros(heads * T, device="cuda")
+    ops.attn_fwd(qkv, ctx, lse, cu, B, heads, max(lens), 0.125, seed, p)
+
+    def drop(h, s, e):      # rows = h*T + q token, cols = kv position within the sequence
+        m = dropout_scale(seed, e - s, e - s, p, row0=h * T + s, col0=0)
+        return torch.from_numpy(m).cuda()
+
+    qr = qkv.float().requires_grad_(True)
+    ref = _ref_attention(qr, cu.tolist(), heads, 0.125, drop)
+    torch.cuda.synchronize()
+    assert (ctx.float() - ref).abs().max().item() < 3e-2
+    dctx = (torch.randn(T, H, device="cuda") * 0.5).bfloat16()
+    ref.backward(dctx.float())
+    dqkv = torch.zeros(T, 3 * H, dtype=torch.bfloat16, device="cuda")
+    ops.attn_bwd(qkv, ctx, dctx, lse, torch.zeros(heads * T, device="cuda"), dqkv, torch.zeros(T, H, device="cuda"), cu, B,
+                 heads, max(lens), 0.125, seed, p)
+    torch.cuda.synchronize()
+    e = (dqkv.float() - qr.grad).abs().max().item()
+    assert e < 3e-2 * max(qr.grad.abs().max().item(), 1.0) + 2e-2, f"dropout backward max err {e}"
+
+
+def _mini_cfg(dropout=0.0, labels=3, name="bert-mini"):
+    from fedb200.config import FedConfig, ModelConfig
+    fed = FedConfig()
+    fed.model = ModelConfig.preset(name, num_labels=labels, hidden_dropout=dropout, attention_dropout=dropout)
+    fed.data.batch_size, fed.data.max_seq_len = 8, 300
+    return fed
+
+
+def _batch(vocab, lens, labels_n, seed=0):
+    from fedb200.data.dataset import TokenDataset, collate_packed, collate_padded
+    rng = np.random.default_rng(seed)
+    seqs = [rng.integers(5, vocab, size=n) for n in lens]
+    ds = TokenDataset.from_sequences(seqs, rng.integers(0, labels_n, size=len(lens)), labels_n)
+    idx = np.arange(len(lens))
+    return collate_packed(ds, idx), collate_padded(ds, idx)
+
+
+def test_fused_bert_matches_torch_forward_and_grads(cuda_lib):
+    from fedb200.models.fused_bert import FusedRunner
+    from fedb200.models.factory import build_model
+    fed = _mini_cfg(0.0)
+    run = FusedRunner(fed.model, fed, "cuda", seed=3)
+    ref = build_model(fed.model, "cuda", seed=3)
+    for k, v in ref.state_dict().items():
+        torch.testing.assert_close(run.state_dict()[k], v)
+    packed, padded = _batch(fed.model.vocab_size, [17, 130, 64, 257, 5, 300], 3)
+    ref.train()
+    out = ref(**{k: v.cuda() for k, v in padded.items()})
+    out.loss.backward()
+    loss = run.train_step(packed, optimizer_step=False)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(run.logits[:6], out.logits, rtol=5e-2, atol=3e-2)
+    assert abs(loss.item() - out.loss.item()) < 3e-2
+    worst = 0.0
+    gmax = max(p.grad.norm().item() for p in ref.parameters())
+    for k, p in ref.named_parameters():
+        g, gr = run.grads.views[k], p.grad
+        # key.bias has an identically-zero gradient (softmax is shift invariant): compare on an absolute floor
+        rel = (g - gr).norm().item() / max(gr.norm().item(), 1e-3 * gmax)
+        worst = max(worst, rel)
+        assert rel < 0.08, f"grad {k}: relative error {rel:.3f} (|ref| {gr.norm().item():.3e})"
+    print("worst relative grad error", worst)
+
+
+def test_fused_bert_training_reduces_loss(cuda_lib):
+    from fedb200.models.fused_bert import FusedRunner
+    fed = _mini_cfg(0.1)
+    fed.lr = 1e-3
+    run = FusedRunner(fed.model, fed, "cuda", seed=0)
+    run.opt.lr = 1e-3
+    packed, _ = _batch(fed.model.vocab_size, [40, 90, 130, 20, 64, 200, 33, 77], 3, seed=5)
+    losses = [run.train_step(packed).item() for _ in range(30)]
+    assert losses[-1] < 0.5 * losses[0], losses[::5]
+    l, c = run.eval_step(packed)
+    assert c.item() >= 6
+
+
+def test_fused_runner_interface_and_state_dict(cuda_lib, tmp_path):
+    from fedb200.data import BatchLoader, make_synthetic
+    from fedb200.models.fused_bert import FusedRunner
+    from fedb200.models.hf_io import load_state, save_pretrained
+    fed = _mini_cfg(0.1, labels=2)
+    run = FusedRunner(fed.model, fed, "cuda", seed=1)
+    ds = make_synthetic("imdb", "train", fed.model.vocab_size, 300, rows=64)
+    stats = run.train_epochs(BatchLoader(ds, 8, shuffle=True), 1)
+    assert stats["steps"] == 8 and math.isfinite(stats["loss"])
+    loss, acc = run.evaluate(BatchLoader(ds, 8))
+    assert 0.0 <= acc <= 1.0 and math.isfinite(loss)
+    save_pretrained(run.state_dict(), fed.model, str(tmp_path / "ck"))
+    sd = load_state(str(tmp_path / "ck"))
+    assert list(sd.keys()) == sorted(run.state_dict().keys()) or set(sd.keys()) == set(run.state_dict().keys())
+    for k, v in run.state_dict().items():
+        torch.testing.assert_close(sd[k], v.cpu())
