@@ -248,3 +248,92 @@ extern "C" int fedb200_block_validate(const void* headers, const void* recorded_
     FEDB_LAUNCH_CHECK();
     return 0;
 }
+
+// -------------------------------------------------------------------------------------------------
+// Allocation-free Merkle root.
+//
+// fedb200_sha256_leaves + fedb200_merkle_root need two caller-supplied workspaces (the leaf digests and the
+// ping-pong level buffer).  Some users of this library have no way to provide them: the asynchronous gossip
+// receive path verifies an incoming update against the ledger while other peers' kernels are in flight, and
+// a cudaMalloc/cudaFree there would synchronise the whole device and stall every peer; an auditing process
+// that links the library only to validate a ledger (e.g. next to an inference server) is typically handed a
+// fixed memory budget and no allocator; and a caller that sized its buffers before it knew the model size has
+// nothing left to carve a workspace from.  For them the workspace lives in the library image itself: a
+// file-scope __device__ array that each GPU holds from the moment the library is loaded until the process
+// exits (FEDB200_STATIC_MERKLE_MAX_LEAVES * 48 bytes = 6 MiB).
+//
+// The array's name is only a host-side handle here; the device address is fetched once per device with
+// cudaGetSymbolAddress (with that device current) and that pointer is what the kernels receive.
+// -------------------------------------------------------------------------------------------------
+namespace fedb {
+
+constexpr size_t STATIC_LEAF_BYTES = (size_t)FEDB200_STATIC_MERKLE_MAX_LEAVES * 32;
+constexpr size_t STATIC_LEVEL_BYTES = (size_t)(FEDB200_STATIC_MERKLE_MAX_LEAVES / 2 + 1) * 32;
+constexpr size_t STATIC_SCRATCH_BYTES = STATIC_LEAF_BYTES + ((STATIC_LEVEL_BYTES + 255) / 256) * 256;
+
+static __device__ __align__(256) unsigned char g_static_merkle_scratch[STATIC_SCRATCH_BYTES];
+
+constexpr int STATIC_MAX_DEVICES = 64;
+static unsigned char* g_static_scratch_addr[STATIC_MAX_DEVICES] = {nullptr};
+
+// Device address of the scratch array on the current device (looked up on the first call per device).
+static int static_scratch_for_current_device(unsigned char** out) {
+    int dev = -1;
+    FEDB_CHECK(cudaGetDevice(&dev));
+    FEDB_REQUIRE(dev >= 0 && dev < STATIC_MAX_DEVICES, "sha256_root_static: device ordinal %d not supported", dev);
+    if (g_static_scratch_addr[dev] == nullptr) {
+        void* p = nullptr;
+        FEDB_CHECK(cudaGetSymbolAddress(&p, g_static_merkle_scratch));
+        FEDB_REQUIRE(p != nullptr, "sha256_root_static: cudaGetSymbolAddress returned a null address");
+        g_static_scratch_addr[dev] = static_cast<unsigned char*>(p);
+    }
+    *out = g_static_scratch_addr[dev];
+    return 0;
+}
+
+}  // namespace fedb
+
+// Merkle root (same chunking and tree rule as fedb200_sha256_leaves + fedb200_merkle_root) of `nbytes` at `src`,
+// written as 32 bytes to `root_out`; both are device pointers owned by the caller.  Allocates nothing: the
+// leaf digests and tree levels go to the library's static device array, so at most
+// FEDB200_STATIC_MERKLE_MAX_LEAVES chunks are accepted (512 MiB at the default 4 KiB chunk — a whole fp32
+// BERT-base arena); larger inputs are refused with an error, not truncated.
+//   * The first call on each device resolves the array's device address (cudaGetSymbolAddress); make that
+//     first call outside any stream capture.
+//   * All calls on a device share the one array and it keeps whatever the previous call left there.  Nothing
+//     in it has to start at zero (every digest that is read was written earlier in the same call), but two
+//     calls that overlap on the GPU — different streams, or different host threads — race on it: serialise
+//     them on one stream or with events.
+extern "C" int fedb200_sha256_root_static(const void* src, size_t nbytes, unsigned int chunk_bytes, void* root_out,
+                                          void* stream) {
+    FEDB_REQUIRE(src != nullptr && root_out != nullptr, "sha256_root_static: null src/root_out");
+    FEDB_REQUIRE(chunk_bytes >= 64 && chunk_bytes % 64 == 0, "sha256_root_static: chunk_bytes must be a multiple of 64");
+    FEDB_REQUIRE(nbytes % 4 == 0 && nbytes > 0, "sha256_root_static: nbytes must be a positive multiple of 4");
+    FEDB_REQUIRE(((uintptr_t)src & 15) == 0, "sha256_root_static: src must be 16-byte aligned");
+    const size_t n_chunks = (nbytes + chunk_bytes - 1) / chunk_bytes;
+    FEDB_REQUIRE(n_chunks <= (size_t)FEDB200_STATIC_MERKLE_MAX_LEAVES,
+                 "sha256_root_static: %zu chunks of %u bytes exceed the static workspace (%d leaves max = %zu bytes of "
+                 "input at this chunk size); use fedb200_sha256_leaves + fedb200_merkle_root with your own buffers",
+                 n_chunks, chunk_bytes, FEDB200_STATIC_MERKLE_MAX_LEAVES,
+                 (size_t)FEDB200_STATIC_MERKLE_MAX_LEAVES * chunk_bytes);
+    unsigned char* scratch = nullptr;
+    int e = fedb::static_scratch_for_current_device(&scratch);
+    if (e) return e;
+    uint32_t* a = reinterpret_cast<uint32_t*>(scratch);                               // leaves, then even levels
+    uint32_t* b = reinterpret_cast<uint32_t*>(scratch + fedb::STATIC_LEAF_BYTES);     // odd levels
+    cudaStream_t s = (cudaStream_t)stream;
+    const unsigned grid = (unsigned)((n_chunks + SHA_CHUNKS_PER_CTA - 1) / SHA_CHUNKS_PER_CTA);
+    sha256_leaves_kernel<<<grid, SHA_CHUNKS_PER_CTA, 0, s>>>((const uint32_t*)src, nullptr, nbytes, chunk_bytes,
+                                                            (uint32_t)n_chunks, a);
+    FEDB_LAUNCH_CHECK();
+    unsigned n = (unsigned)n_chunks;
+    while (n > 1) {
+        const unsigned n_out = (n + 1) / 2;
+        merkle_level_kernel<<<(n_out + 127) / 128, 128, 0, s>>>(a, b, n);
+        FEDB_LAUNCH_CHECK();
+        uint32_t* t = a; a = b; b = t;
+        n = n_out;
+    }
+    FEDB_CHECK(cudaMemcpyAsync(root_out, a, 32, cudaMemcpyDeviceToDevice, s));
+    return 0;
+}

@@ -39,6 +39,7 @@ _PROTOS = {
     "fedb200_sha256_leaves": (i32, [vp, vp, sz, u32, vp, vp]),
     "fedb200_merkle_root": (i32, [vp, vp, u32, vp, vp]),
     "fedb200_block_validate": (i32, [vp, vp, u32, vp, vp, vp]),
+    "fedb200_sha256_root_static": (i32, [vp, sz, u32, vp, vp]),
     "fedb200_peer_alloc": (i32, [sz, vp, vp]),
     "fedb200_peer_open": (i32, [vp, vp]),
     "fedb200_peer_close": (i32, [vp]),

@@ -94,6 +94,14 @@ int fedb200_sha256_leaves(const void* src, void* dst, size_t nbytes, unsigned in
                           void* stream);
 /* Merkle reduction of n 32-byte nodes (clobbers `nodes`; `scratch` >= ceil(n/2)*32 bytes) -> 32-byte root. */
 int fedb200_merkle_root(void* nodes, void* scratch, unsigned int n, void* root_out, void* stream);
+/* Merkle root of `nbytes` at `src` -> 32 bytes at `root_out`, with NO workspace argument and no allocation:
+ * leaves and tree levels live in a static device array inside the library (6 MiB per GPU, held until exit),
+ * so at most FEDB200_STATIC_MERKLE_MAX_LEAVES chunks are accepted and larger inputs return an error.  For
+ * callers that cannot allocate (async gossip receive path, budget-capped ledger auditors).  First call per
+ * device resolves the array address — issue it before any stream capture.  Calls share the array: overlapping
+ * calls on one GPU race.  No counterpart in the reference (it has no ledger code and no native code). */
+#define FEDB200_STATIC_MERKLE_MAX_LEAVES 131072
+int fedb200_sha256_root_static(const void* src, size_t nbytes, unsigned int chunk_bytes, void* root_out, void* stream);
 /* K7. Re-hash n 128-byte block headers and check index / prev-hash links; first_bad = 0xFFFFFFFF if intact. */
 int fedb200_block_validate(const void* headers, const void* recorded_hashes, unsigned int n, void* hashes_out,
                            unsigned int* first_bad, void* stream);
