@@ -2,7 +2,7 @@
 // Same algorithm as nx.pagerank (alpha 0.85, L1 tolerance N*tol, <= max_iter sweeps, out-weight row
 // normalisation, uniform teleport and dangling redistribution) followed by the reference's thresholding
 // (All_graphs_IMDB_dataset.ipynb:168-176).  mode 0: `mat` is the edge-weight matrix w[u][v];
-// mode 1: `mat` is a Gram matrix of client updates -> cosine -> max(.,0) with no self loops (the on-line
+// mode 1: `mat` is a Gram matrix of client updates -> (1 + cos)/2 * norm ratio, no self loops (the on-line
 // scorer).  N <= 128 nodes: one CTA, the matrix lives in shared memory, arithmetic in fp64 so the result
 // matches the CPU oracle to ~1e-12.  Latency-bound by construction.
 #include "common.cuh"
@@ -28,9 +28,10 @@ __global__ void __launch_bounds__(PR_MAX_N) pagerank_kernel(const float* __restr
         for (int v = 0; v < n; ++v) {
             double w = (double)mat[u * n + v];
             if (mode == 1) {
-                const double nu = (double)mat[u * n + u], nv = (double)mat[v * n + v];
-                const double den = sqrt(fmax(nu, 1e-30)) * sqrt(fmax(nv, 1e-30));
-                w = (u == v) ? 0.0 : fmax(w / den, 0.0);
+                // w = (1 + cos) / 2 * (smaller norm / larger norm), no self loops (fedb200/anomaly/cosine.py)
+                const double nu = fmax((double)mat[u * n + u], 1e-30), nv = fmax((double)mat[v * n + v], 1e-30);
+                const double cs = fmin(fmax(w / sqrt(nu * nv), -1.0), 1.0);
+                w = (u == v) ? 0.0 : 0.5 * (1.0 + cs) * sqrt(fmin(nu, nv) / fmax(nu, nv));
             }
             P[u * n + v] = w;
             out += w;
