@@ -185,10 +185,11 @@ class FedRuntime:
         if self.ledger is None:
             return
         with self.timer.phase("ledger"):
-            mine = [(i["peer"], i["root"].hex(), i["batches"]) for i in infos]
+            # every rank contributes (peer, root, n_k, route) of its own peers; all ranks append the same blocks
+            mine = [(i["peer"], i["root"].hex(), i["batches"], list(route_of(i["peer"])) if route_of else [])
+                    for i in infos]
             every = sorted(sum(self.comm.all_gather_object(mine), []))
-            for peer, root_hex, n in every:
-                route = route_of(peer) if route_of else []
+            for peer, root_hex, n, route in every:
                 self.ledger.append(rnd, peer, BROADCAST, bytes.fromhex(root_hex), self.nbytes, n, route,
                                    timestamp_ns=rnd * 1_000_000 + peer)
             if self.cfg.num_rounds <= 4 or rnd % 5 == 0:

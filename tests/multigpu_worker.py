@@ -1,0 +1,112 @@
+"""Worker run under torchrun (one process per GPU) by tests/test_multigpu.py: fused peer-memory collectives vs
+torch.distributed NCCL + torch ops."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from fedb200.parallel import init_distributed, make_comm
+
+
+def main():
+    rank, world, local = init_distributed(torch.device("cuda"))
+    dev = torch.device("cuda", local)
+    comm = make_comm("peer", dev, rank, world)
+    assert comm.name == "peer"
+    torch.manual_seed(100 + rank)
+
+    # ---- K1 fused FedAvg reduce: weighted mean with per-rank weights, odd length (scalar tail) ----------
+    n = 3_000_003
+    acc = comm.alloc("t_acc", n)
+    out = comm.alloc("t_out", n)
+    shadow = comm.alloc("t_shadow", n, torch.bfloat16)
+    w = float(rank + 1)
+    x = torch.randn(n, device=dev)
+    acc.copy_(x * w)                                        # acc_r = n_r * w_r
+    comm.weighted_mean(acc, w, out, shadow)
+    ref = (x * w).clone()
+    dist.all_reduce(ref)
+    ref /= sum(range(1, world + 1))
+    torch.cuda.synchronize()
+    comm.check_errors()
+    torch.testing.assert_close(out, ref, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(shadow.float(), ref.bfloat16().float(), rtol=0, atol=4e-2)
+    for it in range(3):                                      # repeated epochs reuse the flag words
+        acc.copy_(x * (it + 1))
+        comm.weighted_mean(acc, 1.0, out)
+        ref = (x * (it + 1)).clone()
+        dist.all_reduce(ref)
+        ref /= world
+        torch.testing.assert_close(out, ref, rtol=1e-5, atol=1e-6)
+
+    # ---- K4 all-gather-fused Gram over peer memory ---------------------------------------------------------
+    P, D = 3, 64 * 997 + 8
+    deltas = comm.alloc("t_deltas", P * D, torch.bfloat16).view(P, D)
+    deltas.copy_((torch.randn(P, D, device=dev) * 0.1).bfloat16())
+    g = comm.gram(deltas, world * P)
+    allrows = [torch.empty_like(deltas) for _ in range(world)]
+    dist.all_gather(allrows, deltas.contiguous())
+    full = torch.cat(allrows, 0).float()
+    gref = full @ full.T
+    torch.cuda.synchronize()
+    comm.check_errors()
+    err = (g - gref).abs().max().item()
+    assert err < 2e-3 * gref.abs().max().item() + 1e-3, f"gram err {err}"
+
+    # ---- K2 routed mixing: out[i] = sum_j W[i, j] slot_j over peer memory ----------------------------------------
+    N, Dm = world * 2, 500_000
+    slots = comm.alloc("t_slots", 2 * Dm).view(2, Dm)
+    outm = comm.alloc("t_mix", 2 * Dm).view(2, Dm)
+    slots.copy_(torch.randn(2, Dm, device=dev))
+    W = np.random.default_rng(0).random((N, N))
+    W[W < 0.3] = 0.0
+    W /= W.sum(1, keepdims=True)
+    comm.mix_rows(slots, W[rank * 2: rank * 2 + 2], outm, N)
+    alls = [torch.empty_like(slots) for _ in range(world)]
+    dist.all_gather(alls, slots.contiguous())
+    S = torch.cat(alls, 0)
+    refm = torch.tensor(W[rank * 2: rank * 2 + 2], dtype=torch.float32, device=dev) @ S
+    torch.cuda.synchronize()
+    comm.check_errors()
+    torch.testing.assert_close(outm, refm, rtol=1e-4, atol=1e-5)
+
+    # ---- whole serverless round through the runtime on the fused backend ------------------------------------------
+    from fedb200.config import FedConfig, ModelConfig
+    from fedb200.runtime import FedRuntime
+    cfg = FedConfig(mode="serverless", num_clients=world, num_rounds=2, device="cuda", backend="fused", comm="peer")
+    cfg.model = ModelConfig.preset("bert-mini", num_labels=2)
+    cfg.data.population, cfg.data.train_per_client, cfg.data.test_per_client = 800, 32, 32
+    cfg.data.max_seq_len, cfg.data.batch_size, cfg.ledger = 128, 16, True
+    cfg.anomaly_detector = "cosine_pagerank"
+    rt = FedRuntime(cfg, echo=False)
+    rt.comm.close()
+    rt.comm = comm                                            # reuse the already-bootstrapped backend
+    rt.global_flat = comm.alloc("r_global", rt.D); rt.global_flat.copy_(rt.runner.flat)
+    rt.slots = comm.alloc("r_slots", rt.P * rt.D).view(rt.P, rt.D)
+    rt.acc = comm.alloc("r_acc", rt.D)
+    res = rt.run()
+    torch.cuda.synchronize()
+    comm.check_errors()
+    mine = rt.slots[0].clone()
+    gathered = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(gathered, mine)
+    torch.testing.assert_close(rt.global_flat, torch.stack(gathered).mean(0), rtol=1e-5, atol=1e-6)
+    chk = torch.tensor([float(rt.global_flat.double().sum())], device=dev, dtype=torch.float64)
+    lo, hi = chk.clone(), chk.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    assert lo.item() == hi.item(), "ranks disagree on the global model"
+    assert rt.ledger.height == 2 * world and rt.ledger.validate() == -1
+    heads = [None] * world
+    dist.all_gather_object(heads, rt.ledger.head.hex())
+    assert len(set(heads)) == 1, "ledgers diverged across ranks"
+    if rank == 0:
+        print("MULTIGPU_OK", world, res["global_accuracies"])
+    comm.close()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
