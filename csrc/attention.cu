@@ -8,7 +8,7 @@
 //   warp 0 TMA   : Q tile once, then K_j / V_j tiles (2-deep ring)
 //   warp 1 MMA   : S = Q K_j^T  (M128 N128 K64, both K-major) -> TMEM;  O_j = P_j V_j (A = P from smem,
 //                  B = V tile read MN-major, so V is never transposed)
-//   warps 2-5    : one thread per q row: two passes over S in TMEM (row max, then exp2 / row sum / dropout),
+//   warps 2-5    : (two CTAs per SM) one thread per q row: two passes over S in TMEM (row max, then exp2 / row sum / dropout),
 //                  P written as bf16 into the 128B-swizzled K-major layout, running O kept in registers
 // backward, one CTA per (128-row kv tile, head, sequence), looping over q tiles:
 //   S^T = K Q_i^T and dP^T = V dO_i^T land in TMEM with the kv index on the lanes, so the thread that owns a kv
@@ -45,7 +45,7 @@ __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t tile_addr, int kstep, 
 // =================================================================================================
 // forward
 // =================================================================================================
-__global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv,
+__global__ void __launch_bounds__(AT_THREADS, 2) attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv,
                                                                  __nv_bfloat16* __restrict__ ctx, float* __restrict__ lse,
                                                                  const int* __restrict__ cu_seqlens, int T, int H,
                                                                  float scale_log2, uint64_t seed, uint32_t keep_thresh,
@@ -58,17 +58,17 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* sQ = smem;
-    uint8_t* sK = sQ + AT_TILE;              // 2 stages
-    uint8_t* sV = sK + 2 * AT_TILE;          // 2 stages
-    uint8_t* sP = sV + 2 * AT_TILE;          // 2 tiles (kv 0-63 | 64-127)
-    __shared__ __align__(8) uint64_t q_full, k_full[2], v_full[2], k_empty[2], v_empty[2], s_full, p_ready, o_full;
+    uint8_t* sK = sQ + AT_TILE;              // single stage: K_{j+1} streams in while the softmax of block j runs
+    uint8_t* sV = sK + AT_TILE;
+    uint8_t* sP = sV + AT_TILE;              // 2 tiles (kv 0-63 | 64-127)
+    __shared__ __align__(8) uint64_t q_full, k_full, v_full, k_empty, v_empty, s_full, p_ready, o_full;
     __shared__ uint32_t tmem_slot;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tm_qkv);
         mbar_init(&q_full, 1);
-        for (int s = 0; s < 2; ++s) { mbar_init(&k_full[s], 1); mbar_init(&v_full[s], 1); mbar_init(&k_empty[s], 1); mbar_init(&v_empty[s], 1); }
+        mbar_init(&k_full, 1); mbar_init(&v_full, 1); mbar_init(&k_empty, 1); mbar_init(&v_empty, 1);
         mbar_init(&s_full, 1); mbar_init(&p_ready, 128); mbar_init(&o_full, 1);
         mbar_fence_init();
     }
@@ -83,14 +83,13 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
             mbar_expect_tx(&q_full, AT_TILE);
             tma_load_2d(sQ, &tm_qkv, &q_full, h * 64, tok0 + q0);
             for (int j = 0; j < n_kv; ++j) {
-                const int s = j & 1;
-                const uint32_t ph = ((uint32_t)(j >> 1) & 1u) ^ 1u;
-                mbar_wait(&k_empty[s], ph);
-                mbar_expect_tx(&k_full[s], AT_TILE);
-                tma_load_2d(sK + s * AT_TILE, &tm_qkv, &k_full[s], H + h * 64, tok0 + j * 128);
-                mbar_wait(&v_empty[s], ph);
-                mbar_expect_tx(&v_full[s], AT_TILE);
-                tma_load_2d(sV + s * AT_TILE, &tm_qkv, &v_full[s], 2 * H + h * 64, tok0 + j * 128);
+                const uint32_t ph = ((uint32_t)j & 1u) ^ 1u;
+                mbar_wait(&k_empty, ph);
+                mbar_expect_tx(&k_full, AT_TILE);
+                tma_load_2d(sK, &tm_qkv, &k_full, H + h * 64, tok0 + j * 128);
+                mbar_wait(&v_empty, ph);
+                mbar_expect_tx(&v_full, AT_TILE);
+                tma_load_2d(sV, &tm_qkv, &v_full, 2 * H + h * 64, tok0 + j * 128);
             }
         }
     } else if (warp == 1) {
@@ -98,33 +97,30 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_fwd_kernel(const __grid_co
             constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
             constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
             const uint32_t aQ = smem_u32(sQ), aP = smem_u32(sP);
+            const uint32_t aK = smem_u32(sK), aV = smem_u32(sV);
             mbar_wait(&q_full, 0);
-            mbar_wait(&k_full[0], 0);
+            mbar_wait(&k_full, 0);
             tc_fence_after_sync();
 #pragma unroll
-            for (int k = 0; k < 4; ++k) umma_bf16(tmem_s, desc_kmajor(aQ, k), desc_kmajor(smem_u32(sK), k), idesc_s, k > 0);
+            for (int k = 0; k < 4; ++k) umma_bf16(tmem_s, desc_kmajor(aQ, k), desc_kmajor(aK, k), idesc_s, k > 0);
             umma_commit(&s_full);
-            umma_commit(&k_empty[0]);
+            umma_commit(&k_empty);
             for (int j = 0; j < n_kv; ++j) {
-                const int s = j & 1;
                 mbar_wait(&p_ready, (uint32_t)j & 1u);
-                mbar_wait(&v_full[s], (uint32_t)(j >> 1) & 1u);
+                mbar_wait(&v_full, (uint32_t)j & 1u);
                 tc_fence_after_sync();
-                const uint32_t aV = smem_u32(sV + s * AT_TILE);
 #pragma unroll
                 for (int k = 0; k < 8; ++k)
                     umma_bf16(tmem_o, desc_kmajor(aP + (k >> 2) * AT_TILE, k & 3), desc_mnmajor(aV, k, 8192), idesc_o, k > 0);
                 umma_commit(&o_full);
-                umma_commit(&v_empty[s]);
+                umma_commit(&v_empty);
                 if (j + 1 < n_kv) {
-                    const int s1 = (j + 1) & 1;
-                    mbar_wait(&k_full[s1], (uint32_t)((j + 1) >> 1) & 1u);
+                    mbar_wait(&k_full, (uint32_t)(j + 1) & 1u);
                     tc_fence_after_sync();
-                    const uint32_t aK = smem_u32(sK + s1 * AT_TILE);
 #pragma unroll
                     for (int k = 0; k < 4; ++k) umma_bf16(tmem_s, desc_kmajor(aQ, k), desc_kmajor(aK, k), idesc_s, k > 0);
                     umma_commit(&s_full);
-                    umma_commit(&k_empty[s1]);
+                    umma_commit(&k_empty);
                 }
             }
         }
@@ -241,18 +237,23 @@ __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __
 // dqkv[:, 0:H] = bf16(dq_accum); dq_accum = 0 (ready for the next call)
 __global__ void __launch_bounds__(256) attn_dq_finish_kernel(float* __restrict__ dq_accum, __nv_bfloat16* __restrict__ dqkv,
                                                              int T, int H) {
-    const size_t n4 = (size_t)T * H / 4, stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
-        const float4 v = reinterpret_cast<float4*>(dq_accum)[i];
-        reinterpret_cast<float4*>(dq_accum)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        const size_t e = i * 4, tok = e / H, col = e % H;
-        uint2 pk;
-        pk.x = pack_bf16x2(v.x, v.y); pk.y = pack_bf16x2(v.z, v.w);
-        *reinterpret_cast<uint2*>(dqkv + tok * 3 * (size_t)H + col) = pk;
+    const int h4 = H / 4;
+    for (int tok = blockIdx.x; tok < T; tok += gridDim.x) {
+        float4* src = reinterpret_cast<float4*>(dq_accum + (size_t)tok * H);
+        __nv_bfloat16* dst = dqkv + (size_t)tok * 3 * H;
+        for (int i = threadIdx.x; i < h4; i += blockDim.x) {
+            const float4 v = src[i];
+            src[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            uint2 pk;
+            pk.x = pack_bf16x2(v.x, v.y); pk.y = pack_bf16x2(v.z, v.w);
+            *reinterpret_cast<uint2*>(dst + i * 4) = pk;
+        }
     }
 }
 
-__global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv,
+constexpr int ATB_THREADS = 320;          // warp 0 TMA, warp 1 MMA, warps 2-9 compute (two per TMEM lane quadrant)
+
+__global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv,
                                                                  const __grid_constant__ CUtensorMap tm_do,
                                                                  const float* __restrict__ lse, const float* __restrict__ delta,
                                                                  __nv_bfloat16* __restrict__ dqkv, float* __restrict__ dq_accum,
@@ -282,7 +283,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_kernel(const __grid_co
         tma_prefetch_desc(&tm_do);
         mbar_init(&kv_full, 1);
         for (int s = 0; s < 2; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_empty[s], 1); }
-        mbar_init(&sdp_full, 1); mbar_init(&pds_ready, 128); mbar_init(&dq_full, 1); mbar_init(&dq_empty, 128);
+        mbar_init(&sdp_full, 1); mbar_init(&pds_ready, 256); mbar_init(&dq_full, 1); mbar_init(&dq_empty, 256);
         mbar_init(&dkv_full, 1);
         mbar_fence_init();
     }
@@ -342,28 +343,33 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_kernel(const __grid_co
             umma_commit(&dkv_full);
         }
     } else {
+        // Eight compute warps: warps w and w+4 share a TMEM lane quadrant (rows) and split the 128 columns of
+        // S^T / dP^T in halves, which are exactly the two 64-column smem tiles of Pd^T / dS^T.
         const int quad = warp & 3;
+        const int half = (warp - 2) >> 2;                     // 0: q columns 0-63, 1: q columns 64-127
         const int r = quad * 32 + lane;                       // kv row for S^T/dP^T/dK/dV, q row for dQ
-        const int t128 = (warp - 2) * 32 + lane;              // 0..127 linear id among the compute threads
+        const int t256 = (warp - 2) * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
         const int kv = kv0 + r;
         const bool kv_ok = kv < len;
+        const uint32_t drop_col = dropout_key(seed) ^ (((uint32_t)kv >> 1) * 0x85EBCA77U);
+        const uint32_t drop_lane = (uint32_t)kv & 1u;
+        const uint32_t drop_row0 = (uint32_t)(h * T + tok0);
+        uint8_t* tp = sP + half * AT_TILE;
+        uint8_t* td = sdS + half * AT_TILE;
         for (int i = 0; i < n_q; ++i) {
             const int qb = i * 128, sl = i & 1;
             {   // stage lse / delta of this q tile (double-buffered by i parity; published by the named barrier)
-                const int q = qb + t128;
-                s_lse[sl][t128] = q < len ? lse[(size_t)h * T + tok0 + q] : 0.f;
-                s_delta[sl][t128] = q < len ? delta[(size_t)h * T + tok0 + q] : 0.f;
+                const int q = qb + (t256 & 127);
+                if (t256 < 128) s_lse[sl][t256] = q < len ? lse[(size_t)h * T + tok0 + q] : 0.f;
+                else            s_delta[sl][t256 - 128] = q < len ? delta[(size_t)h * T + tok0 + q] : 0.f;
             }
-            asm volatile("bar.sync 1, 128;" ::: "memory");
+            asm volatile("bar.sync 1, 256;" ::: "memory");
             mbar_wait(&sdp_full, (uint32_t)i & 1u);
             tc_fence_after_sync();
-            if (i > 0) {
-                // the previous iteration's dV/dK/dQ MMAs read sP/sdS: they are complete once dq_full(i-1) fired,
-                // which this thread already waited on below before looping.
-            }
 #pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
+            for (int cc = 0; cc < 2; ++cc) {
+                const int c = half * 2 + cc;
                 uint32_t rs[32], rp[32];
                 tmem_ld_32x32(tm_st + lane_addr + c * 32, rs);
                 tmem_ld_32x32(tm_dpt + lane_addr + c * 32, rp);
@@ -376,32 +382,29 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_kernel(const __grid_co
                     const float p = ok ? exp2f(__uint_as_float(rs[jq]) * scale_log2 - s_lse[sl][ql]) : 0.f;
                     float mk = 1.f;
                     if (use_dropout)
-                        mk = dropout_scale(seed, (uint32_t)(h * T + tok0 + q), (uint32_t)kv, keep_thresh, inv_keep);
+                        mk = dropout_lane(hash32(drop_col ^ ((drop_row0 + (uint32_t)q) * 0x9E3779B1U)), drop_lane, keep_thresh, inv_keep);
                     pd[jq] = p * mk;
                     ds[jq] = p * (__uint_as_float(rp[jq]) * mk - s_delta[sl][ql]) * scale;
                 }
-                uint8_t* tp = sP + (c >> 1) * AT_TILE;
-                uint8_t* td = sdS + (c >> 1) * AT_TILE;
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {
-                    st_swizzled_chunk(tp, r, (c & 1) * 4 + g, pd + g * 8);
-                    st_swizzled_chunk(td, r, (c & 1) * 4 + g, ds + g * 8);
+                    st_swizzled_chunk(tp, r, cc * 4 + g, pd + g * 8);
+                    st_swizzled_chunk(td, r, cc * 4 + g, ds + g * 8);
                 }
             }
             fence_async_smem();
             tc_fence_before_sync();
             mbar_arrive(&pds_ready);
-            // dQ tile: lanes are q rows now
+            // dQ tile: lanes are q rows now; each half drains 32 of the 64 head-dim columns
             mbar_wait(&dq_full, (uint32_t)i & 1u);
             tc_fence_after_sync();
             const int q = qb + r;
-#pragma unroll
-            for (int c = 0; c < 2; ++c) {
+            {
                 uint32_t raw[32];
-                tmem_ld_32x32(tm_dq + lane_addr + c * 32, raw);
+                tmem_ld_32x32(tm_dq + lane_addr + half * 32, raw);
                 tmem_ld_wait();
                 if (q < len) {
-                    float* dst = dq_accum + (size_t)(tok0 + q) * H + h * 64 + c * 32;
+                    float* dst = dq_accum + (size_t)(tok0 + q) * H + h * 64 + half * 32;
 #pragma unroll
                     for (int g = 0; g < 8; ++g)
                         atomicAdd(reinterpret_cast<float4*>(dst + g * 4),
@@ -414,8 +417,8 @@ __global__ void __launch_bounds__(AT_THREADS, 1) attn_bwd_kernel(const __grid_co
         }
         mbar_wait(&dkv_full, 0);
         tc_fence_after_sync();
-#pragma unroll
-        for (int which = 0; which < 2; ++which) {            // 0: dK -> K block, 1: dV -> V block
+        {   // half 0 writes dK into the K block of dqkv, half 1 writes dV into the V block
+            const int which = half;
 #pragma unroll
             for (int c = 0; c < 2; ++c) {
                 uint32_t raw[32];
@@ -452,7 +455,7 @@ extern "C" int fedb200_attn_fwd(const void* qkv, void* ctx, float* lse, const in
     CUtensorMap tm;
     int e = make_tmap_bf16_2d(&tm, qkv, (uint64_t)T, (uint64_t)3 * H, (uint64_t)3 * H, 128, 64);
     if (e) return e;
-    const size_t smem = 7 * AT_TILE + 1024;
+    const size_t smem = 5 * AT_TILE + 1024;
     static bool configured = false;
     if (!configured) {
         FEDB_CHECK(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -486,12 +489,12 @@ extern "C" int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dc
         configured = true;
     }
     dim3 grid((max_seqlen + 127) / 128, heads, B);
-    attn_bwd_kernel<<<grid, AT_THREADS, smem, s>>>(tm, tmdo, lse, delta, (__nv_bfloat16*)dqkv, dq_accum, cu_seqlens, T, H,
+    attn_bwd_kernel<<<grid, ATB_THREADS, smem, s>>>(tm, tmdo, lse, delta, (__nv_bfloat16*)dqkv, dq_accum, cu_seqlens, T, H,
                                                    scale, scale * LOG2E, seed, dropout_thresh16(dropout_p),
                                                    1.0f / (1.0f - dropout_p), dropout_p > 0.f);
     FEDB_LAUNCH_CHECK();
-    int blocks = sm_count() * 8;
-    attn_dq_finish_kernel<<<blocks, 256, 0, s>>>(dq_accum, (__nv_bfloat16*)dqkv, T, H);
+    const int fin_blocks = T < sm_count() * 16 ? T : sm_count() * 16;
+    attn_dq_finish_kernel<<<fin_blocks, H / 4 >= 256 ? 256 : 192, 0, s>>>(dq_accum, (__nv_bfloat16*)dqkv, T, H);
     FEDB_LAUNCH_CHECK();
     return 0;
 }

@@ -61,35 +61,40 @@ __device__ __forceinline__ float2 unpack_bf16x2(uint32_t v) {
     return __bfloat1622float2(t);
 }
 
-// Counter-based dropout.  One 64-bit murmur-style hash of (seed, row, col / 4) yields four 16-bit lanes, one
-// per column of the aligned 4-column group; element (row, col) is kept iff its lane < thresh16 where
-// thresh16 = round((1 - p) * 65536).  Forward and backward kernels regenerate the same mask from the seed, so
-// no mask tensor is ever stored.  Every kernel in the library uses this one convention.
-__device__ __forceinline__ uint64_t mix_hash64(uint64_t x) {
-    x ^= x >> 33; x *= 0xff51afd7ed558ccdULL;
-    x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL;
-    x ^= x >> 33;
+// Counter-based dropout.  One 32-bit hash of (seed, row, col / 2) yields two 16-bit lanes, one per column of
+// the aligned column pair; element (row, col) is kept iff its lane < thresh16 = round((1 - p) * 65536).
+// Forward and backward kernels regenerate the same mask from the seed, so no mask tensor is ever stored.  A
+// 32-bit mixer (two multiplies) keeps the cost at ~5 instructions per element even in kernels that walk a
+// column (attention backward), where only one lane of each word is used.  fedb200/ops/rng.py is the host replica.
+__device__ __forceinline__ uint32_t hash32(uint32_t x) {
+    x ^= x >> 16; x *= 0x7feb352dU;
+    x ^= x >> 15; x *= 0x846ca68bU;
+    x ^= x >> 16;
     return x;
 }
-__device__ __forceinline__ uint64_t dropout_word(uint64_t seed, uint32_t row, uint32_t col4) {
-    return mix_hash64(seed ^ (((uint64_t)row << 32) | (uint64_t)col4));
+__device__ __forceinline__ uint32_t dropout_key(uint64_t seed) {
+    return (uint32_t)seed ^ ((uint32_t)(seed >> 32) * 0xC2B2AE3DU);
 }
-__device__ __forceinline__ float dropout_lane(uint64_t word, int lane4, uint32_t thresh16, float inv_keep) {
-    return (uint32_t)((word >> (16 * lane4)) & 0xFFFFu) < thresh16 ? inv_keep : 0.0f;
+__device__ __forceinline__ uint32_t dropout_word(uint32_t key, uint32_t row, uint32_t col2) {
+    return hash32(key ^ (row * 0x9E3779B1U) ^ (col2 * 0x85EBCA77U));
+}
+__device__ __forceinline__ float dropout_lane(uint32_t word, uint32_t lane2, uint32_t thresh16, float inv_keep) {
+    return ((word >> (16u * lane2)) & 0xFFFFu) < thresh16 ? inv_keep : 0.0f;
 }
 // scalar form: multiplier (0 or 1/(1-p)) for element (row, col); p == 0 callers skip the call entirely
 __device__ __forceinline__ float dropout_scale(uint64_t seed, uint32_t row, uint32_t col, uint32_t thresh16,
                                                float inv_keep) {
-    return dropout_lane(dropout_word(seed, row, col >> 2), (int)(col & 3u), thresh16, inv_keep);
+    return dropout_lane(dropout_word(dropout_key(seed), row, col >> 1), col & 1u, thresh16, inv_keep);
 }
 // scales 8 consecutive values starting at column col0 (col0 % 8 == 0)
 __device__ __forceinline__ void dropout_apply8(float* v, uint64_t seed, uint32_t row, uint32_t col0,
                                                uint32_t thresh16, float inv_keep) {
-    const uint64_t w0 = dropout_word(seed, row, col0 >> 2), w1 = dropout_word(seed, row, (col0 >> 2) + 1);
+    const uint32_t key = dropout_key(seed);
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        v[k] *= dropout_lane(w0, k, thresh16, inv_keep);
-        v[4 + k] *= dropout_lane(w1, k, thresh16, inv_keep);
+        const uint32_t w = dropout_word(key, row, (col0 >> 1) + k);
+        v[2 * k] *= dropout_lane(w, 0u, thresh16, inv_keep);
+        v[2 * k + 1] *= dropout_lane(w, 1u, thresh16, inv_keep);
     }
 }
 __host__ __device__ inline uint32_t dropout_thresh16(float p) {

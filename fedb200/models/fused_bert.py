@@ -135,6 +135,51 @@ class FusedRunner:
         self.h2d_bytes = 0
         self.d2h_bytes = 0
         self.base_seed = (int(seed or 0) * 0x9E3779B1 + 0x1234567) & 0xFFFFFFFF
+        self.use_engine = True                  # native step executor (csrc/bert_engine.cu); False = Python twin
+        self._plan = self._build_plan()
+        self._sms = torch.cuda.get_device_properties(self.device).multi_processor_count
+
+    def _build_plan(self):
+        """Fill the C plan with raw device pointers (valid for the life of the runner: nothing is reallocated)."""
+        import ctypes as C
+        from ..ops._lib import BertPlan, MAX_LAYERS
+        c = self.cfg
+        if self.L > MAX_LAYERS:
+            raise ValueError(f"{self.L} layers exceed the native plan capacity ({MAX_LAYERS})")
+        P = BertPlan()
+        P.H, P.I, P.L, P.heads, P.C, P.type_vocab, P.act = self.H, self.I, self.L, self.heads, self.C, c.type_vocab_size, 0
+        P.ln_eps, P.p_hidden, P.p_attn = c.layer_norm_eps, c.hidden_dropout, c.attention_dropout
+        w, g = (lambda k: self.arena.views[k].data_ptr()), (lambda k: self.grads.views[k].data_ptr())
+        e = "bert.embeddings."
+        for f, k in (("word", e + "word_embeddings.weight"), ("pos", e + "position_embeddings.weight"),
+                     ("type", e + "token_type_embeddings.weight"), ("emb_lnw", e + "LayerNorm.weight"),
+                     ("emb_lnb", e + "LayerNorm.bias"), ("Wp", "bert.pooler.dense.weight"), ("bp", "bert.pooler.dense.bias"),
+                     ("Wc", "classifier.weight"), ("bc", "classifier.bias")):
+            setattr(P, f, w(k))
+            setattr(P, "g_" + f, g(k))
+        for f, t in (("emb_mean", self.emb_mean), ("emb_rstd", self.emb_rstd), ("ids", self.d_ids), ("pos_ids", self.d_pos),
+                     ("tt", self.d_tt), ("cu_seqlens", self.d_cu), ("labels", self.d_labels), ("pooled", self.pooled),
+                     ("pooled_drop", self.pooled_drop), ("dpre", self.dpre), ("logits", self.logits),
+                     ("dlogits", self.dlogits), ("loss", self.loss_vec), ("pred", self.pred), ("dx", self.dx),
+                     ("dzb", self.dzb), ("dfb", self.dfb), ("dctx", self.dctx), ("du", self.du), ("dqkv", self.dqkv),
+                     ("dq_accum", self.dq_accum), ("delta", self.delta)):
+            setattr(P, f, t.data_ptr())
+        for l in range(self.L):
+            k, a, Ly = self.lk[l], self.act[l], P.layer[l]
+            Ly.wqkv, Ly.bqkv = self.wqkv_bf[l].data_ptr(), self.bqkv[l].data_ptr()
+            Ly.g_wqkv, Ly.g_bqkv = self.gwqkv[l].data_ptr(), self.gbqkv[l].data_ptr()
+            for f, key in (("wo", "o.w"), ("w1", "f1.w"), ("w2", "f2.w")):
+                setattr(Ly, f, self.shadow.views[k[key]].data_ptr())
+                setattr(Ly, "g_" + f, g(k[key]))
+            for f, key in (("bo", "o.b"), ("b1", "f1.b"), ("b2", "f2.b"), ("ln1w", "ln1.w"), ("ln1b", "ln1.b"),
+                           ("ln2w", "ln2.w"), ("ln2b", "ln2.b")):
+                setattr(Ly, f, w(k[key]))
+                setattr(Ly, "g_" + f, g(k[key]))
+            Ly.x_in, Ly.x_out = self.xs[l].data_ptr(), self.xs[l + 1].data_ptr()
+            for f in ("qkv", "ctx", "z1", "a1", "u", "g", "z2", "mean1", "rstd1", "mean2", "rstd2", "lse"):
+                setattr(Ly, f, a[f].data_ptr())
+        self._plan_ref = C.byref(P)
+        return P
 
     # ---- parameters ----------------------------------------------------------------------------------------
     @property
@@ -213,6 +258,26 @@ class FusedRunner:
 
     # ---- forward ---------------------------------------------------------------------------------------------------
     def _forward(self, T: int, B: int, max_len: int, train: bool) -> None:
+        if not self.use_engine:
+            return self._forward_py(T, B, max_len, train)
+        from ..ops import _lib
+        _lib.call("fedb200_bert_forward", self._plan_ref, T, B, max_len, int(train), self._step_seed(), self._sms,
+                  torch.cuda.current_stream().cuda_stream)
+        _lib.count(3 + 7 * self.L)
+
+    def _backward(self, T: int, B: int, max_len: int) -> None:
+        if not self.use_engine:
+            return self._backward_py(T, B, max_len)
+        from ..ops import _lib
+        _lib.call("fedb200_bert_backward", self._plan_ref, T, B, max_len, self._step_seed(), self._sms,
+                  torch.cuda.current_stream().cuda_stream)
+        _lib.count(4 + 17 * self.L)
+
+    def _step_seed(self) -> int:
+        return (self.base_seed * 0x100000001B3 + self.step_count) & 0x7FFFFFFFFFFFFFFF
+
+    def _forward_py(self, T: int, B: int, max_len: int, train: bool) -> None:
+        """Python twin of csrc/bert_engine.cu::fedb200_bert_forward (kept for debugging / documentation)."""
         ops, H, I, c = self.ops, self.H, self.I, self.cfg
         ph = c.hidden_dropout if train else 0.0
         pa = c.attention_dropout if train else 0.0
@@ -244,7 +309,8 @@ class FusedRunner:
                      self._seed(98, 0), ph)
 
     # ---- backward --------------------------------------------------------------------------------------------------
-    def _backward(self, T: int, B: int, max_len: int) -> None:
+    def _backward_py(self, T: int, B: int, max_len: int) -> None:
+        """Python twin of csrc/bert_engine.cu::fedb200_bert_backward."""
         ops, H, I, c = self.ops, self.H, self.I, self.cfg
         ph, pa = c.hidden_dropout, c.attention_dropout
         cu = self.d_cu[:B + 1]

@@ -40,6 +40,8 @@ _PROTOS = {
     "fedb200_merkle_root": (i32, [vp, vp, u32, vp, vp]),
     "fedb200_block_validate": (i32, [vp, vp, u32, vp, vp, vp]),
     "fedb200_sha256_root_static": (i32, [vp, sz, u32, vp, vp]),
+    "fedb200_bert_forward": (i32, [vp, i32, i32, i32, i32, u64, i32, vp]),
+    "fedb200_bert_backward": (i32, [vp, i32, i32, i32, u64, i32, vp]),
     "fedb200_peer_alloc": (i32, [sz, vp, vp]),
     "fedb200_peer_open": (i32, [vp, vp]),
     "fedb200_peer_close": (i32, [vp]),
@@ -47,6 +49,30 @@ _PROTOS = {
     "fedb200_fedavg_reduce": (i32, [vp, vp, vp, vp, i32, i32, sz, f32, f32, u32, i32, vp]),
     "fedb200_peer_barrier": (i32, [vp, i32, i32, u32, i32, vp]),
 }
+
+
+class BertLayer(C.Structure):
+    """Mirror of ``fedb200_bert_layer`` (include/fedb200.h)."""
+    _fields_ = [(n, vp) for n in (
+        "wqkv", "wo", "w1", "w2", "bqkv", "bo", "b1", "b2", "ln1w", "ln1b", "ln2w", "ln2b",
+        "g_wqkv", "g_bqkv", "g_wo", "g_bo", "g_w1", "g_b1", "g_w2", "g_b2", "g_ln1w", "g_ln1b", "g_ln2w", "g_ln2b",
+        "x_in", "x_out", "qkv", "ctx", "z1", "a1", "u", "g", "z2", "mean1", "rstd1", "mean2", "rstd2", "lse")]
+
+
+MAX_LAYERS = 48
+
+
+class BertPlan(C.Structure):
+    """Mirror of ``fedb200_bert_plan`` (include/fedb200.h)."""
+    _fields_ = ([(n, i32) for n in ("H", "I", "L", "heads", "C", "type_vocab", "act")]
+                + [(n, f32) for n in ("ln_eps", "p_hidden", "p_attn")]
+                + [(n, vp) for n in (
+                    "word", "pos", "type", "emb_lnw", "emb_lnb", "Wp", "bp", "Wc", "bc",
+                    "g_word", "g_pos", "g_type", "g_emb_lnw", "g_emb_lnb", "g_Wp", "g_bp", "g_Wc", "g_bc",
+                    "emb_mean", "emb_rstd", "ids", "pos_ids", "tt", "cu_seqlens", "labels",
+                    "pooled", "pooled_drop", "dpre", "logits", "dlogits", "loss", "pred",
+                    "dx", "dzb", "dfb", "dctx", "du", "dqkv", "dq_accum", "delta")]
+                + [("layer", BertLayer * MAX_LAYERS)])
 
 
 class KernelError(RuntimeError):

@@ -1,26 +1,31 @@
 """Host replica of the library-wide counter RNG used for dropout (``csrc/common.cuh``).
 
-One 64-bit murmur-style hash of ``(seed, row, col // 4)`` yields four 16-bit lanes; element
-``(row, col)`` is kept iff lane ``col % 4`` is below ``round((1 - p) * 65536)``.  Tests use this to
-build the exact mask a kernel applied, so dropout paths are checked against an fp32 reference instead
-of only statistically."""
+One 32-bit hash of ``(seed, row, col // 2)`` yields two 16-bit lanes; element ``(row, col)`` is kept iff
+lane ``col % 2`` is below ``round((1 - p) * 65536)``.  Tests use this to build the exact mask a kernel
+applied, so dropout paths are checked against an fp32 reference instead of only statistically."""
 from __future__ import annotations
 
 import numpy as np
 
-_M1 = np.uint64(0xFF51AFD7ED558CCD)
-_M2 = np.uint64(0xC4CEB9FE1A85EC53)
+_U32 = np.uint64(0xFFFFFFFF)
 
 
-def mix_hash64(x: np.ndarray) -> np.ndarray:
-    x = x.astype(np.uint64)
-    with np.errstate(over="ignore"):
-        x ^= x >> np.uint64(33)
-        x *= _M1
-        x ^= x >> np.uint64(33)
-        x *= _M2
-        x ^= x >> np.uint64(33)
+def _mul32(a: np.ndarray, b: int) -> np.ndarray:
+    return (a.astype(np.uint64) * np.uint64(b)) & _U32
+
+
+def hash32(x: np.ndarray) -> np.ndarray:
+    x = x.astype(np.uint64) & _U32
+    x ^= x >> np.uint64(16)
+    x = _mul32(x, 0x7FEB352D)
+    x ^= x >> np.uint64(15)
+    x = _mul32(x, 0x846CA68B)
+    x ^= x >> np.uint64(16)
     return x
+
+
+def dropout_key(seed: int) -> int:
+    return (seed & 0xFFFFFFFF) ^ ((((seed >> 32) & 0xFFFFFFFF) * 0xC2B2AE3D) & 0xFFFFFFFF)
 
 
 def thresh16(p: float) -> int:
@@ -32,8 +37,8 @@ def dropout_keep(seed: int, rows: np.ndarray, cols: np.ndarray, p: float) -> np.
     """Boolean keep-mask for the broadcast of ``rows`` x ``cols`` (uint32 indices)."""
     r = np.asarray(rows, dtype=np.uint64)
     c = np.asarray(cols, dtype=np.uint64)
-    word = mix_hash64(np.uint64(seed) ^ ((r << np.uint64(32)) | (c >> np.uint64(2))))
-    lane = (word >> (np.uint64(16) * (c & np.uint64(3)))) & np.uint64(0xFFFF)
+    word = hash32(np.uint64(dropout_key(seed)) ^ _mul32(r, 0x9E3779B1) ^ _mul32(c >> np.uint64(1), 0x85EBCA77))
+    lane = (word >> (np.uint64(16) * (c & np.uint64(1)))) & np.uint64(0xFFFF)
     return lane < np.uint64(thresh16(p))
 
 

@@ -82,6 +82,47 @@ int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dctx, const f
                      float* dq_accum, const int* cu_seqlens, int B, int T, int heads, int max_seqlen, float scale,
                      unsigned long long seed, float dropout_p, void* stream);
 
+/* ---- native step executor ------------------------------------------------------------------------------------- */
+/* One call = the whole forward (or backward) launch sequence of the fused BERT trainer.  The plan holds raw
+ * device pointers into the caller's arenas / workspace (filled once by fedb200/models/fused_bert.py), so a
+ * training step costs one host call instead of ~270 Python-level launches.  Reference: the body of
+ * `train()` / `test()`, src/Servercase/server_IID_IMDB.py:108-135. */
+#define FEDB200_MAX_LAYERS 48
+typedef struct {
+    /* bf16 shadow weights, fp32 master biases / LN params, fp32 gradients */
+    const void *wqkv, *wo, *w1, *w2;
+    const float *bqkv, *bo, *b1, *b2, *ln1w, *ln1b, *ln2w, *ln2b;
+    float *g_wqkv, *g_bqkv, *g_wo, *g_bo, *g_w1, *g_b1, *g_w2, *g_b2, *g_ln1w, *g_ln1b, *g_ln2w, *g_ln2b;
+    /* saved activations */
+    void *x_in, *x_out, *qkv, *ctx, *z1, *a1, *u, *g, *z2;
+    float *mean1, *rstd1, *mean2, *rstd2, *lse;
+} fedb200_bert_layer;
+
+typedef struct {
+    int H, I, L, heads, C, type_vocab, act;
+    float ln_eps, p_hidden, p_attn;
+    /* embeddings + head (fp32 master) and their gradients */
+    const float *word, *pos, *type, *emb_lnw, *emb_lnb, *Wp, *bp, *Wc, *bc;
+    float *g_word, *g_pos, *g_type, *g_emb_lnw, *g_emb_lnb, *g_Wp, *g_bp, *g_Wc, *g_bc;
+    float *emb_mean, *emb_rstd;
+    /* inputs (packed tokens) */
+    const int *ids, *pos_ids, *tt, *cu_seqlens, *labels;
+    /* head buffers */
+    float *pooled, *pooled_drop, *dpre, *logits, *dlogits, *loss;
+    int* pred;
+    /* backward workspace */
+    void *dx, *dzb, *dfb, *dctx, *du, *dqkv;
+    float *dq_accum, *delta;
+    fedb200_bert_layer layer[FEDB200_MAX_LAYERS];
+} fedb200_bert_plan;
+
+/* `plan` is a HOST pointer.  T packed tokens in B sequences, longest max_len.  `train` enables dropout and saves
+ * what backward needs; `step_seed` must be the same for the forward and the backward of one step. */
+int fedb200_bert_forward(const fedb200_bert_plan* plan, int T, int B, int max_len, int train,
+                         unsigned long long step_seed, int sm_count, void* stream);
+int fedb200_bert_backward(const fedb200_bert_plan* plan, int T, int B, int max_len, unsigned long long step_seed,
+                          int sm_count, void* stream);
+
 /* ---- federated kernels --------------------------------------------------------------------------------------- */
 /* K4. Gram matrix of client updates over a column slice, tcgen05 + TMA straight from (peer) buffers. */
 int fedb200_gram_bf16(const void* const* rows_ptrs, int n_ranks, int rows_per_rank, size_t D, size_t ld,
