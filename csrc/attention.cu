@@ -234,20 +234,42 @@ __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __
     delta[(size_t)h * T + tok] = s;
 }
 
-// dqkv[:, 0:H] = bf16(dq_accum); dq_accum = 0 (ready for the next call)
-__global__ void __launch_bounds__(256) attn_dq_finish_kernel(float* __restrict__ dq_accum, __nv_bfloat16* __restrict__ dqkv,
-                                                             int T, int H) {
-    const int h4 = H / 4;
-    for (int tok = blockIdx.x; tok < T; tok += gridDim.x) {
-        float4* src = reinterpret_cast<float4*>(dq_accum + (size_t)tok * H);
-        __nv_bfloat16* dst = dqkv + (size_t)tok * 3 * H;
-        for (int i = threadIdx.x; i < h4; i += blockDim.x) {
-            const float4 v = src[i];
-            src[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-            uint2 pk;
-            pk.x = pack_bf16x2(v.x, v.y); pk.y = pack_bf16x2(v.z, v.w);
-            *reinterpret_cast<uint2*>(dst + i * 4) = pk;
+// Finishing pass over dqkv [T, 3H]: the Q third is converted from the fp32 atomics buffer (which is re-zeroed for
+// the next call), and — when `dbias` is given — the column sums of all three thirds (the q/k/v bias gradients)
+// are accumulated in the same sweep, so the backward needs no separate column-sum kernel for dqkv.
+// blockDim = (32, 8): a warp-row covers 64 contiguous columns; rows are strided over y and blockIdx.y.
+__global__ void __launch_bounds__(256) attn_bwd_finish_kernel(float* __restrict__ dq_accum, __nv_bfloat16* __restrict__ dqkv,
+                                                              float* __restrict__ dbias, int T, int H, int rows_per_block) {
+    __shared__ float2 red[8][32];
+    const int col = (blockIdx.x * 32 + threadIdx.x) * 2;          // column within [0, 3H)
+    const int r0 = blockIdx.y * rows_per_block, r1 = min(T, r0 + rows_per_block);
+    float2 acc = make_float2(0.f, 0.f);
+    if (col < 3 * H) {
+        if (col < H) {
+            for (int r = r0 + threadIdx.y; r < r1; r += 8) {
+                float2* src = reinterpret_cast<float2*>(dq_accum + (size_t)r * H + col);
+                const float2 v = *src;
+                *src = make_float2(0.f, 0.f);
+                const uint32_t pk = pack_bf16x2(v.x, v.y);
+                *reinterpret_cast<uint32_t*>(dqkv + (size_t)r * 3 * H + col) = pk;
+                const float2 f = unpack_bf16x2(pk);               // sum what the GEMMs will consume
+                acc.x += f.x; acc.y += f.y;
+            }
+        } else if (dbias != nullptr) {
+            for (int r = r0 + threadIdx.y; r < r1; r += 8) {
+                const float2 f = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(dqkv + (size_t)r * 3 * H + col));
+                acc.x += f.x; acc.y += f.y;
+            }
         }
+    }
+    if (dbias == nullptr) return;
+    red[threadIdx.y][threadIdx.x] = acc;
+    __syncthreads();
+    if (threadIdx.y == 0 && col < 3 * H) {
+#pragma unroll
+        for (int y = 1; y < 8; ++y) { acc.x += red[y][threadIdx.x].x; acc.y += red[y][threadIdx.x].y; }
+        atomicAdd(dbias + col, acc.x);
+        atomicAdd(dbias + col + 1, acc.y);
     }
 }
 
@@ -470,8 +492,9 @@ extern "C" int fedb200_attn_fwd(const void* qkv, void* ctx, float* lse, const in
 }
 
 extern "C" int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dctx, const float* lse, float* delta,
-                                void* dqkv, float* dq_accum, const int* cu_seqlens, int B, int T, int heads,
-                                int max_seqlen, float scale, unsigned long long seed, float dropout_p, void* stream) {
+                                void* dqkv, float* dq_accum, float* dbias_qkv, const int* cu_seqlens, int B, int T,
+                                int heads, int max_seqlen, float scale, unsigned long long seed, float dropout_p,
+                                void* stream) {
     FEDB_REQUIRE(B > 0 && T > 0 && heads > 0 && max_seqlen > 0, "attn_bwd: empty problem");
     const int H = heads * 64;
     cudaStream_t s = (cudaStream_t)stream;
@@ -493,8 +516,14 @@ extern "C" int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dc
                                                    scale, scale * LOG2E, seed, dropout_thresh16(dropout_p),
                                                    1.0f / (1.0f - dropout_p), dropout_p > 0.f);
     FEDB_LAUNCH_CHECK();
-    const int fin_blocks = T < sm_count() * 16 ? T : sm_count() * 16;
-    attn_dq_finish_kernel<<<fin_blocks, H / 4 >= 256 ? 256 : 192, 0, s>>>(dq_accum, (__nv_bfloat16*)dqkv, T, H);
+    {
+        const int col_blocks = (3 * H + 63) / 64;
+        int row_blocks = (sm_count() * 8 + col_blocks - 1) / col_blocks;
+        if (row_blocks > (T + 31) / 32) row_blocks = (T + 31) / 32;
+        if (row_blocks < 1) row_blocks = 1;
+        const int rpb = (T + row_blocks - 1) / row_blocks;
+        attn_bwd_finish_kernel<<<dim3(col_blocks, row_blocks), dim3(32, 8), 0, s>>>(dq_accum, (__nv_bfloat16*)dqkv, dbias_qkv, T, H, rpb);
+    }
     FEDB_LAUNCH_CHECK();
     return 0;
 }

@@ -102,9 +102,8 @@ extern "C" int fedb200_bert_backward(const fedb200_bert_plan* p, int T, int B, i
                                    0, 0.f, 1, 0, stream));
         FEDB_TRY(fedb200_gemm_bf16(2, df, H, a.ctx, H, H, H, T, FEDB200_EPI_ATOMIC_F32, a.g_wo, nullptr, H, nullptr, nullptr, 0,
                                    p->act, 0, 0.f, wgrad_splits(H, H, T, sms), 0, stream));
-        FEDB_TRY(fedb200_attn_bwd(a.qkv, a.ctx, p->dctx, a.lse, p->delta, p->dqkv, p->dq_accum, p->cu_seqlens, B, T, p->heads,
-                                  max_len, scale, op_seed(step_seed, l, 1), pa, stream));
-        FEDB_TRY(fedb200_colsum_bf16(p->dqkv, a.g_bqkv, T, 3 * H, 3 * H, stream));
+        FEDB_TRY(fedb200_attn_bwd(a.qkv, a.ctx, p->dctx, a.lse, p->delta, p->dqkv, p->dq_accum, a.g_bqkv, p->cu_seqlens, B, T,
+                                  p->heads, max_len, scale, op_seed(step_seed, l, 1), pa, stream));
         FEDB_TRY(fedb200_gemm_bf16(1, p->dqkv, 3 * H, a.wqkv, H, T, H, 3 * H, FEDB200_EPI_ADD, p->dx, nullptr, H, nullptr, p->dzb,
                                    H, p->act, 0, 0.f, 1, 0, stream));
         FEDB_TRY(fedb200_gemm_bf16(2, p->dqkv, 3 * H, a.x_in, H, 3 * H, H, T, FEDB200_EPI_ATOMIC_F32, a.g_wqkv, nullptr, H, nullptr,

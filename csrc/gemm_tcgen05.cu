@@ -3,12 +3,13 @@
 // Replaces the cuBLAS calls behind nn.Linear in the reference's train loop
 // (src/Servercase/server_IID_IMDB.py:108-118; shapes in SURVEY §2.6).
 //
-// Structure (persistent, warp-specialised, one CTA per SM, 192 threads):
+// Structure (persistent, warp-specialised, one CTA per SM, 320 threads):
 //   warp 0  TMA producer   : cp.async.bulk.tensor tiles of A and B into a 4-deep 128B-swizzled smem ring
 //   warp 1  MMA issuer     : one elected thread issues tcgen05.mma (cta_group::1, M=128, N=BN, K=16),
 //                            accumulators double-buffered in TMEM (2 x BN columns), tcgen05.commit frees slots
-//   warps 2-5 epilogue     : tcgen05.ld 32 rows x 32 columns per warp, fused bias / dropout / residual /
-//                            GELU / GELU' / fp32 split-K reduction, direct 16-byte global stores
+//   warps 2-9 epilogue     : tcgen05.ld 32 rows x 32 columns per warp (two warps per lane quadrant interleave
+//                            the column chunks), fused bias / dropout / residual / GELU / GELU' / fp32 split-K
+//                            reduction, residual chunks prefetched one ahead, direct 16-byte global stores
 // Operand layouts (selected per call, all fed by TMA, no transposes are ever materialised):
 //   forward  y = x W^T      A K-major  (x  [M, K]),        B K-major  (W [N, K], the HF Linear layout)
 //   dgrad    dx = dy W      A K-major  (dy [M, N']),       B MN-major (W [N', K'] read as [K = N', N = K'])
@@ -22,7 +23,8 @@ namespace fedb {
 constexpr int GM_BM = 128;
 constexpr int GM_BK = 64;
 constexpr int GM_STAGES = 4;
-constexpr int GM_THREADS = 192;
+constexpr int GM_EPI_WARPS = 8;            // two warps per TMEM lane quadrant; they interleave the 32-column chunks
+constexpr int GM_THREADS = 64 + GM_EPI_WARPS * 32;
 constexpr int GM_A_BYTES = GM_BM * GM_BK * 2;     // 16 KB
 
 struct GemmParams {
@@ -95,7 +97,7 @@ __global__ void __launch_bounds__(GM_THREADS, 1) gemm_tcgen05_kernel(const __gri
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
         for (int s = 0; s < GM_STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], 4); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], GM_EPI_WARPS); }
         mbar_fence_init();
     }
     if (warp == 1) tmem_alloc(&tmem_base_slot, TMEM_COLS);
@@ -167,7 +169,13 @@ __global__ void __launch_bounds__(GM_THREADS, 1) gemm_tcgen05_kernel(const __gri
         }
     } else {
         // =============================== epilogue warps ===============================
+        // Warps w and w+4 read the same TMEM lane quadrant (rows) and take alternate 32-column chunks; with a
+        // single warp per SM sub-partition the elementwise math (GELU, dropout hash) was latency-bound.
         const int quad = warp & 3;                       // TMEM lane quadrant this warp may read
+        const int half = (warp - 2) >> 2;                // 0: even chunks, 1: odd chunks
+        constexpr int N_CHUNKS = BN / 32;
+        const bool needs_aux = p.aux != nullptr && (p.epi == FEDB200_EPI_BIAS_DROP_RES || p.epi == FEDB200_EPI_MUL_GELU_GRAD ||
+                                                    p.epi == FEDB200_EPI_ADD);
         uint32_t local = 0;
         for (int w = blockIdx.x; w < total; w += gridDim.x, ++local) {
             const int tile = w / p.splits;
@@ -175,16 +183,37 @@ __global__ void __launch_bounds__(GM_THREADS, 1) gemm_tcgen05_kernel(const __gri
             const uint32_t buf = local & 1u;
             const int split = w % p.splits;
             const bool has_k = split * kb_per_split < k_blocks;
-            mbar_wait(&acc_full[buf], (local >> 1) & 1u);
-            tc_fence_after_sync();
             const int row = m_blk * GM_BM + quad * 32 + lane;
             const bool row_ok = row < p.M;
+            // prefetch the first aux chunk while the accumulator is still being produced
+            uint4 aux_raw[4];
+            auto fetch_aux = [&](int c) {
+                const int col0 = n_blk * BN + c * 32;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    aux_raw[q] = make_uint4(0u, 0u, 0u, 0u);
+                    if (needs_aux && row_ok && c < N_CHUNKS && col0 + q * 8 < p.N)
+                        aux_raw[q] = __ldg(reinterpret_cast<const uint4*>(p.aux + (size_t)row * p.ld_aux + col0) + q);
+                }
+            };
+            fetch_aux(half);
+            mbar_wait(&acc_full[buf], (local >> 1) & 1u);
+            tc_fence_after_sync();
 #pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
+            for (int c = half; c < N_CHUNKS; c += 2) {
                 const int col0 = n_blk * BN + c * 32;
                 if (col0 >= p.N) break;                  // warp-uniform
                 uint32_t raw[32];
                 tmem_ld_32x32(tmem_base + ((uint32_t)(quad * 32) << 16) + buf * BN + c * 32, raw);
+                float r[32];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float2 a0 = unpack_bf16x2(aux_raw[q].x), a1 = unpack_bf16x2(aux_raw[q].y);
+                    const float2 a2 = unpack_bf16x2(aux_raw[q].z), a3 = unpack_bf16x2(aux_raw[q].w);
+                    r[q * 8 + 0] = a0.x; r[q * 8 + 1] = a0.y; r[q * 8 + 2] = a1.x; r[q * 8 + 3] = a1.y;
+                    r[q * 8 + 4] = a2.x; r[q * 8 + 5] = a2.y; r[q * 8 + 6] = a3.x; r[q * 8 + 7] = a3.y;
+                }
+                fetch_aux(c + 2);                        // next chunk's residual / pre-activation is in flight during the math
                 tmem_ld_wait();
                 const int nvalid = min(32, p.N - col0);
                 if (row_ok) {
@@ -212,8 +241,6 @@ __global__ void __launch_bounds__(GM_THREADS, 1) gemm_tcgen05_kernel(const __gri
                         if (p.epi == FEDB200_EPI_BIAS) {
                             store_bf16x32(o, v, nvalid);
                         } else if (p.epi == FEDB200_EPI_BIAS_DROP_RES) {
-                            float r[32];
-                            load_bf16x32(p.aux + (size_t)row * p.ld_aux + col0, r, nvalid);
                             if (p.use_dropout) {
 #pragma unroll
                                 for (int q = 0; q < 4; ++q)
@@ -232,18 +259,12 @@ __global__ void __launch_bounds__(GM_THREADS, 1) gemm_tcgen05_kernel(const __gri
                             }
                             store_bf16x32(reinterpret_cast<__nv_bfloat16*>(p.out2) + (size_t)row * p.ldo + col0, v, nvalid);
                         } else if (p.epi == FEDB200_EPI_MUL_GELU_GRAD) {
-                            float u[32];
-                            load_bf16x32(p.aux + (size_t)row * p.ld_aux + col0, u, nvalid);
 #pragma unroll
-                            for (int j = 0; j < 32; ++j) v[j] *= p.act ? gelu_tanh_grad(u[j]) : gelu_erf_grad(u[j]);
+                            for (int j = 0; j < 32; ++j) v[j] *= p.act ? gelu_tanh_grad(r[j]) : gelu_erf_grad(r[j]);
                             store_bf16x32(o, v, nvalid);
                         } else {    // FEDB200_EPI_ADD
-                            if (p.aux != nullptr) {
-                                float r[32];
-                                load_bf16x32(p.aux + (size_t)row * p.ld_aux + col0, r, nvalid);
 #pragma unroll
-                                for (int j = 0; j < 32; ++j) v[j] += r[j];
-                            }
+                            for (int j = 0; j < 32; ++j) v[j] += r[j];       // r is zero when there is no aux
                             store_bf16x32(o, v, nvalid);
                         }
                     }

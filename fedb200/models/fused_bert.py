@@ -271,7 +271,7 @@ class FusedRunner:
         from ..ops import _lib
         _lib.call("fedb200_bert_backward", self._plan_ref, T, B, max_len, self._step_seed(), self._sms,
                   torch.cuda.current_stream().cuda_stream)
-        _lib.count(4 + 17 * self.L)
+        _lib.count(4 + 16 * self.L)
 
     def _step_seed(self) -> int:
         return (self.base_seed * 0x100000001B3 + self.step_count) & 0x7FFFFFFFFFFFFFFF
@@ -339,8 +339,7 @@ class FusedRunner:
             ops.gemm(1, df, self._wb(k["o.w"]), self.dctx[:T], T, H, H, ops.EPI_ADD)
             ops.gemm(2, df, a["ctx"][:T], self._g(k["o.w"]), H, H, T, ops.EPI_ATOMIC_F32, splits=self._splits(H, H, T))
             ops.attn_bwd(a["qkv"][:T], a["ctx"][:T], self.dctx[:T], a["lse"], self.delta, self.dqkv[:T],
-                         self.dq_accum[:T], cu, B, self.heads, max_len, scale, self._seed(l, 1), pa)
-            ops.colsum_bf16(self.dqkv[:T], self.gbqkv[l])
+                         self.dq_accum[:T], cu, B, self.heads, max_len, scale, self._seed(l, 1), pa, dbias=self.gbqkv[l])
             ops.gemm(1, self.dqkv[:T], self.wqkv_bf[l], dx, T, H, 3 * H, ops.EPI_ADD, aux=dzb)
             ops.gemm(2, self.dqkv[:T], x, self.gwqkv[l], 3 * H, H, T, ops.EPI_ATOMIC_F32, splits=self._splits(3 * H, H, T))
         ops.embed_bwd(dx, self.d_ids[:T], self.d_pos[:T], self.d_tt[:T], self._w("bert.embeddings.word_embeddings.weight"),

@@ -78,9 +78,11 @@ int fedb200_head_bwd(const void* x, const int* first_tok, const float* Wp, const
  * qkv is [T, 3H] bf16 (Q | K | V), ctx/dctx [T, H], lse [heads, T] fp32; cu_seqlens is int32 [B+1] on device. */
 int fedb200_attn_fwd(const void* qkv, void* ctx, float* lse, const int* cu_seqlens, int B, int T, int heads,
                      int max_seqlen, float scale, unsigned long long seed, float dropout_p, void* stream);
+/* dq_accum: fp32 [T, H] scratch, zero on entry, left zero on exit.  dbias_qkv (optional, fp32 [3H]): the q/k/v bias
+ * gradients (column sums of dqkv) are accumulated into it by the finishing pass. */
 int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dctx, const float* lse, float* delta, void* dqkv,
-                     float* dq_accum, const int* cu_seqlens, int B, int T, int heads, int max_seqlen, float scale,
-                     unsigned long long seed, float dropout_p, void* stream);
+                     float* dq_accum, float* dbias_qkv, const int* cu_seqlens, int B, int T, int heads, int max_seqlen,
+                     float scale, unsigned long long seed, float dropout_p, void* stream);
 
 /* ---- native step executor ------------------------------------------------------------------------------------- */
 /* One call = the whole forward (or backward) launch sequence of the fused BERT trainer.  The plan holds raw

@@ -52,9 +52,11 @@ def test_attention_fwd_bwd_no_dropout(cuda_lib, lens, heads):
     dqkv = torch.zeros(T, 3 * H, dtype=torch.bfloat16, device="cuda")
     dq_acc = torch.zeros(T, H, device="cuda")
     delta = torch.zeros(heads * T, device="cuda")
-    ops.attn_bwd(qkv, ctx, dctx, lse, delta, dqkv, dq_acc, cu, B, heads, max(lens), scale)
+    dbias = torch.ones(3 * H, device="cuda")
+    ops.attn_bwd(qkv, ctx, dctx, lse, delta, dqkv, dq_acc, cu, B, heads, max(lens), scale, dbias=dbias)
     torch.cuda.synchronize()
     g = qr.grad
+    torch.testing.assert_close(dbias, 1.0 + dqkv.float().sum(0), rtol=1e-3, atol=1e-2)    # fused q/k/v bias gradient
     for name, sl in (("dQ", slice(0, H)), ("dK", slice(H, 2 * H)), ("dV", slice(2 * H, 3 * H))):
         e = (dqkv[:, sl].float() - g[:, sl]).abs().max().item()
         scale_ref = g[:, sl].abs().max().item()
