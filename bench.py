@@ -268,7 +268,8 @@ def run_torch_baseline(args):
         with torch.no_grad():
             for batch in loader:
                 batch = {k: v.to(dev) for k, v in batch.items()}
-                out = model(**batch)
+                with torch.autocast("cuda", dtype=torch.bfloat16, enabled=args.amp):
+                    out = model(**batch)
                 correct += int((out.logits.argmax(-1) == batch["labels"]).sum().item())
         return correct
 
@@ -278,7 +279,9 @@ def run_torch_baseline(args):
         model.train()
         for batch in tr:
             batch = {k: v.to(dev) for k, v in batch.items()}
-            model(**batch).loss.backward()
+            with torch.autocast("cuda", dtype=torch.bfloat16, enabled=args.amp):
+                loss = model(**batch).loss
+            loss.backward()
             opt.step()
             opt.zero_grad()
         evaluate(te)
@@ -325,7 +328,7 @@ def run_torch_baseline(args):
         print(json.dumps({"metric": "train_samples_per_s (FL round = local epoch + local eval + aggregate + global eval)",
                           "value": round(v, 2), "unit": "samples/s", "n_gpus": n, "steps": K, "warmup": W,
                           "ms_per_step": round(t.item() / K * 1e3, 3), "higher_is_better": True, "scaling": "weak",
-                          "vs_baseline": round(v / PUBLISHED_TRAIN_SAMPLES_PER_S, 2), "dtype": "fp32", "data": "synthetic",
+                          "vs_baseline": round(v / PUBLISHED_TRAIN_SAMPLES_PER_S, 2), "dtype": "bf16-autocast" if args.amp else "fp32", "data": "synthetic",
                           "impl": "torch_baseline", "clocks": clocks,
                           "config": {"model": "transformers BertForSequenceClassification (BioBERT shape)", "agg": args.agg,
                                      "peers": n, "seq_len": args.seq_len, "batch_per_peer": args.batch_size,
@@ -350,6 +353,7 @@ def main():
     ap.add_argument("--comm", default="auto")
     ap.add_argument("--agg", default="numpy", choices=["numpy", "nccl"])
     ap.add_argument("--no-ledger", action="store_true")
+    ap.add_argument("--amp", action="store_true", help="torch_baseline only: bf16 autocast instead of the reference's fp32")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
