@@ -43,10 +43,16 @@ extern "C" int fedb200_bert_forward(const fedb200_bert_plan* p, int T, int B, in
     FEDB_REQUIRE(p != nullptr && T > 0 && B > 0, "bert_forward: empty batch");
     FEDB_REQUIRE(p->L >= 1 && p->L <= FEDB200_MAX_LAYERS, "bert_forward: %d layers (max %d)", p->L, FEDB200_MAX_LAYERS);
     const int H = p->H, I = p->I;
+    const int E = p->E > 0 ? p->E : H;
     const float ph = train ? p->p_hidden : 0.f, pa = train ? p->p_attn : 0.f;
+    const float pe = train ? p->p_embed : 0.f, phead = train ? p->p_head : 0.f;
     const float scale = 1.0f / sqrtf((float)(H / p->heads));
-    FEDB_TRY(fedb200_embed_fwd(p->ids, p->pos_ids, p->tt, p->word, p->pos, p->type, p->emb_lnw, p->emb_lnb, p->layer[0].x_in,
-                               p->emb_mean, p->emb_rstd, T, H, p->ln_eps, op_seed(step_seed, 99, 0), ph, stream));
+    void* emb_dst = E == H ? p->layer[0].x_in : p->emb_out;
+    FEDB_TRY(fedb200_embed_fwd(p->ids, p->pos_ids, p->tt, p->word, p->pos, p->type, p->emb_lnw, p->emb_lnb, emb_dst,
+                               p->emb_mean, p->emb_rstd, T, E, p->ln_eps, op_seed(step_seed, 99, 0), pe, stream));
+    if (E != H)      // ALBERT: embedding_hidden_mapping_in
+        FEDB_TRY(fedb200_gemm_bf16(0, p->emb_out, E, p->map_w, E, T, H, E, FEDB200_EPI_BIAS, p->layer[0].x_in, nullptr, H, p->map_b,
+                                   nullptr, 0, p->act, 0, 0.f, 1, 0, stream));
     for (int l = 0; l < p->L; ++l) {
         const fedb200_bert_layer& a = p->layer[l];
         FEDB_TRY(fedb200_gemm_bf16(0, a.x_in, H, a.wqkv, H, T, 3 * H, H, FEDB200_EPI_BIAS, a.qkv, nullptr, 3 * H, a.bqkv,
@@ -64,7 +70,7 @@ extern "C" int fedb200_bert_forward(const fedb200_bert_plan* p, int T, int B, in
     }
     FEDB_TRY(fedb200_head_fwd(p->layer[p->L - 1].x_out, p->cu_seqlens, p->Wp, p->bp, p->Wc, p->bc, p->labels, p->pooled,
                               p->pooled_drop, p->logits, p->loss, p->pred, p->dlogits, B, H, p->C, 1.0f / (float)B,
-                              op_seed(step_seed, 98, 0), ph, stream));
+                              op_seed(step_seed, 98, 0), phead, stream));
     return 0;
 }
 
@@ -73,14 +79,15 @@ extern "C" int fedb200_bert_backward(const fedb200_bert_plan* p, int T, int B, i
     FEDB_REQUIRE(p != nullptr && T > 0 && B > 0, "bert_backward: empty batch");
     const int H = p->H, I = p->I;
     const int sms = sm_count_hint > 0 ? sm_count_hint : sm_count();
+    const int E = p->E > 0 ? p->E : H;
     const float ph = p->p_hidden, pa = p->p_attn;
     const float scale = 1.0f / sqrtf((float)(H / p->heads));
     cudaStream_t s = (cudaStream_t)stream;
     void* df = ph > 0.f ? p->dfb : p->dzb;          // dense-output gradient seen through its dropout mask
     FEDB_CHECK(cudaMemsetAsync(p->dx, 0, (size_t)T * H * 2, s));
     FEDB_TRY(fedb200_head_bwd(p->layer[p->L - 1].x_out, p->cu_seqlens, p->Wp, p->Wc, p->pooled, p->pooled_drop, p->dlogits,
-                              p->dpre, p->g_Wp, p->g_bp, p->g_Wc, p->g_bc, p->dx, B, H, p->C, op_seed(step_seed, 98, 0), ph,
-                              stream));
+                              p->dpre, p->g_Wp, p->g_bp, p->g_Wc, p->g_bc, p->dx, B, H, p->C, op_seed(step_seed, 98, 0),
+                              p->p_head, stream));
     for (int l = p->L - 1; l >= 0; --l) {
         const fedb200_bert_layer& a = p->layer[l];
         // ---- FFN block ----
@@ -109,8 +116,17 @@ extern "C" int fedb200_bert_backward(const fedb200_bert_plan* p, int T, int B, i
         FEDB_TRY(fedb200_gemm_bf16(2, p->dqkv, 3 * H, a.x_in, H, 3 * H, H, T, FEDB200_EPI_ATOMIC_F32, a.g_wqkv, nullptr, H, nullptr,
                                    nullptr, 0, p->act, 0, 0.f, wgrad_splits(3 * H, H, T, sms), 0, stream));
     }
-    FEDB_TRY(fedb200_embed_bwd(p->dx, p->ids, p->pos_ids, p->tt, p->word, p->pos, p->type, p->emb_lnw, p->emb_mean, p->emb_rstd,
-                               p->g_word, p->g_pos, p->g_type, p->g_emb_lnw, p->g_emb_lnb, T, H, p->type_vocab,
-                               op_seed(step_seed, 99, 0), ph, stream));
+    const void* d_emb = p->dx;
+    if (E != H) {    // back through the ALBERT embedding projection: bias, weight and input gradients
+        FEDB_TRY(fedb200_colsum_bf16(p->dx, p->g_map_b, T, H, H, stream));
+        FEDB_TRY(fedb200_gemm_bf16(2, p->dx, H, p->emb_out, E, H, E, T, FEDB200_EPI_ATOMIC_F32, p->g_map_w, nullptr, E, nullptr,
+                                   nullptr, 0, p->act, 0, 0.f, wgrad_splits(H, E, T, sms), 0, stream));
+        FEDB_TRY(fedb200_gemm_bf16(1, p->dx, H, p->map_w, E, T, E, H, FEDB200_EPI_ADD, p->d_emb, nullptr, E, nullptr, nullptr, 0,
+                                   p->act, 0, 0.f, 1, 0, stream));
+        d_emb = p->d_emb;
+    }
+    FEDB_TRY(fedb200_embed_bwd(d_emb, p->ids, p->pos_ids, p->tt, p->word, p->pos, p->type, p->emb_lnw, p->emb_mean, p->emb_rstd,
+                               p->g_word, p->g_pos, p->g_type, p->g_emb_lnw, p->g_emb_lnb, T, E, p->type_vocab,
+                               op_seed(step_seed, 99, 0), p->p_embed, stream));
     return 0;
 }

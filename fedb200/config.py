@@ -28,6 +28,8 @@ MODEL_PRESETS = {
     # small head_dim-64 shape for GPU tests of the fused trainer
     "bert-mini": dict(arch="bert", vocab_size=2048, hidden_size=128, num_layers=2, num_heads=2,
                       intermediate_size=256, max_position=512),
+    "albert-mini": dict(arch="albert", vocab_size=2048, hidden_size=128, num_layers=3, num_heads=2,
+                        intermediate_size=256, embedding_size=64, max_position=512),
     # tiny shapes for CPU tests
     "bert-tiny": dict(arch="bert", vocab_size=512, hidden_size=64, num_layers=2, num_heads=2,
                       intermediate_size=128, max_position=128),

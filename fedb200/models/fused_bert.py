@@ -46,15 +46,50 @@ def _layer_keys(l: int) -> Dict[str, str]:
     }
 
 
+def _albert_layer_keys() -> Dict[str, str]:
+    p = "albert.encoder.albert_layer_groups.0.albert_layers.0."
+    return {
+        "q.w": p + "attention.query.weight", "k.w": p + "attention.key.weight", "v.w": p + "attention.value.weight",
+        "q.b": p + "attention.query.bias", "k.b": p + "attention.key.bias", "v.b": p + "attention.value.bias",
+        "o.w": p + "attention.dense.weight", "o.b": p + "attention.dense.bias",
+        "ln1.w": p + "attention.LayerNorm.weight", "ln1.b": p + "attention.LayerNorm.bias",
+        "f1.w": p + "ffn.weight", "f1.b": p + "ffn.bias", "f2.w": p + "ffn_output.weight", "f2.b": p + "ffn_output.bias",
+        "ln2.w": p + "full_layer_layer_norm.weight", "ln2.b": p + "full_layer_layer_norm.bias",
+    }
+
+
+_LAYER_ORDER = ("q.w", "k.w", "v.w", "q.b", "k.b", "v.b", "o.w", "o.b", "ln1.w", "ln1.b", "f1.w", "f1.b", "f2.w", "f2.b",
+                "ln2.w", "ln2.b")
+
+
+def _roles(cfg: ModelConfig):
+    """HF key names of every tensor the engine touches, per architecture.  ALBERT shares ONE layer's weights
+    across all ``num_layers`` applications (every entry of ``layers`` is the same dict) and adds the
+    128 -> H embedding projection."""
+    if cfg.arch == "bert":
+        e = "bert.embeddings."
+        return dict(word=e + "word_embeddings.weight", pos=e + "position_embeddings.weight",
+                    type=e + "token_type_embeddings.weight", emb_lnw=e + "LayerNorm.weight", emb_lnb=e + "LayerNorm.bias",
+                    map_w=None, map_b=None, layers=[_layer_keys(l) for l in range(cfg.num_layers)],
+                    Wp="bert.pooler.dense.weight", bp="bert.pooler.dense.bias", Wc="classifier.weight", bc="classifier.bias")
+    e = "albert.embeddings."
+    lk = _albert_layer_keys()
+    return dict(word=e + "word_embeddings.weight", pos=e + "position_embeddings.weight",
+                type=e + "token_type_embeddings.weight", emb_lnw=e + "LayerNorm.weight", emb_lnb=e + "LayerNorm.bias",
+                map_w="albert.encoder.embedding_hidden_mapping_in.weight", map_b="albert.encoder.embedding_hidden_mapping_in.bias",
+                layers=[lk] * cfg.num_layers, Wp="albert.pooler.weight", bp="albert.pooler.bias", Wc="classifier.weight",
+                bc="classifier.bias")
+
+
 class FusedRunner:
-    """Drop-in for :class:`fedb200.trainer.local.TorchRunner` on a CUDA device (BERT family)."""
+    """Drop-in for :class:`fedb200.trainer.local.TorchRunner` on a CUDA device (BERT and ALBERT families)."""
 
     backend = "fused"
 
     def __init__(self, model_cfg: ModelConfig, fed: Optional[FedConfig] = None, device="cuda", seed: Optional[int] = 0,
                  max_tokens: Optional[int] = None, max_batch: Optional[int] = None):
-        if model_cfg.arch != "bert":
-            raise ValueError("the fused runner implements the BERT family; use backend='torch' for ALBERT")
+        if model_cfg.arch not in ("bert", "albert"):
+            raise ValueError(f"no fused implementation for architecture {model_cfg.arch!r}")
         if model_cfg.head_dim != 64:
             raise ValueError("fused attention is specialised for head_dim 64 (BERT-base/large, BioBERT)")
         from ..ops import cuda_ops           # fails loudly if libfedb200.so is missing
@@ -70,14 +105,19 @@ class FusedRunner:
         ref = build_model(c, "cpu", seed)
         sd = ref.state_dict()
         hf_order = list(sd.keys())
-        order = ["bert.embeddings.word_embeddings.weight", "bert.embeddings.position_embeddings.weight",
-                 "bert.embeddings.token_type_embeddings.weight", "bert.embeddings.LayerNorm.weight",
-                 "bert.embeddings.LayerNorm.bias"]
-        self.lk = [_layer_keys(l) for l in range(self.L)]
+        self.roles = R = _roles(c)
+        self.E = c.embedding_size if c.arch == "albert" else c.hidden_size
+        order = [R["word"], R["pos"], R["type"], R["emb_lnw"], R["emb_lnb"]]
+        if R["map_w"]:
+            order += [R["map_w"], R["map_b"]]
+        self.lk = R["layers"]
+        seen = set()
         for k in self.lk:
-            order += [k[n] for n in ("q.w", "k.w", "v.w", "q.b", "k.b", "v.b", "o.w", "o.b", "ln1.w", "ln1.b", "f1.w",
-                                     "f1.b", "f2.w", "f2.b", "ln2.w", "ln2.b")]
-        order += ["bert.pooler.dense.weight", "bert.pooler.dense.bias", "classifier.weight", "classifier.bias"]
+            if id(k) in seen:
+                continue
+            seen.add(id(k))
+            order += [k[n] for n in _LAYER_ORDER]
+        order += [R["Wp"], R["bp"], R["Wc"], R["bc"]]
         assert sorted(order) == sorted(hf_order), "unexpected parameter set"
         shapes = OrderedDict((k, tuple(sd[k].shape)) for k in order)
         self.arena = FlatArena(shapes, torch.float32, self.device, key_order=hf_order)
@@ -111,6 +151,8 @@ class FusedRunner:
                          mean1=f32(T), rstd1=f32(T), mean2=f32(T), rstd2=f32(T), lse=f32(self.heads * T))
                     for _ in range(L)]
         self.emb_mean, self.emb_rstd = f32(T), f32(T)
+        self.emb_out = bf(T, self.E) if self.E != H else None
+        self.d_emb = bf(T, self.E) if self.E != H else None
         self.dx, self.dzb, self.dfb, self.dctx = bf(T, H), bf(T, H), bf(T, H), bf(T, H)
         self.du, self.dqkv = bf(T, I), bf(T, 3 * H)
         self.dq_accum = torch.zeros(T, H, dtype=torch.float32, device=dev)
@@ -147,16 +189,23 @@ class FusedRunner:
         if self.L > MAX_LAYERS:
             raise ValueError(f"{self.L} layers exceed the native plan capacity ({MAX_LAYERS})")
         P = BertPlan()
-        P.H, P.I, P.L, P.heads, P.C, P.type_vocab, P.act = self.H, self.I, self.L, self.heads, self.C, c.type_vocab_size, 0
-        P.ln_eps, P.p_hidden, P.p_attn = c.layer_norm_eps, c.hidden_dropout, c.attention_dropout
+        R = self.roles
+        albert = c.arch == "albert"
+        P.H, P.I, P.L, P.heads, P.C, P.type_vocab = self.H, self.I, self.L, self.heads, self.C, c.type_vocab_size
+        P.act, P.E = (1 if albert else 0), self.E
+        P.ln_eps = c.layer_norm_eps
+        if albert:       # albert-base-v2: no encoder dropout, classifier dropout 0.1 (see models/albert.py)
+            P.p_hidden, P.p_attn, P.p_embed, P.p_head = 0.0, 0.0, 0.0, (0.1 if c.hidden_dropout > 0 else 0.0)
+        else:
+            P.p_hidden, P.p_attn, P.p_embed, P.p_head = c.hidden_dropout, c.attention_dropout, c.hidden_dropout, c.hidden_dropout
         w, g = (lambda k: self.arena.views[k].data_ptr()), (lambda k: self.grads.views[k].data_ptr())
-        e = "bert.embeddings."
-        for f, k in (("word", e + "word_embeddings.weight"), ("pos", e + "position_embeddings.weight"),
-                     ("type", e + "token_type_embeddings.weight"), ("emb_lnw", e + "LayerNorm.weight"),
-                     ("emb_lnb", e + "LayerNorm.bias"), ("Wp", "bert.pooler.dense.weight"), ("bp", "bert.pooler.dense.bias"),
-                     ("Wc", "classifier.weight"), ("bc", "classifier.bias")):
-            setattr(P, f, w(k))
-            setattr(P, "g_" + f, g(k))
+        for f in ("word", "pos", "type", "emb_lnw", "emb_lnb", "Wp", "bp", "Wc", "bc"):
+            setattr(P, f, w(R[f]))
+            setattr(P, "g_" + f, g(R[f]))
+        if albert:
+            P.map_w, P.map_b = self.shadow.views[R["map_w"]].data_ptr(), w(R["map_b"])
+            P.g_map_w, P.g_map_b = g(R["map_w"]), g(R["map_b"])
+            P.emb_out, P.d_emb = self.emb_out.data_ptr(), self.d_emb.data_ptr()
         for f, t in (("emb_mean", self.emb_mean), ("emb_rstd", self.emb_rstd), ("ids", self.d_ids), ("pos_ids", self.d_pos),
                      ("tt", self.d_tt), ("cu_seqlens", self.d_cu), ("labels", self.d_labels), ("pooled", self.pooled),
                      ("pooled_drop", self.pooled_drop), ("dpre", self.dpre), ("logits", self.logits),
@@ -277,7 +326,9 @@ class FusedRunner:
         return (self.base_seed * 0x100000001B3 + self.step_count) & 0x7FFFFFFFFFFFFFFF
 
     def _forward_py(self, T: int, B: int, max_len: int, train: bool) -> None:
-        """Python twin of csrc/bert_engine.cu::fedb200_bert_forward (kept for debugging / documentation)."""
+        """Python twin of csrc/bert_engine.cu::fedb200_bert_forward (kept for debugging / documentation; BERT only)."""
+        if self.cfg.arch != "bert":
+            raise NotImplementedError("the Python twin covers BERT; ALBERT runs on the native executor only")
         ops, H, I, c = self.ops, self.H, self.I, self.cfg
         ph = c.hidden_dropout if train else 0.0
         pa = c.attention_dropout if train else 0.0

@@ -64,12 +64,13 @@ MAX_LAYERS = 48
 
 class BertPlan(C.Structure):
     """Mirror of ``fedb200_bert_plan`` (include/fedb200.h)."""
-    _fields_ = ([(n, i32) for n in ("H", "I", "L", "heads", "C", "type_vocab", "act")]
-                + [(n, f32) for n in ("ln_eps", "p_hidden", "p_attn")]
+    _fields_ = ([(n, i32) for n in ("H", "I", "L", "heads", "C", "type_vocab", "act", "E")]
+                + [(n, f32) for n in ("ln_eps", "p_hidden", "p_attn", "p_embed", "p_head")]
                 + [(n, vp) for n in (
                     "word", "pos", "type", "emb_lnw", "emb_lnb", "Wp", "bp", "Wc", "bc",
                     "g_word", "g_pos", "g_type", "g_emb_lnw", "g_emb_lnb", "g_Wp", "g_bp", "g_Wc", "g_bc",
-                    "emb_mean", "emb_rstd", "ids", "pos_ids", "tt", "cu_seqlens", "labels",
+                    "emb_mean", "emb_rstd", "map_w", "map_b", "g_map_w", "g_map_b", "emb_out", "d_emb",
+                    "ids", "pos_ids", "tt", "cu_seqlens", "labels",
                     "pooled", "pooled_drop", "dpre", "logits", "dlogits", "loss", "pred",
                     "dx", "dzb", "dfb", "dctx", "du", "dqkv", "dq_accum", "delta")]
                 + [("layer", BertLayer * MAX_LAYERS)])

@@ -110,7 +110,8 @@ def make_runner(fed: FedConfig, device=None, seed: Optional[int] = None):
     seed = fed.seed if seed is None else seed
     backend = fed.backend
     if backend == "auto":
-        backend = "fused" if (dev.type == "cuda" and fed.model.arch == "bert") else "torch"
+        fusable = fed.model.arch in ("bert", "albert") and fed.model.head_dim == 64 and fed.model.hidden_size <= 1024
+        backend = "fused" if (dev.type == "cuda" and fusable) else "torch"
     if backend == "fused":
         from ..models.fused_bert import FusedRunner
         return FusedRunner(fed.model, fed, dev, seed)

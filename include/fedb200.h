@@ -101,12 +101,18 @@ typedef struct {
 } fedb200_bert_layer;
 
 typedef struct {
-    int H, I, L, heads, C, type_vocab, act;
-    float ln_eps, p_hidden, p_attn;
+    int H, I, L, heads, C, type_vocab, act;   /* act: 0 erf GELU (BERT), 1 tanh GELU (ALBERT gelu_new) */
+    int E;                                    /* embedding width; E != H adds the ALBERT 128 -> H projection */
+    float ln_eps, p_hidden, p_attn, p_embed, p_head;
     /* embeddings + head (fp32 master) and their gradients */
     const float *word, *pos, *type, *emb_lnw, *emb_lnb, *Wp, *bp, *Wc, *bc;
     float *g_word, *g_pos, *g_type, *g_emb_lnw, *g_emb_lnb, *g_Wp, *g_bp, *g_Wc, *g_bc;
     float *emb_mean, *emb_rstd;
+    /* factorised-embedding projection (ALBERT): bf16 shadow weight [H, E], fp32 bias, grads, [T, E] buffers */
+    const void* map_w;
+    const float* map_b;
+    float *g_map_w, *g_map_b;
+    void *emb_out, *d_emb;
     /* inputs (packed tokens) */
     const int *ids, *pos_ids, *tt, *cu_seqlens, *labels;
     /* head buffers */
