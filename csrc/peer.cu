@@ -148,6 +148,16 @@ __global__ void __launch_bounds__(32) peer_barrier_kernel(const PeerTable t, int
     cross_rank_barrier(t, FLG_BAR, rank, world, epoch, clock64() + timeout_cycles);
 }
 
+// Single-word progress flags for the asynchronous gossip executor (K3): `pub[p]` / `done[p]` epochs are written by
+// the owning rank with a system-scope release and polled by consumers on other GPUs with acquire loads.
+__global__ void flag_set_kernel(unsigned int* flag, unsigned int value) {
+    __threadfence_system();
+    st_release_sys(flag, value);
+}
+__global__ void flag_wait_kernel(const unsigned int* flag, unsigned int value, long long timeout_cycles, unsigned int* err) {
+    if (!spin_until(flag, value, clock64() + timeout_cycles, true) && err != nullptr) *err = 1u;
+}
+
 }  // namespace fedb
 
 using namespace fedb;
@@ -216,6 +226,20 @@ extern "C" int fedb200_peer_barrier(unsigned int* const* flag_ptrs, int rank, in
         t.flags[p] = p < world ? flag_ptrs[p] : nullptr;
     }
     peer_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(t, rank, world, epoch, timeout_to_cycles(timeout_ms));
+    FEDB_LAUNCH_CHECK();
+    return 0;
+}
+
+// Publish / await one monotone progress word (device-side, stream-ordered; no host involvement).
+extern "C" int fedb200_flag_set(unsigned int* flag, unsigned int value, void* stream) {
+    flag_set_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(flag, value);
+    FEDB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int fedb200_flag_wait(const unsigned int* flag, unsigned int value, int timeout_ms, unsigned int* err,
+                                 void* stream) {
+    flag_wait_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(flag, value, timeout_to_cycles(timeout_ms), err);
     FEDB_LAUNCH_CHECK();
     return 0;
 }

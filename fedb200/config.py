@@ -105,6 +105,10 @@ class FedConfig:
     serverless_semantics: str = "parallel"
     asynchronous: bool = False
     staleness_decay: float = 0.5       # alpha(tau) = base / (1 + tau)^decay
+    async_scheduled: bool = False      # force the deterministic schedule-driven executor (always used when world > 1)
+    async_epoch_s: float = 0.05        # modelled local-epoch duration of the schedule's virtual clock
+    async_spread: float = 0.5          # peer heterogeneity of the modelled durations
+    async_fanout: Optional[int] = None # destinations per publish (None = every reachable peer)
     topology: str = "full"             # full | ring | reference10 | random
     route_optimizer: bool = True
     anomaly_detector: str = "none"     # none | pagerank | modz | dbscan | community | cosine_pagerank
@@ -146,6 +150,8 @@ def build_parser(defaults: Optional[FedConfig] = None, description: str = "") ->
     p.add_argument("--comm", default=d.comm, choices=["auto", "loopback", "peer", "nccl"])
     p.add_argument("--semantics", default=d.serverless_semantics, choices=["parallel", "handoff"])
     p.add_argument("--async", dest="asynchronous", action="store_true", default=d.asynchronous)
+    p.add_argument("--async-scheduled", action="store_true", default=d.async_scheduled)
+    p.add_argument("--async-fanout", type=int, default=d.async_fanout)
     p.add_argument("--topology", default=d.topology)
     p.add_argument("--no-route-optimizer", dest="route_optimizer", action="store_false", default=d.route_optimizer)
     p.add_argument("--anomaly-detector", default=d.anomaly_detector)
@@ -180,6 +186,7 @@ def config_from_args(args: argparse.Namespace, defaults: Optional[FedConfig] = N
     cfg.num_clients, cfg.num_rounds, cfg.lr = args.clients, args.rounds, args.lr
     cfg.device, cfg.backend, cfg.comm = args.device, args.backend, args.comm
     cfg.serverless_semantics, cfg.asynchronous = args.semantics, args.asynchronous
+    cfg.async_scheduled, cfg.async_fanout = args.async_scheduled, args.async_fanout
     cfg.topology, cfg.route_optimizer = args.topology, args.route_optimizer
     cfg.anomaly_detector, cfg.inject_anomalies, cfg.inject_kind = (
         args.anomaly_detector, args.inject_anomalies, args.inject_kind)

@@ -76,6 +76,19 @@ class Comm:
         """Global ``[N, N]`` Gram matrix of all peers' delta rows (fp32, on every rank)."""
         raise NotImplementedError
 
+    # -- async executor hooks (single-process backends: stream order already provides the ordering) ----------
+    def peer_ptr(self, t: torch.Tensor, rank: int) -> int:
+        return t.data_ptr()
+
+    def flag_set(self, flags: torch.Tensor, index: int, value: int) -> None:
+        flags[index] = value
+
+    def flag_wait(self, flags: torch.Tensor, owner_rank: int, index: int, value: int) -> None:
+        pass
+
+    def check_errors(self) -> None:
+        pass
+
     def close(self) -> None:
         pass
 

@@ -117,6 +117,24 @@ class PeerComm(Comm):
         dist.all_reduce(t, op=dist.ReduceOp.SUM if op == "sum" else dist.ReduceOp.MAX)
         return t.tolist()
 
+    def peer_ptr(self, t: torch.Tensor, rank: int) -> int:
+        """Address of the same symmetric location as ``t`` inside ``rank``'s copy of the buffer."""
+        buf, off = self._locate(t)
+        return buf.ptrs[rank] + off
+
+    def flag_set(self, flags: torch.Tensor, index: int, value: int) -> None:
+        call("fedb200_flag_set", flags.data_ptr() + 4 * index, int(value), torch.cuda.current_stream().cuda_stream)
+        count()
+        self.launches += 1
+
+    def flag_wait(self, flags: torch.Tensor, owner_rank: int, index: int, value: int) -> None:
+        """Block the current stream until ``owner_rank``'s copy of ``flags[index]`` has reached ``value``."""
+        err = self.flags.tensor.data_ptr() + 4 * 18
+        call("fedb200_flag_wait", self.peer_ptr(flags, owner_rank) + 4 * index, int(value), self.timeout_ms, err,
+             torch.cuda.current_stream().cuda_stream)
+        count()
+        self.launches += 1
+
     def check_errors(self) -> None:
         if int(self.flags.tensor.view(torch.int32)[18].item()) != 0:
             raise RuntimeError("a peer-memory barrier timed out (flag protocol error or a rank is missing)")

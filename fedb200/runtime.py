@@ -289,10 +289,129 @@ class FedRuntime:
                 "samples": sum(i["samples"] for i in infos), "tokens": sum(i["tokens"] for i in infos)}
 
     # ---- asynchronous serverless (virtual-time event engine) -------------------------------------------
+    def run_async_scheduled(self) -> Dict:
+        """Multi-GPU asynchronous gossip: every rank derives the same virtual-time schedule
+        (:mod:`fedb200.p2p.schedule`) and executes its own peers' events; cross-GPU ordering is enforced by
+        device-side progress flags in peer memory (``pub`` / ``done`` epochs), never by host barriers."""
+        from .p2p import build_async_schedule, model_durations
+        from .parallel.placement import owner_of
+        cfg, N, D, comm = self.cfg, self.N, self.D, self.comm
+        on_gpu = self.device.type == "cuda"
+        if self.world > 1 and comm.name != "peer":
+            raise NotImplementedError("multi-rank asynchronous gossip needs the peer-memory backend (device flags)")
+        masked = list(self.static_masked)
+        dur = model_durations(N, cfg.async_epoch_s, cfg.async_spread, cfg.seed)
+        sched = build_async_schedule(self.topo, self.nbytes, cfg.num_rounds, dur, cfg.staleness_decay, masked=masked,
+                                     route_optimizer=cfg.route_optimizer, fanout=cfg.async_fanout)
+        R, P = sched.slots_per_peer, self.P
+        outbox = comm.alloc("async_outbox", P * R * D).view(P, R, D)
+        state = comm.alloc("async_state", P * D).view(P, D)
+        flags = comm.alloc("async_flags", 2 * N + 2, torch.int32)        # pub[0, N) | done[N, 2N)
+        for li in range(len(self.local_ids)):
+            state[li].copy_(self.global_flat)
+        if on_gpu:
+            torch.cuda.synchronize()
+        comm.barrier()
+        mine = [ev for ev in sched.events if owner_of(ev.peer, N, self.world)[0] == self.rank]
+        root_table = torch.zeros(max(len(mine), 1), 32, dtype=torch.uint8, device=self.device) if self.ledger is not None else None
+        if self.ledger is not None and on_gpu:
+            from .ops import cuda_ops
+            nch = (self.nbytes + self.ledger.chunk_bytes - 1) // self.ledger.chunk_bytes
+            leaves_ws = torch.empty(nch, 32, dtype=torch.uint8, device=self.device)
+            scratch_ws = torch.empty((nch + 1) // 2 + 1, 32, dtype=torch.uint8, device=self.device)
+        samples = tokens = 0
+        t0 = time.perf_counter()
+        for n_mine, ev in enumerate(mine):
+            li = owner_of(ev.peer, N, self.world)[1]
+            tr, _ = client_loaders(self.corpus, cfg.data, ev.peer, ev.epoch - 1, pin=on_gpu)
+            with self.timer.phase("train"):
+                self.runner.load_flat(state[li])
+                self.runner.sync_shadow()
+                self.runner.train_epochs(tr, cfg.local_epochs)
+                self.injector.maybe_corrupt(ev.peer, self.runner.flat, state[li], ev.epoch - 1)
+            samples, tokens = samples + tr.num_samples, tokens + tr.num_tokens()
+            with self.timer.phase("aggregate"):
+                srcs, ws = [self.runner.flat], [ev.self_weight]
+                for s_peer, s_epoch, w in zip(ev.sources, ev.source_epochs, ev.weights):
+                    rs, ls = owner_of(s_peer, N, self.world)
+                    if rs != self.rank:
+                        comm.flag_wait(flags, rs, s_peer, s_epoch)            # that version has been published
+                    slot = sched.slot_of(s_peer, s_epoch)
+                    srcs.append(comm.peer_ptr(outbox[ls, slot], rs) if on_gpu else outbox[ls, slot])
+                    ws.append(w)
+                if on_gpu:
+                    from .ops import cuda_ops
+                    cuda_ops.mix_n(srcs, ws, state[li])
+                    comm.launches += 1
+                else:
+                    acc = torch.zeros_like(state[li])
+                    for b, w in zip(srcs, ws):
+                        acc.add_(b, alpha=float(w))
+                    state[li].copy_(acc)
+                comm.flag_set(flags, N + ev.peer, ev.epoch)                   # done: sources may be overwritten
+            with self.timer.phase("publish"):
+                for c_peer, c_epoch in ev.overwrite_waits:                     # consumers of the version this slot held
+                    rc = owner_of(c_peer, N, self.world)[0]
+                    if rc != self.rank:
+                        comm.flag_wait(flags, rc, N + c_peer, c_epoch)
+                dst = outbox[li, ev.slot]
+                if self.ledger is not None and on_gpu:
+                    cuda_ops.sha256_leaves(state[li], dst, self.ledger.chunk_bytes, leaves_ws)
+                    cuda_ops.merkle_root(leaves_ws, scratch_ws, root_table[n_mine])
+                    comm.launches += 2
+                else:
+                    dst.copy_(state[li])
+                    if self.ledger is not None:
+                        from .ledger.merkle import merkle_root
+                        root_table[n_mine] = torch.frombuffer(bytearray(merkle_root(dst.numpy().tobytes(), self.ledger.chunk_bytes)),
+                                                              dtype=torch.uint8)
+                comm.flag_set(flags, ev.peer, ev.epoch)                        # pub
+        if on_gpu:
+            torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+        comm.barrier()
+        comm.check_errors()
+        # ---- consensus model, evaluation, ledger ----------------------------------------------------------------
+        keep_w = [0.0 if k in masked else 1.0 for k in self.local_ids]
+        L = len(self.local_ids)
+        if on_gpu:
+            from .ops import cuda_ops
+            live = [i for i in range(L) if keep_w[i] != 0.0]
+            if live:
+                cuda_ops.mix_n([state[i] for i in live], [1.0] * len(live), self.acc)
+            else:
+                self.acc.zero_()
+        else:
+            self.acc.zero_()
+            for i in range(L):
+                if keep_w[i]:
+                    self.acc.add_(state[i])
+        comm.weighted_mean(self.acc, float(sum(keep_w)), self.global_flat)
+        self.runner.load_flat(self.global_flat)
+        self.runner.sync_shadow()
+        gl, ga = self.runner.evaluate(global_test_loader(self.corpus, cfg.data, cfg.num_rounds, pin=on_gpu))
+        self.global_accuracies.append(float(ga))
+        if self.ledger is not None:
+            rows = root_table.cpu().numpy()
+            local = [(ev.index, ev.peer, ev.epoch, bytes(rows[i]).hex(), ev.dests[:16]) for i, ev in enumerate(mine)]
+            for idx, peer, epoch, root_hex, dests in sorted(sum(comm.all_gather_object(local), [])):
+                self.ledger.append(epoch, peer, BROADCAST, bytes.fromhex(root_hex), self.nbytes, 0, dests,
+                                   timestamp_ns=idx)
+            self.ledger.assert_valid()
+        tot = comm.reduce_scalars([samples, tokens], "sum")
+        mx = comm.reduce_scalars([wall], "max")[0]
+        res = {"accuracy": float(ga), "loss": float(gl), "mixes": len(sched.events), "makespan_model_s": sched.makespan,
+               "async_comm_time": sched.async_comm_time, "sync_equiv_comm_time": sched.sync_equiv_comm_time,
+               "outbox_slots": R, "masked": masked, "wall_s": mx, "samples_per_s": tot[0] / mx if mx else None,
+               "info_passing": info_passing_time(self.topo, self.nbytes, 0, removed=masked)}
+        self.async_schedule = sched
+        self.async_state = state
+        self.log.log("async_done", **res)
+        return res
+
     def run_async(self) -> Dict:
-        if self.world != 1:
-            raise NotImplementedError("asynchronous gossip currently runs all peers in one process "
-                                      "(several peers per GPU); use sync rounds for multi-rank runs")
+        if self.world != 1 or self.cfg.async_scheduled:
+            return self.run_async_scheduled()
         cfg = self.cfg
         state = self.comm.alloc("async_state", self.N * self.D).view(self.N, self.D)
         inbox = {}

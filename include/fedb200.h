@@ -173,6 +173,12 @@ int fedb200_fedavg_reduce(const float* const* acc_ptrs, float* const* out_ptrs, 
 int fedb200_peer_barrier(unsigned int* const* flag_ptrs, int rank, int world, unsigned int epoch, int timeout_ms,
                          void* stream);
 
+/* K3 signalling: monotone progress words in peer memory (`flag` may be a peer-mapped pointer for the wait).  The wait
+ * spins on the device with a clock-bounded deadline; on timeout it sets *err (optional) and returns so the stream
+ * never hangs.  Used by the schedule-driven asynchronous gossip executor (fedb200/runtime.py). */
+int fedb200_flag_set(unsigned int* flag, unsigned int value, void* stream);
+int fedb200_flag_wait(const unsigned int* flag, unsigned int value, int timeout_ms, unsigned int* err, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -102,8 +102,35 @@ def main():
     heads = [None] * world
     dist.all_gather_object(heads, rt.ledger.head.hex())
     assert len(set(heads)) == 1, "ledgers diverged across ranks"
+    # ---- asynchronous gossip across GPUs: schedule-driven executor, device-side pub/done flags ---------------------
+    cfg2 = FedConfig(mode="serverless", num_clients=2 * world, num_rounds=3, device="cuda", backend="fused", comm="peer",
+                     asynchronous=True, ledger=True, topology="full")
+    cfg2.model = ModelConfig.preset("bert-mini", num_labels=2)
+    cfg2.data.population, cfg2.data.train_per_client, cfg2.data.test_per_client = 800, 32, 32
+    cfg2.data.max_seq_len, cfg2.data.batch_size = 128, 16
+    cfg2.async_epoch_s, cfg2.async_spread = 0.001, 1.0          # short modelled epochs so versions overlap and slots recycle
+    rt2 = FedRuntime(cfg2, echo=False)
+    rt2.comm.close()
+    rt2.comm = comm
+    rt2.global_flat = comm.alloc("a_global", rt2.D); rt2.global_flat.copy_(rt2.runner.flat)
+    rt2.acc = comm.alloc("a_acc", rt2.D)
+    ares = rt2.run()["last"]
+    torch.cuda.synchronize()
+    comm.check_errors()
+    assert ares["mixes"] == 3 * 2 * world and rt2.ledger.height == ares["mixes"] and rt2.ledger.validate() == -1
+    chk = torch.tensor([float(rt2.global_flat.double().sum())], device=dev, dtype=torch.float64)
+    lo, hi = chk.clone(), chk.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    assert lo.item() == hi.item(), "ranks disagree on the async consensus model"
+    heads = [None] * world
+    dist.all_gather_object(heads, rt2.ledger.head.hex())
+    assert len(set(heads)) == 1, "async ledgers diverged across ranks"
+    # the consensus equals the mean of every peer's final state
+    mine = rt2.async_state[: len(rt2.local_ids)].sum(0)
+    dist.all_reduce(mine)
+    torch.testing.assert_close(rt2.global_flat, mine / (2 * world), rtol=1e-5, atol=1e-6)
     if rank == 0:
-        print("MULTIGPU_OK", world, res["global_accuracies"])
+        print("MULTIGPU_OK", world, res["global_accuracies"], "async slots", ares["outbox_slots"], "mixes", ares["mixes"])
     comm.close()
     dist.destroy_process_group()
 

@@ -143,3 +143,27 @@ rt.close()
     a = [float(x) for x in [l for l in r2.stdout.splitlines() if l.startswith("CHK")][0].split()[1:]]
     b = [float(x) for x in [l for l in r1.stdout.splitlines() if l.startswith("CHK")][0].split()[1:]]
     assert a == pytest.approx(b, rel=1e-5)
+
+
+def test_scheduled_async_executor_matches_schedule_and_ledger():
+    """Schedule-driven async executor (the multi-GPU path) on the loopback backend: every scheduled mix and publish
+    happens once, slots are reused exactly, the ledger records every publish in global order."""
+    from fedb200.p2p import build_async_schedule, model_durations
+    cfg = _cfg(asynchronous=True, async_scheduled=True, num_clients=5, num_rounds=3, ledger=True)
+    rt = FedRuntime(cfg, echo=False)
+    out = rt.run()
+    sched = rt.async_schedule
+    assert out["last"]["mixes"] == 15 == len(sched.events)
+    assert rt.ledger.height == 15 and rt.ledger.validate() == -1
+    assert [b.sender for b in rt.ledger.blocks] == [ev.peer for ev in sched.events]
+    assert out["last"]["async_comm_time"] <= out["last"]["sync_equiv_comm_time"]
+    # schedule invariants: weights sum to one, a slot is only reused after its last consumer
+    for ev in sched.events:
+        assert abs(sum(ev.weights) + ev.self_weight - 1.0) < 1e-12
+        for c_peer, c_epoch in ev.overwrite_waits:
+            c_idx = next(e.index for e in sched.events if e.peer == c_peer and e.epoch == c_epoch)
+            assert c_idx < ev.index
+    again = build_async_schedule(rt.topo, rt.nbytes, 3, model_durations(5, cfg.async_epoch_s, cfg.async_spread, cfg.seed),
+                                 cfg.staleness_decay)
+    assert [(e.peer, e.epoch, e.sources, e.slot) for e in again.events] == [(e.peer, e.epoch, e.sources, e.slot) for e in sched.events]
+    rt.close()
