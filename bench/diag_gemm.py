@@ -40,21 +40,28 @@ def run(layout, M, N, K, splits=1):
 
 
 if __name__ == "__main__":
+    from fedb200.ops import _lib
+    import sys as _sys
+    modes = [int(a) for a in _sys.argv[1:]] or [0]
+    T_list = [16384, 9187]
     for layout in (0, 1, 2):
         for (M, N, K) in [(128, 64, 64), (128, 128, 64), (128, 256, 64), (128, 256, 256), (256, 512, 128), (304, 768, 768)]:
             run(layout, M, N, K, splits=1 if layout != 2 else 2)
-    # timing on BERT-base shapes (tokens = 16384)
-    T = 16384
-    for name, layout, M, N, K, epi, splits in [("fwd qkv", 0, T, 2304, 768, ops.EPI_BIAS, 1), ("fwd ffn-up", 0, T, 3072, 768, ops.EPI_BIAS, 1),
-                                               ("fwd ffn-down", 0, T, 768, 3072, ops.EPI_BIAS, 1), ("dgrad ffn-down", 1, T, 3072, 768, ops.EPI_ADD, 1),
-                                               ("wgrad ffn-up", 2, 3072, 768, T, ops.EPI_ATOMIC_F32, 8), ("wgrad attn-out", 2, 768, 768, T, ops.EPI_ATOMIC_F32, 16)]:
-        shp = {0: ((M, K), (N, K)), 1: ((M, K), (K, N)), 2: ((K, M), (K, N))}[layout]
-        A = torch.randn(*shp[0], device="cuda").bfloat16(); B = torch.randn(*shp[1], device="cuda").bfloat16()
-        out = torch.zeros(M, N, device="cuda", dtype=torch.float32 if layout == 2 else torch.bfloat16)
-        try:
-            ms = cuda_time_ms(lambda: ops.gemm(layout, A, B, out, M, N, K, epi=epi, splits=splits), warmup=3, iters=10)
-            a2, b2 = (A, B.T) if layout == 0 else ((A, B) if layout == 1 else (A.T, B))
-            ms_ref = cuda_time_ms(lambda: torch.matmul(a2, b2), warmup=3, iters=10)
-            print(f"time {name}: {ms:.3f} ms = {2*M*N*K/ms/1e9:.1f} TFLOP/s   (torch.matmul {ms_ref:.3f} ms = {2*M*N*K/ms_ref/1e9:.1f} TFLOP/s)")
-        except Exception as e:
-            print(f"time {name}: EXC {e}")
+    # timing on BERT-base shapes
+    for mode in modes:
+      _lib.lib().fedb200_set_gemm_mode(mode)
+      for T in T_list:
+        print(f"--- gemm mode {mode} (0 auto/pairs, 1 single-CTA), tokens {T}")
+        for name, layout, M, N, K, epi, splits in [("fwd qkv", 0, T, 2304, 768, ops.EPI_BIAS, 1), ("fwd ffn-up", 0, T, 3072, 768, ops.EPI_BIAS, 1),
+                                                   ("fwd ffn-down", 0, T, 768, 3072, ops.EPI_BIAS, 1), ("dgrad ffn-down", 1, T, 3072, 768, ops.EPI_ADD, 1),
+                                                   ("wgrad ffn-up", 2, 3072, 768, T, ops.EPI_ATOMIC_F32, 8), ("wgrad attn-out", 2, 768, 768, T, ops.EPI_ATOMIC_F32, 16)]:
+            shp = {0: ((M, K), (N, K)), 1: ((M, K), (K, N)), 2: ((K, M), (K, N))}[layout]
+            A = torch.randn(*shp[0], device="cuda").bfloat16(); B = torch.randn(*shp[1], device="cuda").bfloat16()
+            out = torch.zeros(M, N, device="cuda", dtype=torch.float32 if layout == 2 else torch.bfloat16)
+            try:
+                ms = cuda_time_ms(lambda: ops.gemm(layout, A, B, out, M, N, K, epi=epi, splits=splits), warmup=3, iters=10)
+                a2, b2 = (A, B.T) if layout == 0 else ((A, B) if layout == 1 else (A.T, B))
+                ms_ref = cuda_time_ms(lambda: torch.matmul(a2, b2), warmup=3, iters=10)
+                print(f"time {name}: {ms:.3f} ms = {2*M*N*K/ms/1e9:.1f} TFLOP/s   (torch.matmul {ms_ref:.3f} ms = {2*M*N*K/ms_ref/1e9:.1f} TFLOP/s)")
+            except Exception as e:
+                print(f"time {name}: EXC {e}")

@@ -15,8 +15,8 @@
 //   dgrad    dx = dy W      A K-major  (dy [M, N']),       B MN-major (W [N', K'] read as [K = N', N = K'])
 //   wgrad    dW = dy^T x    A MN-major (dy [tokens, N']),  B MN-major (x [tokens, K']), split-K over tokens,
 //                           fp32 vector atomics into the gradient arena
-#include "common.cuh"
-#include "../include/fedb200.h"
+#include "gemm_epilogue.cuh"
+#include <stdlib.h>
 
 namespace fedb {
 
@@ -26,50 +26,6 @@ constexpr int GM_STAGES = 4;
 constexpr int GM_EPI_WARPS = 8;            // two warps per TMEM lane quadrant; they interleave the 32-column chunks
 constexpr int GM_THREADS = 64 + GM_EPI_WARPS * 32;
 constexpr int GM_A_BYTES = GM_BM * GM_BK * 2;     // 16 KB
-
-struct GemmParams {
-    int M, N, K;
-    int splits;             // split-K factor (EPI_ATOMIC only)
-    int epi;
-    void* out;              // bf16 [M, ldo] (fp32 for EPI_ATOMIC)
-    void* out2;             // bf16 [M, ldo]: GELU output for EPI_BIAS_GELU
-    int ldo;
-    const float* bias;      // [N] or null
-    const __nv_bfloat16* aux;   // residual / pre-activation, [M, ld_aux]
-    int ld_aux;
-    int act;                // 0 = erf GELU (BERT), 1 = tanh GELU (ALBERT gelu_new)
-    unsigned long long seed;
-    uint32_t keep_thresh;
-    float inv_keep;
-    int use_dropout;
-};
-
-__device__ __forceinline__ void store_bf16x32(__nv_bfloat16* dst, const float (&v)[32], int ncols_valid) {
-    // dst is 16-byte aligned (column offsets are multiples of 32, ldo multiple of 8)
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        if (q * 8 < ncols_valid) {
-            uint4 o;
-            o.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]); o.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
-            o.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]); o.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
-            *reinterpret_cast<uint4*>(dst + q * 8) = o;
-        }
-    }
-}
-__device__ __forceinline__ void load_bf16x32(const __nv_bfloat16* src, float (&v)[32], int ncols_valid) {
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        if (q * 8 < ncols_valid) {
-            const uint4 r = *reinterpret_cast<const uint4*>(src + q * 8);
-            const float2 a = unpack_bf16x2(r.x), b = unpack_bf16x2(r.y), c = unpack_bf16x2(r.z), d = unpack_bf16x2(r.w);
-            v[q * 8 + 0] = a.x; v[q * 8 + 1] = a.y; v[q * 8 + 2] = b.x; v[q * 8 + 3] = b.y;
-            v[q * 8 + 4] = c.x; v[q * 8 + 5] = c.y; v[q * 8 + 6] = d.x; v[q * 8 + 7] = d.y;
-        } else {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) v[q * 8 + k] = 0.f;
-        }
-    }
-}
 
 template <int A_MN, int B_MN, int BN>
 __global__ void __launch_bounds__(GM_THREADS, 1) gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
@@ -173,9 +129,6 @@ __global__ void __launch_bounds__(GM_THREADS, 1) gemm_tcgen05_kernel(const __gri
         // single warp per SM sub-partition the elementwise math (GELU, dropout hash) was latency-bound.
         const int quad = warp & 3;                       // TMEM lane quadrant this warp may read
         const int half = (warp - 2) >> 2;                // 0: even chunks, 1: odd chunks
-        constexpr int N_CHUNKS = BN / 32;
-        const bool needs_aux = p.aux != nullptr && (p.epi == FEDB200_EPI_BIAS_DROP_RES || p.epi == FEDB200_EPI_MUL_GELU_GRAD ||
-                                                    p.epi == FEDB200_EPI_ADD);
         uint32_t local = 0;
         for (int w = blockIdx.x; w < total; w += gridDim.x, ++local) {
             const int tile = w / p.splits;
@@ -184,93 +137,8 @@ __global__ void __launch_bounds__(GM_THREADS, 1) gemm_tcgen05_kernel(const __gri
             const int split = w % p.splits;
             const bool has_k = split * kb_per_split < k_blocks;
             const int row = m_blk * GM_BM + quad * 32 + lane;
-            const bool row_ok = row < p.M;
-            // prefetch the first aux chunk while the accumulator is still being produced
-            uint4 aux_raw[4];
-            auto fetch_aux = [&](int c) {
-                const int col0 = n_blk * BN + c * 32;
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    aux_raw[q] = make_uint4(0u, 0u, 0u, 0u);
-                    if (needs_aux && row_ok && c < N_CHUNKS && col0 + q * 8 < p.N)
-                        aux_raw[q] = __ldg(reinterpret_cast<const uint4*>(p.aux + (size_t)row * p.ld_aux + col0) + q);
-                }
-            };
-            fetch_aux(half);
-            mbar_wait(&acc_full[buf], (local >> 1) & 1u);
-            tc_fence_after_sync();
-#pragma unroll 1
-            for (int c = half; c < N_CHUNKS; c += 2) {
-                const int col0 = n_blk * BN + c * 32;
-                if (col0 >= p.N) break;                  // warp-uniform
-                uint32_t raw[32];
-                tmem_ld_32x32(tmem_base + ((uint32_t)(quad * 32) << 16) + buf * BN + c * 32, raw);
-                float r[32];
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const float2 a0 = unpack_bf16x2(aux_raw[q].x), a1 = unpack_bf16x2(aux_raw[q].y);
-                    const float2 a2 = unpack_bf16x2(aux_raw[q].z), a3 = unpack_bf16x2(aux_raw[q].w);
-                    r[q * 8 + 0] = a0.x; r[q * 8 + 1] = a0.y; r[q * 8 + 2] = a1.x; r[q * 8 + 3] = a1.y;
-                    r[q * 8 + 4] = a2.x; r[q * 8 + 5] = a2.y; r[q * 8 + 6] = a3.x; r[q * 8 + 7] = a3.y;
-                }
-                fetch_aux(c + 2);                        // next chunk's residual / pre-activation is in flight during the math
-                tmem_ld_wait();
-                const int nvalid = min(32, p.N - col0);
-                if (row_ok) {
-                    float v[32];
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = has_k ? __uint_as_float(raw[j]) : 0.f;
-                    if (p.epi == FEDB200_EPI_ATOMIC_F32) {
-                        float* o = reinterpret_cast<float*>(p.out) + (size_t)row * p.ldo + col0;
-#pragma unroll
-                        for (int q = 0; q < 8; ++q)
-                            if (q * 4 < nvalid)
-                                atomicAdd(reinterpret_cast<float4*>(o + q * 4),
-                                          make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]));
-                    } else {
-                        if (p.bias != nullptr) {
-#pragma unroll
-                            for (int q = 0; q < 8; ++q) {
-                                if (q * 4 < nvalid) {
-                                    const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0) + q);
-                                    v[q * 4] += b4.x; v[q * 4 + 1] += b4.y; v[q * 4 + 2] += b4.z; v[q * 4 + 3] += b4.w;
-                                }
-                            }
-                        }
-                        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.ldo + col0;
-                        if (p.epi == FEDB200_EPI_BIAS) {
-                            store_bf16x32(o, v, nvalid);
-                        } else if (p.epi == FEDB200_EPI_BIAS_DROP_RES) {
-                            if (p.use_dropout) {
-#pragma unroll
-                                for (int q = 0; q < 4; ++q)
-                                    dropout_apply8(v + q * 8, p.seed, (uint32_t)row, (uint32_t)(col0 + q * 8), p.keep_thresh, p.inv_keep);
-                            }
-#pragma unroll
-                            for (int j = 0; j < 32; ++j) v[j] += r[j];
-                            store_bf16x32(o, v, nvalid);
-                        } else if (p.epi == FEDB200_EPI_BIAS_GELU) {
-                            store_bf16x32(o, v, nvalid);
-                            // activate the bf16-rounded pre-activation so backward (which re-reads it) is consistent
-#pragma unroll
-                            for (int j = 0; j < 32; ++j) {
-                                const float u = __bfloat162float(__float2bfloat16_rn(v[j]));
-                                v[j] = p.act ? gelu_tanh(u) : gelu_erf(u);
-                            }
-                            store_bf16x32(reinterpret_cast<__nv_bfloat16*>(p.out2) + (size_t)row * p.ldo + col0, v, nvalid);
-                        } else if (p.epi == FEDB200_EPI_MUL_GELU_GRAD) {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j) v[j] *= p.act ? gelu_tanh_grad(r[j]) : gelu_erf_grad(r[j]);
-                            store_bf16x32(o, v, nvalid);
-                        } else {    // FEDB200_EPI_ADD
-#pragma unroll
-                            for (int j = 0; j < 32; ++j) v[j] += r[j];       // r is zero when there is no aux
-                            store_bf16x32(o, v, nvalid);
-                        }
-                    }
-                }
-                __syncwarp();
-            }
+            gemm_epilogue_tile<BN>(p, tmem_base + ((uint32_t)(quad * 32) << 16) + buf * BN, row, n_blk * BN, half, has_k,
+                                   &acc_full[buf], (local >> 1) & 1u);
             tc_fence_before_sync();
             __syncwarp();
             if (lane == 0) mbar_arrive(&acc_empty[buf]);
@@ -301,9 +169,27 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
     return 0;
 }
 
+int gemm2_dispatch(int layout, const void* A, int lda, const void* B, int ldb, const GemmParams& p, int BN, int max_ctas,
+                   cudaStream_t s);      // gemm2_tcgen05.cu
+
 }  // namespace fedb
 
 using namespace fedb;
+
+// 0 = auto (CTA pairs whenever the shape allows), 1 = force the 1-CTA kernel, 2 = force pairs.  Also settable through
+// the FEDB200_GEMM_MODE environment variable (read once); used by the A/B benchmark in bench/diag_gemm.py.
+static int g_gemm_mode = -1;
+extern "C" int fedb200_set_gemm_mode(int mode) {
+    g_gemm_mode = mode;
+    return 0;
+}
+static int gemm_mode() {
+    if (g_gemm_mode < 0) {
+        const char* e = getenv("FEDB200_GEMM_MODE");
+        g_gemm_mode = e ? atoi(e) : 0;
+    }
+    return g_gemm_mode;
+}
 
 // layout: 0 = NT (A [M,K] K-major, B [N,K] K-major)           forward
 //         1 = NN (A [M,K] K-major, B [K,N] row-major)          dgrad
@@ -329,6 +215,16 @@ extern "C" int fedb200_gemm_bf16(int layout, const void* A, int lda, const void*
 
     const int BN = N >= 256 ? 256 : (N >= 128 ? 128 : 64);
     const int a_mn = layout == 2, b_mn = layout != 0;
+    if (BN >= 128 && gemm_mode() != 1) {
+        // CTA-pair kernel: 256 x BN tile per two SMs, each SM loads half of B
+        GemmParams pp;
+        pp.M = M; pp.N = N; pp.K = K; pp.splits = splits; pp.epi = epi; pp.out = out; pp.out2 = out2; pp.ldo = ldo;
+        pp.bias = bias; pp.aux = (const __nv_bfloat16*)aux; pp.ld_aux = ld_aux; pp.act = act; pp.seed = seed;
+        pp.keep_thresh = dropout_thresh16(dropout_p);
+        pp.inv_keep = 1.0f / (1.0f - dropout_p);
+        pp.use_dropout = dropout_p > 0.f;
+        return gemm2_dispatch(layout, A, lda, B, ldb, pp, BN, max_ctas, (cudaStream_t)stream);
+    }
     CUtensorMap ta, tb;
     int e;
     if (!a_mn) e = make_tmap_bf16_2d(&ta, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, GM_BM, GM_BK);

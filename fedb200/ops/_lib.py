@@ -26,6 +26,7 @@ _PROTOS = {
     "fedb200_delta_bf16": (i32, [vp, vp, vp, sz, vp]),
     "fedb200_gemm_bf16": (i32, [i32, vp, i32, vp, i32, i32, i32, i32, i32, vp, vp, i32, vp, vp, i32, i32, u64, f32,
                                 i32, i32, vp]),
+    "fedb200_set_gemm_mode": (i32, [i32]),
     "fedb200_layernorm_fwd": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, f32, vp]),
     "fedb200_layernorm_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, u64, f32, vp]),
     "fedb200_embed_fwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, f32, u64, f32, vp]),

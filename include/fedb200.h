@@ -51,6 +51,8 @@ int fedb200_delta_bf16(const float* a, const float* b, void* out, size_t n, void
 int fedb200_gemm_bf16(int layout, const void* A, int lda, const void* B, int ldb, int M, int N, int K, int epi,
                       void* out, void* out2, int ldo, const float* bias, const void* aux, int ld_aux, int act,
                       unsigned long long seed, float dropout_p, int splits, int max_ctas, void* stream);
+/* GEMM kernel selection: 0 auto (CTA pairs, cta_group::2, when N >= 128), 1 force the 1-CTA kernel, 2 force pairs. */
+int fedb200_set_gemm_mode(int mode);
 /* K10. LayerNorm over bf16 rows (eps 1e-12 in BERT). bwd also emits dgamma/dbeta and the producing layer's dbias. */
 int fedb200_layernorm_fwd(const void* z, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
                           int T, int H, float eps, void* stream);
