@@ -62,7 +62,7 @@ extern "C" int fedb200_bert_forward(const fedb200_bert_plan* p, int T, int B, in
         FEDB_TRY(fedb200_gemm_bf16(0, a.ctx, H, a.wo, H, T, H, H, FEDB200_EPI_BIAS_DROP_RES, a.z1, nullptr, H, a.bo, a.x_in,
                                    H, p->act, op_seed(step_seed, l, 2), ph, 1, 0, stream));
         FEDB_TRY(fedb200_layernorm_fwd(a.z1, a.ln1w, a.ln1b, a.a1, a.mean1, a.rstd1, T, H, p->ln_eps, stream));
-        FEDB_TRY(fedb200_gemm_bf16(0, a.a1, H, a.w1, H, T, I, H, FEDB200_EPI_BIAS_GELU, a.u, a.g, I, a.b1, nullptr, 0, p->act, 0,
+        FEDB_TRY(fedb200_gemm_bf16(0, a.a1, H, a.w1, H, T, I, H, FEDB200_EPI_BIAS_GELU, train ? a.u : nullptr, a.g, I, a.b1, nullptr, 0, p->act, 0,
                                    0.f, 1, 0, stream));
         FEDB_TRY(fedb200_gemm_bf16(0, a.g, I, a.w2, I, T, H, I, FEDB200_EPI_BIAS_DROP_RES, a.z2, nullptr, H, a.b2, a.a1, H,
                                    p->act, op_seed(step_seed, l, 3), ph, 1, 0, stream));

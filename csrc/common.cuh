@@ -102,27 +102,27 @@ __host__ __device__ inline uint32_t dropout_thresh16(float p) {
     return keep >= 1.0f ? 65536u : (uint32_t)(keep * 65536.0f + 0.5f);
 }
 
-// erf-form GELU (BERT) and its derivative from ONE exponential: with u = |x| / sqrt(2),
-//   erf(u) = 1 - t (a1 + t (a2 + t (a3 + t (a4 + t a5)))) exp(-u^2),  t = 1 / (1 + p u)     (Abramowitz-Stegun 7.1.26,
-// |error| <= 1.5e-7), and exp(-u^2) = exp(-x^2 / 2) is also the Gaussian density the derivative needs.
-// ~14 instructions instead of erff + expf; the epilogue warps of the FFN GEMMs are latency-bound on this.
-__device__ __forceinline__ void gelu_erf_parts(float x, float& cdf, float& e) {
-    const float u = fabsf(x) * 0.70710678118654752f;
-    const float t = __frcp_rn(fmaf(0.3275911f, u, 1.0f));
-    e = __expf(-u * u);
-    const float poly = t * fmaf(t, fmaf(t, fmaf(t, fmaf(t, 1.061405429f, -1.453152027f), 1.421413741f), -0.284496736f), 0.254829592f);
-    const float half_erf = 0.5f - 0.5f * poly * e;           // erf(u) / 2
-    cdf = x >= 0.f ? 0.5f + half_erf : 0.5f - half_erf;
+// erf-form GELU (BERT): gelu(x) = x * Phi(x).  The Gaussian CDF is evaluated as
+//   Phi(x) = 0.5 + 0.5 * tanh(x * (c0 + c1 x^2 + c2 x^4)),   |x| clamped to 8,
+// a least-squares fit of atanh(erf(x / sqrt 2)) (bench/fit_gelu.py): max |Phi error| 3.7e-5, max |gelu error| 3.0e-5 —
+// two orders of magnitude below bf16 resolution, so the result rounds like the exact erf form.  With the hardware
+// tanh (MUFU.TANH) this is 9 instructions; erff + expf cost ~3x more and made the FFN GEMM epilogues ALU-bound
+// (profiles/).  NOT the "gelu_new" approximation (that one is gelu_tanh below, ALBERT's activation).
+__device__ __forceinline__ float tanh_fast(float x) {
+    float y;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
 }
-__device__ __forceinline__ float gelu_erf(float x) {
-    float cdf, e;
-    gelu_erf_parts(x, cdf, e);
-    return x * cdf;
+__device__ __forceinline__ float gauss_cdf(float x) {
+    const float xc = fminf(fmaxf(x, -8.0f), 8.0f);
+    const float x2 = xc * xc;
+    const float p = fmaf(x2, fmaf(x2, -0.0003438328493771962f, 0.03694645550401846f), 0.7975903260635063f);
+    return fmaf(0.5f, tanh_fast(xc * p), 0.5f);
 }
+__device__ __forceinline__ float gelu_erf(float x) { return x * gauss_cdf(x); }
 __device__ __forceinline__ float gelu_erf_grad(float x) {
-    float cdf, e;
-    gelu_erf_parts(x, cdf, e);
-    return fmaf(x * 0.39894228040143268f, e, cdf);
+    // Phi(x) + x * phi(x),  phi(x) = exp(-x^2 / 2) / sqrt(2 pi)
+    return fmaf(x * 0.39894228040143268f, exp2f(-0.72134752044448170f * x * x), gauss_cdf(x));
 }
 __device__ __forceinline__ float gelu_tanh(float x) {
     const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);

@@ -60,10 +60,14 @@ __device__ __forceinline__ void gemm_epilogue_tile(const GemmParams& p, uint32_t
     const bool needs_aux = p.aux != nullptr && (p.epi == FEDB200_EPI_BIAS_DROP_RES || p.epi == FEDB200_EPI_MUL_GELU_GRAD ||
                                                 p.epi == FEDB200_EPI_ADD);
     const bool row_ok = row < p.M;
-    // prefetch the first aux chunk while the accumulator is still being produced
+    // prefetch the first aux chunk (and the chunk's bias: one coalesced 128-byte load per warp, later broadcast with
+    // shuffles) while the accumulator is still being produced
+    const int lane_id = threadIdx.x & 31;
     uint4 aux_raw[4];
+    float bias_lane = 0.f;
     auto fetch_aux = [&](int c) {
         const int col0 = col_base + c * 32;
+        bias_lane = (p.bias != nullptr && c < N_CHUNKS && col0 + lane_id < p.N) ? __ldg(p.bias + col0 + lane_id) : 0.f;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
             aux_raw[q] = make_uint4(0u, 0u, 0u, 0u);
@@ -88,13 +92,17 @@ __device__ __forceinline__ void gemm_epilogue_tile(const GemmParams& p, uint32_t
             r[q * 8 + 0] = a0.x; r[q * 8 + 1] = a0.y; r[q * 8 + 2] = a1.x; r[q * 8 + 3] = a1.y;
             r[q * 8 + 4] = a2.x; r[q * 8 + 5] = a2.y; r[q * 8 + 6] = a3.x; r[q * 8 + 7] = a3.y;
         }
+        const float bias_cur = bias_lane;
         fetch_aux(c + 2);                        // next chunk's residual / pre-activation is in flight during the math
         tmem_ld_wait();
+        float bv[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) bv[j] = p.bias != nullptr ? __shfl_sync(0xffffffffu, bias_cur, j) : 0.f;
         const int nvalid = min(32, p.N - col0);
         if (row_ok) {
             float v[32];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = has_k ? __uint_as_float(raw[j]) : 0.f;
+            for (int j = 0; j < 32; ++j) v[j] = (has_k ? __uint_as_float(raw[j]) : 0.f) + bv[j];
             if (p.epi == FEDB200_EPI_ATOMIC_F32) {
                 float* o = reinterpret_cast<float*>(p.out) + (size_t)row * p.ldo + col0;
 #pragma unroll
@@ -103,15 +111,6 @@ __device__ __forceinline__ void gemm_epilogue_tile(const GemmParams& p, uint32_t
                         atomicAdd(reinterpret_cast<float4*>(o + q * 4),
                                   make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]));
             } else {
-                if (p.bias != nullptr) {
-#pragma unroll
-                    for (int q = 0; q < 8; ++q) {
-                        if (q * 4 < nvalid) {
-                            const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0) + q);
-                            v[q * 4] += b4.x; v[q * 4 + 1] += b4.y; v[q * 4 + 2] += b4.z; v[q * 4 + 3] += b4.w;
-                        }
-                    }
-                }
                 __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.ldo + col0;
                 if (p.epi == FEDB200_EPI_BIAS) {
                     store_bf16x32(o, v, nvalid);
@@ -125,7 +124,7 @@ __device__ __forceinline__ void gemm_epilogue_tile(const GemmParams& p, uint32_t
                     for (int j = 0; j < 32; ++j) v[j] += r[j];
                     store_bf16x32(o, v, nvalid);
                 } else if (p.epi == FEDB200_EPI_BIAS_GELU) {
-                    store_bf16x32(o, v, nvalid);
+                    if (p.out != nullptr) store_bf16x32(o, v, nvalid);      // inference keeps only the activated output
                     // activate the bf16-rounded pre-activation so backward (which re-reads it) is consistent
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
