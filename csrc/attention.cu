@@ -5,7 +5,7 @@
 // token range, so the padding mask of the reference becomes "kv index < sequence length".
 //
 // forward, one CTA per (128-row q tile, head, sequence); 192 threads:
-//   warp 0 TMA   : Q tile once, then K_j / V_j tiles (2-deep ring)
+//   warp 0 TMA   : Q tile once, then K_j / V_j tiles (single stage each; two CTAs per SM overlap instead)
 //   warp 1 MMA   : S = Q K_j^T  (M128 N128 K64, both K-major) -> TMEM;  O_j = P_j V_j (A = P from smem,
 //                  B = V tile read MN-major, so V is never transposed)
 //   warps 2-5    : (two CTAs per SM) one thread per q row: two passes over S in TMEM (row max, then exp2 / row sum / dropout),
@@ -16,7 +16,9 @@
 //   K-major for dK += dS^T Q_i and MN-major for dQ_i = dS K (no transposes anywhere).  dV/dK accumulate in
 //   TMEM across the q loop; dQ tiles are reduced across kv CTAs with fp32 vector atomics into `dq_accum`
 //   (scratch, [T, H] fp32, must be zero on entry; the finishing kernel converts it to bf16 and re-zeroes it).
-// Dropout uses the library-wide counter RNG: row = head * T + q token, col = kv position in the sequence.
+// Dropout uses the library-wide counter RNG: row = head * T + q token, col = kv position in the sequence.  The forward
+// can also store its keep decisions as bit words ([heads, T, ceil(max_seqlen/32)] uint32); given those, the backward
+// reads one word per q row instead of re-hashing every element (13 -> 4 instructions per element).
 // lse is stored in base-2 units of the scaled scores: lse2 = max2 + log2(sum), p = exp2(s*scale*log2e - lse2).
 #include "common.cuh"
 #include "../include/fedb200.h"
@@ -49,7 +51,8 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attn_fwd_kernel(const __grid_co
                                                                  __nv_bfloat16* __restrict__ ctx, float* __restrict__ lse,
                                                                  const int* __restrict__ cu_seqlens, int T, int H,
                                                                  float scale_log2, uint64_t seed, uint32_t keep_thresh,
-                                                                 float inv_keep, int use_dropout) {
+                                                                 float inv_keep, int use_dropout,
+                                                                 uint32_t* __restrict__ drop_bits, int bits_stride) {
     const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * 128;
     const int tok0 = cu_seqlens[b], len = cu_seqlens[b + 1] - tok0;
     if (q0 >= len) return;
@@ -132,6 +135,7 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attn_fwd_kernel(const __grid_co
         const int q_tok = tok0 + q0 + r;
         const bool q_ok = q0 + r < len;
         const uint32_t drop_row = (uint32_t)(h * T + q_tok);
+        const uint32_t drop_key = dropout_key(seed);
         float o[64];
 #pragma unroll
         for (int d = 0; d < 64; ++d) o[d] = 0.f;
@@ -169,9 +173,12 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attn_fwd_kernel(const __grid_co
                 }
                 l_run += rs;
                 if (use_dropout) {
+                    // 32 keep decisions of this row as one word; the backward re-reads the word instead of re-hashing
+                    const uint32_t bits = dropout_bits32(drop_key, drop_row, (uint32_t)(j * 128 + c * 32), keep_thresh);
+                    if (drop_bits != nullptr && q_ok && j * 4 + c < bits_stride)      // chunks past max_seqlen are fully masked
+                        drop_bits[((size_t)h * T + q_tok) * bits_stride + j * 4 + c] = bits;
 #pragma unroll
-                    for (int g = 0; g < 4; ++g)
-                        dropout_apply8(p + g * 8, seed, drop_row, (uint32_t)(j * 128 + c * 32 + g * 8), keep_thresh, inv_keep);
+                    for (int i = 0; i < 32; ++i) p[i] = (bits >> i) & 1u ? p[i] * inv_keep : 0.f;
                 }
                 uint8_t* tile = sP + (c >> 1) * AT_TILE;
 #pragma unroll
@@ -273,7 +280,9 @@ __global__ void __launch_bounds__(256) attn_bwd_finish_kernel(float* __restrict_
     }
 }
 
-constexpr int ATB_THREADS = 320;          // warp 0 TMA, warp 1 MMA, warps 2-9 compute (two per TMEM lane quadrant)
+constexpr int ATB_CWARPS = 16;            // compute warps: four per TMEM lane quadrant, 32 q-columns each
+constexpr int ATB_CTHREADS = ATB_CWARPS * 32;
+constexpr int ATB_THREADS = 64 + ATB_CTHREADS;   // warp 0 TMA, warp 1 MMA, warps 2-17 compute
 
 __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv,
                                                                  const __grid_constant__ CUtensorMap tm_do,
@@ -281,7 +290,8 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
                                                                  __nv_bfloat16* __restrict__ dqkv, float* __restrict__ dq_accum,
                                                                  const int* __restrict__ cu_seqlens, int T, int H,
                                                                  float scale, float scale_log2, uint64_t seed,
-                                                                 uint32_t keep_thresh, float inv_keep, int use_dropout) {
+                                                                 uint32_t keep_thresh, float inv_keep, int use_dropout,
+                                                                 const uint32_t* __restrict__ drop_bits, int bits_stride) {
     const int b = blockIdx.z, h = blockIdx.y, kv0 = blockIdx.x * 128;
     const int tok0 = cu_seqlens[b], len = cu_seqlens[b + 1] - tok0;
     if (kv0 >= len) return;
@@ -305,7 +315,7 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
         tma_prefetch_desc(&tm_do);
         mbar_init(&kv_full, 1);
         for (int s = 0; s < 2; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_empty[s], 1); }
-        mbar_init(&sdp_full, 1); mbar_init(&pds_ready, 256); mbar_init(&dq_full, 1); mbar_init(&dq_empty, 256);
+        mbar_init(&sdp_full, 1); mbar_init(&pds_ready, ATB_CTHREADS); mbar_init(&dq_full, 1); mbar_init(&dq_empty, ATB_CTHREADS);
         mbar_init(&dkv_full, 1);
         mbar_fence_init();
     }
@@ -365,70 +375,84 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
             umma_commit(&dkv_full);
         }
     } else {
-        // Eight compute warps: warps w and w+4 share a TMEM lane quadrant (rows) and split the 128 columns of
-        // S^T / dP^T in halves, which are exactly the two 64-column smem tiles of Pd^T / dS^T.
+        // Sixteen compute warps: the four warps of a TMEM lane quadrant (rows) take one 32-column group of
+        // S^T / dP^T each; column groups 0-1 / 2-3 are the two 64-column smem tiles of Pd^T / dS^T.
         const int quad = warp & 3;
-        const int half = (warp - 2) >> 2;                     // 0: q columns 0-63, 1: q columns 64-127
+        const int cg = (warp - 2) >> 2;                       // q-column group 0..3
         const int r = quad * 32 + lane;                       // kv row for S^T/dP^T/dK/dV, q row for dQ
-        const int t256 = (warp - 2) * 32 + lane;
+        const int tid = (warp - 2) * 32 + lane;               // 0..511
         const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
         const int kv = kv0 + r;
         const bool kv_ok = kv < len;
         const uint32_t drop_col = dropout_key(seed) ^ (((uint32_t)kv >> 1) * 0x85EBCA77U);
         const uint32_t drop_lane = (uint32_t)kv & 1u;
         const uint32_t drop_row0 = (uint32_t)(h * T + tok0);
-        uint8_t* tp = sP + half * AT_TILE;
-        uint8_t* td = sdS + half * AT_TILE;
+        const int kv_chunk = kv >> 5;                         // warp-uniform (kv0 and quad*32 are multiples of 32)
+        uint8_t* tp = sP + (cg >> 1) * AT_TILE;
+        uint8_t* td = sdS + (cg >> 1) * AT_TILE;
         for (int i = 0; i < n_q; ++i) {
             const int qb = i * 128, sl = i & 1;
             {   // stage lse / delta of this q tile (double-buffered by i parity; published by the named barrier)
-                const int q = qb + (t256 & 127);
-                if (t256 < 128) s_lse[sl][t256] = q < len ? lse[(size_t)h * T + tok0 + q] : 0.f;
-                else            s_delta[sl][t256 - 128] = q < len ? delta[(size_t)h * T + tok0 + q] : 0.f;
+                const int q = qb + (tid & 127);
+                if (tid < 128) s_lse[sl][tid] = q < len ? lse[(size_t)h * T + tok0 + q] : 0.f;
+                else if (tid < 256) s_delta[sl][tid - 128] = q < len ? delta[(size_t)h * T + tok0 + q] : 0.f;
             }
-            asm volatile("bar.sync 1, 256;" ::: "memory");
+            // keep-bits of this warp's 32 q rows for its kv chunk: lane l holds the word of q = qb + cg*32 + l
+            uint32_t my_bits = 0xFFFFFFFFu;
+            if (use_dropout && drop_bits != nullptr) {
+                const int q = qb + cg * 32 + lane;
+                if (q < len && kv_chunk < bits_stride) my_bits = __ldg(drop_bits + ((size_t)h * T + tok0 + q) * bits_stride + kv_chunk);
+            }
+            asm volatile("bar.sync 1, 512;" ::: "memory");
             mbar_wait(&sdp_full, (uint32_t)i & 1u);
             tc_fence_after_sync();
+            const bool full_tile = kv0 + 128 <= len && qb + 128 <= len;       // no masking needed (block-uniform)
 #pragma unroll 1
-            for (int cc = 0; cc < 2; ++cc) {
-                const int c = half * 2 + cc;
-                uint32_t rs[32], rp[32];
-                tmem_ld_32x32(tm_st + lane_addr + c * 32, rs);
-                tmem_ld_32x32(tm_dpt + lane_addr + c * 32, rp);
+            for (int hc = 0; hc < 2; ++hc) {                                   // two 16-column halves of the group
+                const int c0 = cg * 32 + hc * 16;
+                uint32_t rs[16], rp[16];
+                tmem_ld_32x16(tm_st + lane_addr + c0, rs);
+                tmem_ld_32x16(tm_dpt + lane_addr + c0, rp);
                 tmem_ld_wait();
-                float pd[32], ds[32];
+                float pd[16], ds[16];
 #pragma unroll
-                for (int jq = 0; jq < 32; ++jq) {
-                    const int ql = c * 32 + jq, q = qb + ql;
-                    const bool ok = kv_ok && q < len;
-                    const float p = ok ? exp2f(__uint_as_float(rs[jq]) * scale_log2 - s_lse[sl][ql]) : 0.f;
+                for (int jq = 0; jq < 16; ++jq) {
+                    const int ql = c0 + jq, q = qb + ql;
+                    float p = exp2f(__uint_as_float(rs[jq]) * scale_log2 - s_lse[sl][ql]);
+                    if (!full_tile) p = (kv_ok && q < len) ? p : 0.f;
                     float mk = 1.f;
-                    if (use_dropout)
-                        mk = dropout_lane(hash32(drop_col ^ ((drop_row0 + (uint32_t)q) * 0x9E3779B1U)), drop_lane, keep_thresh, inv_keep);
+                    if (use_dropout) {
+                        if (drop_bits != nullptr) {
+                            const uint32_t w = __shfl_sync(0xffffffffu, my_bits, hc * 16 + jq);
+                            mk = (w >> lane) & 1u ? inv_keep : 0.f;
+                        } else {
+                            mk = dropout_lane(hash32(drop_col ^ ((drop_row0 + (uint32_t)q) * 0x9E3779B1U)), drop_lane, keep_thresh, inv_keep);
+                        }
+                    }
                     pd[jq] = p * mk;
                     ds[jq] = p * (__uint_as_float(rp[jq]) * mk - s_delta[sl][ql]) * scale;
                 }
 #pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                    st_swizzled_chunk(tp, r, cc * 4 + g, pd + g * 8);
-                    st_swizzled_chunk(td, r, cc * 4 + g, ds + g * 8);
+                for (int g = 0; g < 2; ++g) {
+                    st_swizzled_chunk(tp, r, (cg & 1) * 4 + hc * 2 + g, pd + g * 8);
+                    st_swizzled_chunk(td, r, (cg & 1) * 4 + hc * 2 + g, ds + g * 8);
                 }
             }
             fence_async_smem();
             tc_fence_before_sync();
             mbar_arrive(&pds_ready);
-            // dQ tile: lanes are q rows now; each half drains 32 of the 64 head-dim columns
+            // dQ tile: lanes are q rows now; each column group drains 16 of the 64 head-dim columns
             mbar_wait(&dq_full, (uint32_t)i & 1u);
             tc_fence_after_sync();
             const int q = qb + r;
             {
-                uint32_t raw[32];
-                tmem_ld_32x32(tm_dq + lane_addr + half * 32, raw);
+                uint32_t raw[16];
+                tmem_ld_32x16(tm_dq + lane_addr + cg * 16, raw);
                 tmem_ld_wait();
                 if (q < len) {
-                    float* dst = dq_accum + (size_t)(tok0 + q) * H + h * 64 + half * 32;
+                    float* dst = dq_accum + (size_t)(tok0 + q) * H + h * 64 + cg * 16;
 #pragma unroll
-                    for (int g = 0; g < 8; ++g)
+                    for (int g = 0; g < 4; ++g)
                         atomicAdd(reinterpret_cast<float4*>(dst + g * 4),
                                   make_float4(__uint_as_float(raw[g * 4]), __uint_as_float(raw[g * 4 + 1]),
                                               __uint_as_float(raw[g * 4 + 2]), __uint_as_float(raw[g * 4 + 3])));
@@ -439,24 +463,21 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
         }
         mbar_wait(&dkv_full, 0);
         tc_fence_after_sync();
-        {   // half 0 writes dK into the K block of dqkv, half 1 writes dV into the V block
-            const int which = half;
+        {   // column groups 0-1 write dK (32 columns each) into the K block of dqkv, groups 2-3 write dV
+            const int which = cg >> 1, c = cg & 1;
+            uint32_t raw[32];
+            tmem_ld_32x32((which ? tm_dv : tm_dk) + lane_addr + c * 32, raw);
+            tmem_ld_wait();
+            if (kv_ok) {
+                __nv_bfloat16* dst = dqkv + (size_t)(tok0 + kv) * 3 * H + (which ? 2 * H : H) + h * 64 + c * 32;
 #pragma unroll
-            for (int c = 0; c < 2; ++c) {
-                uint32_t raw[32];
-                tmem_ld_32x32((which ? tm_dv : tm_dk) + lane_addr + c * 32, raw);
-                tmem_ld_wait();
-                if (kv_ok) {
-                    __nv_bfloat16* dst = dqkv + (size_t)(tok0 + kv) * 3 * H + (which ? 2 * H : H) + h * 64 + c * 32;
-#pragma unroll
-                    for (int g = 0; g < 4; ++g) {
-                        uint4 pk;
-                        pk.x = pack_bf16x2(__uint_as_float(raw[g * 8 + 0]), __uint_as_float(raw[g * 8 + 1]));
-                        pk.y = pack_bf16x2(__uint_as_float(raw[g * 8 + 2]), __uint_as_float(raw[g * 8 + 3]));
-                        pk.z = pack_bf16x2(__uint_as_float(raw[g * 8 + 4]), __uint_as_float(raw[g * 8 + 5]));
-                        pk.w = pack_bf16x2(__uint_as_float(raw[g * 8 + 6]), __uint_as_float(raw[g * 8 + 7]));
-                        *reinterpret_cast<uint4*>(dst + g * 8) = pk;
-                    }
+                for (int g = 0; g < 4; ++g) {
+                    uint4 pk;
+                    pk.x = pack_bf16x2(__uint_as_float(raw[g * 8 + 0]), __uint_as_float(raw[g * 8 + 1]));
+                    pk.y = pack_bf16x2(__uint_as_float(raw[g * 8 + 2]), __uint_as_float(raw[g * 8 + 3]));
+                    pk.z = pack_bf16x2(__uint_as_float(raw[g * 8 + 4]), __uint_as_float(raw[g * 8 + 5]));
+                    pk.w = pack_bf16x2(__uint_as_float(raw[g * 8 + 6]), __uint_as_float(raw[g * 8 + 7]));
+                    *reinterpret_cast<uint4*>(dst + g * 8) = pk;
                 }
             }
         }
@@ -471,7 +492,8 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
 using namespace fedb;
 
 extern "C" int fedb200_attn_fwd(const void* qkv, void* ctx, float* lse, const int* cu_seqlens, int B, int T, int heads,
-                                int max_seqlen, float scale, unsigned long long seed, float dropout_p, void* stream) {
+                                int max_seqlen, float scale, unsigned long long seed, float dropout_p, void* drop_bits,
+                                void* stream) {
     FEDB_REQUIRE(B > 0 && T > 0 && heads > 0 && max_seqlen > 0, "attn_fwd: empty problem");
     const int H = heads * 64;
     CUtensorMap tm;
@@ -486,7 +508,7 @@ extern "C" int fedb200_attn_fwd(const void* qkv, void* ctx, float* lse, const in
     dim3 grid((max_seqlen + 127) / 128, heads, B);
     attn_fwd_kernel<<<grid, AT_THREADS, smem, (cudaStream_t)stream>>>(
         tm, (__nv_bfloat16*)ctx, lse, cu_seqlens, T, H, scale * LOG2E, seed, dropout_thresh16(dropout_p),
-        1.0f / (1.0f - dropout_p), dropout_p > 0.f);
+        1.0f / (1.0f - dropout_p), dropout_p > 0.f, (uint32_t*)drop_bits, (max_seqlen + 31) / 32);
     FEDB_LAUNCH_CHECK();
     return 0;
 }
@@ -494,7 +516,7 @@ extern "C" int fedb200_attn_fwd(const void* qkv, void* ctx, float* lse, const in
 extern "C" int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dctx, const float* lse, float* delta,
                                 void* dqkv, float* dq_accum, float* dbias_qkv, const int* cu_seqlens, int B, int T,
                                 int heads, int max_seqlen, float scale, unsigned long long seed, float dropout_p,
-                                void* stream) {
+                                const void* drop_bits, void* stream) {
     FEDB_REQUIRE(B > 0 && T > 0 && heads > 0 && max_seqlen > 0, "attn_bwd: empty problem");
     const int H = heads * 64;
     cudaStream_t s = (cudaStream_t)stream;
@@ -514,7 +536,8 @@ extern "C" int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dc
     dim3 grid((max_seqlen + 127) / 128, heads, B);
     attn_bwd_kernel<<<grid, ATB_THREADS, smem, s>>>(tm, tmdo, lse, delta, (__nv_bfloat16*)dqkv, dq_accum, cu_seqlens, T, H,
                                                    scale, scale * LOG2E, seed, dropout_thresh16(dropout_p),
-                                                   1.0f / (1.0f - dropout_p), dropout_p > 0.f);
+                                                   1.0f / (1.0f - dropout_p), dropout_p > 0.f, (const uint32_t*)drop_bits,
+                                                   (max_seqlen + 31) / 32);
     FEDB_LAUNCH_CHECK();
     {
         const int col_blocks = (3 * H + 63) / 64;

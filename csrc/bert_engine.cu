@@ -58,7 +58,7 @@ extern "C" int fedb200_bert_forward(const fedb200_bert_plan* p, int T, int B, in
         FEDB_TRY(fedb200_gemm_bf16(0, a.x_in, H, a.wqkv, H, T, 3 * H, H, FEDB200_EPI_BIAS, a.qkv, nullptr, 3 * H, a.bqkv,
                                    nullptr, 0, p->act, 0, 0.f, 1, 0, stream));
         FEDB_TRY(fedb200_attn_fwd(a.qkv, a.ctx, a.lse, p->cu_seqlens, B, T, p->heads, max_len, scale, op_seed(step_seed, l, 1),
-                                  pa, stream));
+                                  pa, train ? a.drop_bits : nullptr, stream));
         FEDB_TRY(fedb200_gemm_bf16(0, a.ctx, H, a.wo, H, T, H, H, FEDB200_EPI_BIAS_DROP_RES, a.z1, nullptr, H, a.bo, a.x_in,
                                    H, p->act, op_seed(step_seed, l, 2), ph, 1, 0, stream));
         FEDB_TRY(fedb200_layernorm_fwd(a.z1, a.ln1w, a.ln1b, a.a1, a.mean1, a.rstd1, T, H, p->ln_eps, stream));
@@ -110,7 +110,7 @@ extern "C" int fedb200_bert_backward(const fedb200_bert_plan* p, int T, int B, i
         FEDB_TRY(fedb200_gemm_bf16(2, df, H, a.ctx, H, H, H, T, FEDB200_EPI_ATOMIC_F32, a.g_wo, nullptr, H, nullptr, nullptr, 0,
                                    p->act, 0, 0.f, wgrad_splits(H, H, T, sms), 0, stream));
         FEDB_TRY(fedb200_attn_bwd(a.qkv, a.ctx, p->dctx, a.lse, p->delta, p->dqkv, p->dq_accum, a.g_bqkv, p->cu_seqlens, B, T,
-                                  p->heads, max_len, scale, op_seed(step_seed, l, 1), pa, stream));
+                                  p->heads, max_len, scale, op_seed(step_seed, l, 1), pa, a.drop_bits, stream));
         FEDB_TRY(fedb200_gemm_bf16(1, p->dqkv, 3 * H, a.wqkv, H, T, H, 3 * H, FEDB200_EPI_ADD, p->dx, nullptr, H, nullptr, p->dzb,
                                    H, p->act, 0, 0.f, 1, 0, stream));
         FEDB_TRY(fedb200_gemm_bf16(2, p->dqkv, 3 * H, a.x_in, H, 3 * H, H, T, FEDB200_EPI_ATOMIC_F32, a.g_wqkv, nullptr, H, nullptr,

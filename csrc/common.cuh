@@ -97,6 +97,17 @@ __device__ __forceinline__ void dropout_apply8(float* v, uint64_t seed, uint32_t
         v[2 * k + 1] *= dropout_lane(w, 1u, thresh16, inv_keep);
     }
 }
+// 32 keep decisions for columns [col0, col0 + 32) of `row` as one bit mask (bit i = column col0 + i is kept)
+__device__ __forceinline__ uint32_t dropout_bits32(uint32_t key, uint32_t row, uint32_t col0, uint32_t thresh16) {
+    uint32_t bits = 0u;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        const uint32_t w = dropout_word(key, row, (col0 >> 1) + k);
+        bits |= ((w & 0xFFFFu) < thresh16 ? 1u : 0u) << (2 * k);
+        bits |= ((w >> 16) < thresh16 ? 1u : 0u) << (2 * k + 1);
+    }
+    return bits;
+}
 __host__ __device__ inline uint32_t dropout_thresh16(float p) {
     const float keep = 1.0f - p;
     return keep >= 1.0f ? 65536u : (uint32_t)(keep * 65536.0f + 0.5f);

@@ -213,8 +213,9 @@ extern "C" int fedb200_gemm_bf16(int layout, const void* A, int lda, const void*
     // make every split non-empty
     while (splits > 1 && (splits - 1) * ((k_blocks + splits - 1) / splits) >= k_blocks) --splits;
 
-    const int BN = N >= 256 ? 256 : (N >= 128 ? 128 : 64);
+    int BN = N >= 256 ? 256 : (N >= 128 ? 128 : 64);
     const int a_mn = layout == 2, b_mn = layout != 0;
+    if (gemm_mode() == 3 && BN == 256) BN = 128;          // experiment: narrower pair tiles
     if (BN >= 128 && gemm_mode() != 1) {
         // CTA-pair kernel: 256 x BN tile per two SMs, each SM loads half of B
         GemmParams pp;

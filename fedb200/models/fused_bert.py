@@ -148,7 +148,9 @@ class FusedRunner:
         f32 = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)
         self.xs = [bf(T, H) for _ in range(L + 1)]
         self.act = [dict(qkv=bf(T, 3 * H), ctx=bf(T, H), z1=bf(T, H), a1=bf(T, H), u=bf(T, I), g=bf(T, I), z2=bf(T, H),
-                         mean1=f32(T), rstd1=f32(T), mean2=f32(T), rstd2=f32(T), lse=f32(self.heads * T))
+                         mean1=f32(T), rstd1=f32(T), mean2=f32(T), rstd2=f32(T), lse=f32(self.heads * T),
+                         drop_bits=(torch.empty(self.heads * T * ((c.max_position + 31) // 32), dtype=torch.int32, device=dev)
+                                    if (c.attention_dropout > 0 and c.arch == "bert") else None))
                     for _ in range(L)]
         self.emb_mean, self.emb_rstd = f32(T), f32(T)
         self.emb_out = bf(T, self.E) if self.E != H else None
@@ -227,6 +229,7 @@ class FusedRunner:
             Ly.x_in, Ly.x_out = self.xs[l].data_ptr(), self.xs[l + 1].data_ptr()
             for f in ("qkv", "ctx", "z1", "a1", "u", "g", "z2", "mean1", "rstd1", "mean2", "rstd2", "lse"):
                 setattr(Ly, f, a[f].data_ptr())
+            Ly.drop_bits = a["drop_bits"].data_ptr() if a["drop_bits"] is not None else None
         self._plan_ref = C.byref(P)
         return P
 
@@ -343,7 +346,8 @@ class FusedRunner:
             k, a = self.lk[l], self.act[l]
             x = self.xs[l][:T]
             ops.gemm(0, x, self.wqkv_bf[l], a["qkv"][:T], T, 3 * H, H, ops.EPI_BIAS, bias=self.bqkv[l])
-            ops.attn_fwd(a["qkv"][:T], a["ctx"][:T], a["lse"], cu, B, self.heads, max_len, scale, self._seed(l, 1), pa)
+            ops.attn_fwd(a["qkv"][:T], a["ctx"][:T], a["lse"], cu, B, self.heads, max_len, scale, self._seed(l, 1), pa,
+                         drop_bits=a["drop_bits"] if train else None)
             ops.gemm(0, a["ctx"][:T], self._wb(k["o.w"]), a["z1"][:T], T, H, H, ops.EPI_BIAS_DROP_RES,
                      bias=self._w(k["o.b"]), aux=x, seed=self._seed(l, 2), dropout_p=ph)
             ops.layernorm_fwd(a["z1"][:T], self._w(k["ln1.w"]), self._w(k["ln1.b"]), a["a1"][:T], a["mean1"][:T],
@@ -390,7 +394,8 @@ class FusedRunner:
             ops.gemm(1, df, self._wb(k["o.w"]), self.dctx[:T], T, H, H, ops.EPI_ADD)
             ops.gemm(2, df, a["ctx"][:T], self._g(k["o.w"]), H, H, T, ops.EPI_ATOMIC_F32, splits=self._splits(H, H, T))
             ops.attn_bwd(a["qkv"][:T], a["ctx"][:T], self.dctx[:T], a["lse"], self.delta, self.dqkv[:T],
-                         self.dq_accum[:T], cu, B, self.heads, max_len, scale, self._seed(l, 1), pa, dbias=self.gbqkv[l])
+                         self.dq_accum[:T], cu, B, self.heads, max_len, scale, self._seed(l, 1), pa, dbias=self.gbqkv[l],
+                         drop_bits=a["drop_bits"])
             ops.gemm(1, self.dqkv[:T], self.wqkv_bf[l], dx, T, H, 3 * H, ops.EPI_ADD, aux=dzb)
             ops.gemm(2, self.dqkv[:T], x, self.gwqkv[l], 3 * H, H, T, ops.EPI_ATOMIC_F32, splits=self._splits(3 * H, H, T))
         ops.embed_bwd(dx, self.d_ids[:T], self.d_pos[:T], self.d_tt[:T], self._w("bert.embeddings.word_embeddings.weight"),

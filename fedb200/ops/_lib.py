@@ -33,8 +33,8 @@ _PROTOS = {
     "fedb200_embed_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, u64, f32, vp]),
     "fedb200_head_fwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, f32, u64, f32, vp]),
     "fedb200_head_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, u64, f32, vp]),
-    "fedb200_attn_fwd": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, f32, u64, f32, vp]),
-    "fedb200_attn_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, u64, f32, vp]),
+    "fedb200_attn_fwd": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, f32, u64, f32, vp, vp]),
+    "fedb200_attn_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, u64, f32, vp, vp]),
     "fedb200_gram_bf16": (i32, [vp, i32, i32, sz, sz, sz, sz, vp, i32, vp]),
     "fedb200_pagerank": (i32, [vp, i32, i32, f64, f64, i32, f64, i32, vp, vp, vp, vp]),
     "fedb200_sha256_leaves": (i32, [vp, vp, sz, u32, vp, vp]),
@@ -59,7 +59,7 @@ class BertLayer(C.Structure):
     _fields_ = [(n, vp) for n in (
         "wqkv", "wo", "w1", "w2", "bqkv", "bo", "b1", "b2", "ln1w", "ln1b", "ln2w", "ln2b",
         "g_wqkv", "g_bqkv", "g_wo", "g_bo", "g_w1", "g_b1", "g_w2", "g_b2", "g_ln1w", "g_ln1b", "g_ln2w", "g_ln2b",
-        "x_in", "x_out", "qkv", "ctx", "z1", "a1", "u", "g", "z2", "mean1", "rstd1", "mean2", "rstd2", "lse")]
+        "x_in", "x_out", "qkv", "ctx", "z1", "a1", "u", "g", "z2", "mean1", "rstd1", "mean2", "rstd2", "lse", "drop_bits")]
 
 
 MAX_LAYERS = 48

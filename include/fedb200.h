@@ -78,13 +78,15 @@ int fedb200_head_bwd(const void* x, const int* first_tok, const float* Wp, const
                      void* stream);
 /* K9. fused masked-softmax attention over packed variable-length sequences (head_dim 64), tcgen05 + TMA.
  * qkv is [T, 3H] bf16 (Q | K | V), ctx/dctx [T, H], lse [heads, T] fp32; cu_seqlens is int32 [B+1] on device. */
+/* drop_bits (optional, uint32 [heads, T, ceil(max_seqlen / 32)]): the forward stores its dropout keep decisions there and
+ * the backward, given the same buffer and max_seqlen, reads them instead of re-hashing (NULL = regenerate from seed). */
 int fedb200_attn_fwd(const void* qkv, void* ctx, float* lse, const int* cu_seqlens, int B, int T, int heads,
-                     int max_seqlen, float scale, unsigned long long seed, float dropout_p, void* stream);
+                     int max_seqlen, float scale, unsigned long long seed, float dropout_p, void* drop_bits, void* stream);
 /* dq_accum: fp32 [T, H] scratch, zero on entry, left zero on exit.  dbias_qkv (optional, fp32 [3H]): the q/k/v bias
  * gradients (column sums of dqkv) are accumulated into it by the finishing pass. */
 int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dctx, const float* lse, float* delta, void* dqkv,
                      float* dq_accum, float* dbias_qkv, const int* cu_seqlens, int B, int T, int heads, int max_seqlen,
-                     float scale, unsigned long long seed, float dropout_p, void* stream);
+                     float scale, unsigned long long seed, float dropout_p, const void* drop_bits, void* stream);
 
 /* ---- native step executor ------------------------------------------------------------------------------------- */
 /* One call = the whole forward (or backward) launch sequence of the fused BERT trainer.  The plan holds raw
@@ -100,6 +102,7 @@ typedef struct {
     /* saved activations */
     void *x_in, *x_out, *qkv, *ctx, *z1, *a1, *u, *g, *z2;
     float *mean1, *rstd1, *mean2, *rstd2, *lse;
+    void* drop_bits;                 /* attention dropout keep-bits (NULL: backward re-hashes) */
 } fedb200_bert_layer;
 
 typedef struct {

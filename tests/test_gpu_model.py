@@ -92,6 +92,17 @@ def test_attention_dropout_exact_mask(cuda_lib):
     torch.cuda.synchronize()
     e = (dqkv.float() - qr.grad).abs().max().item()
     assert e < 3e-2 * max(qr.grad.abs().max().item(), 1.0) + 2e-2, f"dropout backward max err {e}"
+    # same thing with the keep-bits stored by the forward and re-read by the backward (the trainer's path)
+    bits = torch.zeros(heads * T * ((max(lens) + 31) // 32), dtype=torch.int32, device="cuda")
+    ctx2 = torch.zeros_like(ctx)
+    ops.attn_fwd(qkv, ctx2, lse, cu, B, heads, max(lens), 0.125, seed, p, drop_bits=bits)
+    assert torch.equal(ctx2, ctx)
+    dqkv2 = torch.zeros_like(dqkv)
+    ops.attn_bwd(qkv, ctx2, dctx, lse, torch.zeros(heads * T, device="cuda"), dqkv2, torch.zeros(T, H, device="cuda"), cu, B,
+                 heads, max(lens), 0.125, seed, p, drop_bits=bits)
+    torch.cuda.synchronize()
+    e2 = (dqkv2.float() - qr.grad).abs().max().item()
+    assert e2 < 3e-2 * max(qr.grad.abs().max().item(), 1.0) + 2e-2, f"stored-bits backward max err {e2}"
 
 
 def _mini_cfg(dropout=0.0, labels=3, name="bert-mini"):
