@@ -14,8 +14,8 @@
 //   S^T = K Q_i^T and dP^T = V dO_i^T land in TMEM with the kv index on the lanes, so the thread that owns a kv
 //   row produces its rows of P^T and dS^T directly in the A-operand layout; the same dS^T buffer is read
 //   K-major for dK += dS^T Q_i and MN-major for dQ_i = dS K (no transposes anywhere).  dV/dK accumulate in
-//   TMEM across the q loop; dQ tiles are reduced across kv CTAs with fp32 vector atomics into `dq_accum`
-//   (scratch, [T, H] fp32, must be zero on entry; the finishing kernel converts it to bf16 and re-zeroes it).
+//   TMEM across the q loop; every kv CTA stores its dQ partial into slot `kv tile` of `dq_accum` (scratch,
+//   [ceil(max_seqlen/128), T, H] bf16, no initialisation needed) and the finishing kernel sums the slots in fp32.
 // Dropout uses the library-wide counter RNG: row = head * T + q token, col = kv position in the sequence.  The forward
 // can also store its keep decisions as bit words ([heads, T, ceil(max_seqlen/32)] uint32); given those, the backward
 // reads one word per q row instead of re-hashing every element (13 -> 4 instructions per element).
@@ -241,22 +241,30 @@ __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __
     delta[(size_t)h * T + tok] = s;
 }
 
-// Finishing pass over dqkv [T, 3H]: the Q third is converted from the fp32 atomics buffer (which is re-zeroed for
-// the next call), and — when `dbias` is given — the column sums of all three thirds (the q/k/v bias gradients)
-// are accumulated in the same sweep, so the backward needs no separate column-sum kernel for dqkv.
-// blockDim = (32, 8): a warp-row covers 64 contiguous columns; rows are strided over y and blockIdx.y.
-__global__ void __launch_bounds__(256) attn_bwd_finish_kernel(float* __restrict__ dq_accum, __nv_bfloat16* __restrict__ dqkv,
-                                                              float* __restrict__ dbias, int T, int H, int rows_per_block) {
+// Finishing pass over dqkv [T, 3H]: the Q third is the sum of the per-kv-tile dQ partials written by the main kernel
+// (`dq_part` is [n_kv_tiles, T, H] bf16; plain stores there instead of atomics: fp32 vector REDs into one [T, H]
+// buffer measured ~200 us per layer of back-pressure, the partial round trip costs ~35 us), and — when `dbias` is
+// given — the column sums of all three thirds (the q/k/v bias gradients) are accumulated in the same sweep, so the
+// backward needs no separate column-sum kernel for dqkv.  One block column per 64 columns, one block row per sequence;
+// blockDim = (32, 8): a warp-row covers 64 contiguous columns, the 8 rows of threads stride over the sequence's tokens.
+__global__ void __launch_bounds__(256) attn_bwd_finish_kernel(const __nv_bfloat16* __restrict__ dq_part, __nv_bfloat16* __restrict__ dqkv,
+                                                              float* __restrict__ dbias, const int* __restrict__ cu_seqlens,
+                                                              int T, int H) {
     __shared__ float2 red[8][32];
     const int col = (blockIdx.x * 32 + threadIdx.x) * 2;          // column within [0, 3H)
-    const int r0 = blockIdx.y * rows_per_block, r1 = min(T, r0 + rows_per_block);
+    const int s0 = cu_seqlens[blockIdx.y], s1 = cu_seqlens[blockIdx.y + 1];
+    const int n_kv = (s1 - s0 + 127) / 128;
+    const int r0 = s0 + blockIdx.z * 64, r1 = min(s1, r0 + 64);          // 64-token slice of the sequence
+    if (r0 >= s1) return;
     float2 acc = make_float2(0.f, 0.f);
     if (col < 3 * H) {
         if (col < H) {
             for (int r = r0 + threadIdx.y; r < r1; r += 8) {
-                float2* src = reinterpret_cast<float2*>(dq_accum + (size_t)r * H + col);
-                const float2 v = *src;
-                *src = make_float2(0.f, 0.f);
+                float2 v = make_float2(0.f, 0.f);
+                for (int j = 0; j < n_kv; ++j) {
+                    const float2 t = unpack_bf16x2(__ldcs(reinterpret_cast<const unsigned int*>(dq_part + ((size_t)j * T + r) * H + col)));
+                    v.x += t.x; v.y += t.y;
+                }
                 const uint32_t pk = pack_bf16x2(v.x, v.y);
                 *reinterpret_cast<uint32_t*>(dqkv + (size_t)r * 3 * H + col) = pk;
                 const float2 f = unpack_bf16x2(pk);               // sum what the GEMMs will consume
@@ -449,13 +457,17 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
                 uint32_t raw[16];
                 tmem_ld_32x16(tm_dq + lane_addr + cg * 16, raw);
                 tmem_ld_wait();
-                if (q < len) {
-                    float* dst = dq_accum + (size_t)(tok0 + q) * H + h * 64 + cg * 16;
+                if (q < len) {       // this kv tile's partial of dQ: plain bf16 stores into slot blockIdx.x
+                    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(dq_accum) + ((size_t)blockIdx.x * T + tok0 + q) * H + h * 64 + cg * 16;
 #pragma unroll
-                    for (int g = 0; g < 4; ++g)
-                        atomicAdd(reinterpret_cast<float4*>(dst + g * 4),
-                                  make_float4(__uint_as_float(raw[g * 4]), __uint_as_float(raw[g * 4 + 1]),
-                                              __uint_as_float(raw[g * 4 + 2]), __uint_as_float(raw[g * 4 + 3])));
+                    for (int g = 0; g < 2; ++g) {
+                        uint4 pk;
+                        pk.x = pack_bf16x2(__uint_as_float(raw[g * 8 + 0]), __uint_as_float(raw[g * 8 + 1]));
+                        pk.y = pack_bf16x2(__uint_as_float(raw[g * 8 + 2]), __uint_as_float(raw[g * 8 + 3]));
+                        pk.z = pack_bf16x2(__uint_as_float(raw[g * 8 + 4]), __uint_as_float(raw[g * 8 + 5]));
+                        pk.w = pack_bf16x2(__uint_as_float(raw[g * 8 + 6]), __uint_as_float(raw[g * 8 + 7]));
+                        __stcs(reinterpret_cast<uint4*>(dst + g * 8), pk);
+                    }
                 }
             }
             tc_fence_before_sync();
@@ -539,14 +551,8 @@ extern "C" int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dc
                                                    1.0f / (1.0f - dropout_p), dropout_p > 0.f, (const uint32_t*)drop_bits,
                                                    (max_seqlen + 31) / 32);
     FEDB_LAUNCH_CHECK();
-    {
-        const int col_blocks = (3 * H + 63) / 64;
-        int row_blocks = (sm_count() * 8 + col_blocks - 1) / col_blocks;
-        if (row_blocks > (T + 31) / 32) row_blocks = (T + 31) / 32;
-        if (row_blocks < 1) row_blocks = 1;
-        const int rpb = (T + row_blocks - 1) / row_blocks;
-        attn_bwd_finish_kernel<<<dim3(col_blocks, row_blocks), dim3(32, 8), 0, s>>>(dq_accum, (__nv_bfloat16*)dqkv, dbias_qkv, T, H, rpb);
-    }
+    attn_bwd_finish_kernel<<<dim3((3 * H + 63) / 64, B, (max_seqlen + 63) / 64), dim3(32, 8), 0, s>>>(
+        (const __nv_bfloat16*)dq_accum, (__nv_bfloat16*)dqkv, dbias_qkv, cu_seqlens, T, H);
     FEDB_LAUNCH_CHECK();
     return 0;
 }

@@ -157,7 +157,7 @@ class FusedRunner:
         self.d_emb = bf(T, self.E) if self.E != H else None
         self.dx, self.dzb, self.dfb, self.dctx = bf(T, H), bf(T, H), bf(T, H), bf(T, H)
         self.du, self.dqkv = bf(T, I), bf(T, 3 * H)
-        self.dq_accum = torch.zeros(T, H, dtype=torch.float32, device=dev)
+        self.dq_accum = torch.empty((c.max_position + 127) // 128 * T, H, dtype=torch.float32, device=dev)   # dQ partial slots
         self.delta = f32(self.heads * T)
         self.pooled, self.pooled_drop, self.dpre = f32(Bm, H), f32(Bm, H), f32(Bm, H)
         self.logits, self.dlogits = f32(Bm, self.C), f32(Bm, self.C)

@@ -143,8 +143,9 @@ def attn_fwd(qkv, ctx, lse, cu_seqlens, B, heads, max_seqlen, scale, seed=0, dro
 
 def attn_bwd(qkv, ctx, dctx, lse, delta, dqkv, dq_accum, cu_seqlens, B, heads, max_seqlen, scale, seed=0,
              dropout_p=0.0, dbias=None, drop_bits=None) -> None:
-    """``dq_accum`` is fp32 scratch (zero in, zero out); ``dbias`` (fp32 [3H], optional) receives the q/k/v
-    bias gradients from the fused finishing pass."""
+    """``dq_accum`` is fp32 scratch of ``ceil(max_seqlen / 128) * T * H`` floats (per-kv-tile dQ partials, no
+    initialisation needed); ``dbias`` (fp32 [3H], optional) receives the q/k/v bias gradients from the fused
+    finishing pass."""
     T = qkv.shape[0]
     call("fedb200_attn_bwd", _p(qkv), _p(ctx), _p(dctx), _p(lse), _p(delta), _p(dqkv), _p(dq_accum), _p(dbias),
          _p(cu_seqlens), B, T, heads, max_seqlen, scale, seed, dropout_p, _p(drop_bits), _stream())

@@ -82,7 +82,8 @@ int fedb200_head_bwd(const void* x, const int* first_tok, const float* Wp, const
  * the backward, given the same buffer and max_seqlen, reads them instead of re-hashing (NULL = regenerate from seed). */
 int fedb200_attn_fwd(const void* qkv, void* ctx, float* lse, const int* cu_seqlens, int B, int T, int heads,
                      int max_seqlen, float scale, unsigned long long seed, float dropout_p, void* drop_bits, void* stream);
-/* dq_accum: fp32 [T, H] scratch, zero on entry, left zero on exit.  dbias_qkv (optional, fp32 [3H]): the q/k/v bias
+/* dq_accum: scratch of at least ceil(max_seqlen / 128) * T * H * 2 bytes (per-kv-tile bf16 dQ partials; no initialisation).
+ * dbias_qkv (optional, fp32 [3H]): the q/k/v bias
  * gradients (column sums of dqkv) are accumulated into it by the finishing pass. */
 int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dctx, const float* lse, float* delta, void* dqkv,
                      float* dq_accum, float* dbias_qkv, const int* cu_seqlens, int B, int T, int heads, int max_seqlen,

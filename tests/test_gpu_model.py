@@ -50,7 +50,7 @@ def test_attention_fwd_bwd_no_dropout(cuda_lib, lens, heads):
     dctx = (torch.randn(T, H, device="cuda") * 0.5).bfloat16()
     ref.backward(dctx.float())
     dqkv = torch.zeros(T, 3 * H, dtype=torch.bfloat16, device="cuda")
-    dq_acc = torch.zeros(T, H, device="cuda")
+    dq_acc = torch.empty((max(lens) + 127) // 128 * T, H, device="cuda")
     delta = torch.zeros(heads * T, device="cuda")
     dbias = torch.ones(3 * H, device="cuda")
     ops.attn_bwd(qkv, ctx, dctx, lse, delta, dqkv, dq_acc, cu, B, heads, max(lens), scale, dbias=dbias)
@@ -61,7 +61,6 @@ def test_attention_fwd_bwd_no_dropout(cuda_lib, lens, heads):
         e = (dqkv[:, sl].float() - g[:, sl]).abs().max().item()
         scale_ref = g[:, sl].abs().max().item()
         assert e < 3e-2 * max(scale_ref, 1.0) + 2e-2, f"{name} max err {e} (ref max {scale_ref})"
-    assert torch.count_nonzero(dq_acc) == 0, "dq_accum scratch must be left zeroed"
 
 
 def test_attention_dropout_exact_mask(cuda_lib):
@@ -87,7 +86,7 @@ def test_attention_dropout_exact_mask(cuda_lib):
     dctx = (torch.randn(T, H, device="cuda") * 0.5).bfloat16()
     ref.backward(dctx.float())
     dqkv = torch.zeros(T, 3 * H, dtype=torch.bfloat16, device="cuda")
-    ops.attn_bwd(qkv, ctx, dctx, lse, torch.zeros(heads * T, device="cuda"), dqkv, torch.zeros(T, H, device="cuda"), cu, B,
+    ops.attn_bwd(qkv, ctx, dctx, lse, torch.zeros(heads * T, device="cuda"), dqkv, torch.empty(4 * T, H, device="cuda"), cu, B,
                  heads, max(lens), 0.125, seed, p)
     torch.cuda.synchronize()
     e = (dqkv.float() - qr.grad).abs().max().item()
@@ -98,7 +97,7 @@ def test_attention_dropout_exact_mask(cuda_lib):
     ops.attn_fwd(qkv, ctx2, lse, cu, B, heads, max(lens), 0.125, seed, p, drop_bits=bits)
     assert torch.equal(ctx2, ctx)
     dqkv2 = torch.zeros_like(dqkv)
-    ops.attn_bwd(qkv, ctx2, dctx, lse, torch.zeros(heads * T, device="cuda"), dqkv2, torch.zeros(T, H, device="cuda"), cu, B,
+    ops.attn_bwd(qkv, ctx2, dctx, lse, torch.zeros(heads * T, device="cuda"), dqkv2, torch.empty(4 * T, H, device="cuda"), cu, B,
                  heads, max(lens), 0.125, seed, p, drop_bits=bits)
     torch.cuda.synchronize()
     e2 = (dqkv2.float() - qr.grad).abs().max().item()
