@@ -95,17 +95,19 @@ def stage_round(rt, rnd, device):
     from fedb200.data.build import client_loaders, global_test_loader
     from fedb200.data.dataset import collate_packed
 
+    to_dev = lambda b: {k: (v.to(device) if isinstance(v, torch.Tensor) else v) for k, v in b.items()}
+
     def dev(loader):
-        out = []
-        for idx in loader.batch_indices():
-            b = collate_packed(loader.dataset, idx)
-            out.append({k: (v.to(device) if isinstance(v, torch.Tensor) else v) for k, v in b.items()})
-        return out
+        return [to_dev(collate_packed(loader.dataset, idx)) for idx in loader.batch_indices()]
+
+    def dev_eval(loader):          # evaluation goes through the runner's packing (same as FusedRunner.evaluate)
+        micro, sizes = rt.runner.eval_plan(loader)
+        return [to_dev(m) for m in micro], sizes
     staged = []
     for k in rt.local_ids:
         tr, te = client_loaders(rt.corpus, rt.cfg.data, k, rnd)
-        staged.append((dev(tr), dev(te), tr.num_samples))
-    return staged, dev(global_test_loader(rt.corpus, rt.cfg.data, rnd))
+        staged.append((dev(tr), dev_eval(te), tr.num_samples))
+    return staged, dev_eval(global_test_loader(rt.corpus, rt.cfg.data, rnd))
 
 
 def kernel_round(rt, staged, gtest):
@@ -124,8 +126,7 @@ def kernel_round(rt, staged, gtest):
             cuda_ops.merkle_root(leaves, rt._bench_scratch, rt._bench_root)
         else:
             rt.slots[li].copy_(run.flat)
-        for b in test_b:                                # local evaluation of the trained peer
-            run.eval_step(b)
+        run.evaluate_packed(*test_b)                    # local evaluation of the trained peer (results stay on device)
         ws.append(1.0)
     if len(ws) == 1 and rt.P == 1:
         rt.comm.weighted_mean(rt.slots[0], 1.0, rt.global_flat)
@@ -134,8 +135,7 @@ def kernel_round(rt, staged, gtest):
         rt.comm.weighted_mean(rt.acc, float(len(ws)), rt.global_flat)
     run.load_flat(rt.global_flat)
     run.sync_shadow()
-    for b in gtest:
-        run.eval_step(b)
+    run.evaluate_packed(*gtest)
 
 
 def run_fedb200(args):

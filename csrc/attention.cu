@@ -144,6 +144,7 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attn_fwd_kernel(const __grid_co
             mbar_wait(&s_full, (uint32_t)j & 1u);
             tc_fence_after_sync();
             const int kv_valid = min(128, len - j * 128);
+            const bool full = kv_valid == 128;            // interior kv tile: no per-element masking (warp-uniform)
             // pass 1: row max
             float mx = -INFINITY;
 #pragma unroll 1
@@ -151,9 +152,14 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attn_fwd_kernel(const __grid_co
                 uint32_t raw[32];
                 tmem_ld_32x32(tmem_s + lane_addr + c * 32, raw);
                 tmem_ld_wait();
+                if (full) {
 #pragma unroll
-                for (int i = 0; i < 32; ++i)
-                    if (c * 32 + i < kv_valid) mx = fmaxf(mx, __uint_as_float(raw[i]));
+                    for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(raw[i]));
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (c * 32 + i < kv_valid) mx = fmaxf(mx, __uint_as_float(raw[i]));
+                }
             }
             const float m_new = fmaxf(m_run, mx * scale_log2);
             const float alpha = exp2f(m_run - m_new);
@@ -166,10 +172,18 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attn_fwd_kernel(const __grid_co
                 tmem_ld_wait();
                 float p[32];
                 float rs = 0.f;
+                if (full) {
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    p[i] = (c * 32 + i < kv_valid) ? exp2f(__uint_as_float(raw[i]) * scale_log2 - m_new) : 0.f;
-                    rs += p[i];
+                    for (int i = 0; i < 32; ++i) {
+                        p[i] = exp2f(fmaf(__uint_as_float(raw[i]), scale_log2, -m_new));
+                        rs += p[i];
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        p[i] = (c * 32 + i < kv_valid) ? exp2f(fmaf(__uint_as_float(raw[i]), scale_log2, -m_new)) : 0.f;
+                        rs += p[i];
+                    }
                 }
                 l_run += rs;
                 if (use_dropout) {

@@ -98,8 +98,12 @@ class FusedRunner:
         self.cfg, self.fed, self.device = model_cfg, fed, torch.device(device)
         c = model_cfg
         self.H, self.I, self.L, self.heads, self.C = c.hidden_size, c.intermediate_size, c.num_layers, c.num_heads, c.num_labels
-        self.max_batch = max_batch or fed.data.batch_size
-        self.max_tokens = max_tokens or self.max_batch * min(fed.data.max_seq_len, c.max_position)
+        self.train_batch = fed.data.batch_size
+        # forward-only passes may pack several reference batches into one launch sequence (same samples, same loss
+        # normalisation, bigger GEMMs): the sequence-count capacity is 4 reference batches, the token capacity is
+        # what one training batch can need
+        self.max_batch = max_batch or 4 * fed.data.batch_size
+        self.max_tokens = max_tokens or fed.data.batch_size * min(fed.data.max_seq_len, c.max_position)
 
         # ---- arenas: HF keys, compute-friendly memory order (q|k|v weights contiguous) -----------------
         ref = build_model(c, "cpu", seed)
@@ -442,16 +446,48 @@ class FusedRunner:
         self.d2h_bytes += 4
         return {"loss": out, "steps": n}
 
-    def evaluate(self, loader) -> Tuple[float, float]:
+    def eval_plan(self, loader):
+        """Pack the loader's (unshuffled) reference batches into as few forward passes as the workspace allows.
+        Returns (list of packed micro-batches, list of reference batch sizes)."""
+        ref = loader.batch_indices()
+        lens = loader.dataset.lengths()
+        micro, cur, cur_tok = [], [], 0
+        for idx in ref:
+            for i in idx:
+                n = int(lens[i])
+                if cur and (cur_tok + n > self.max_tokens or len(cur) >= self.max_batch):
+                    micro.append(collate_packed(loader.dataset, np.asarray(cur)))
+                    cur, cur_tok = [], 0
+                cur.append(int(i))
+                cur_tok += n
+        if cur:
+            micro.append(collate_packed(loader.dataset, np.asarray(cur)))
+        return micro, [len(i) for i in ref]
+
+    def evaluate_packed(self, micro, ref_sizes) -> Tuple[torch.Tensor, torch.Tensor]:
+        """Forward passes over pre-packed micro-batches; returns device scalars (sum over REFERENCE batches of the
+        batch-mean loss, number of correct predictions)."""
+        losses, correct = [], torch.zeros((), dtype=torch.int64, device=self.device)
+        for mb in micro:
+            T, B, max_len = self._upload(mb)
+            self._forward(T, B, max_len, train=False)
+            losses.append(self.loss_vec[:B].clone())
+            correct += (self.pred[:B] == self.d_labels[:B]).sum()
+        per_sample = torch.cat(losses)
         loss_sum = torch.zeros((), device=self.device)
-        correct = torch.zeros((), dtype=torch.int64, device=self.device)
-        total = 0
-        for idx in loader.batch_indices():
-            l, c = self.eval_step(collate_packed(loader.dataset, idx))
-            loss_sum += l
-            correct += c
-            total += len(idx)
+        o = 0
+        for n in ref_sizes:                       # mixed normalisation of the reference: sum of batch means
+            loss_sum += per_sample[o:o + n].mean()
+            o += n
+        return loss_sum, correct
+
+    def evaluate(self, loader) -> Tuple[float, float]:
+        micro, ref_sizes = self.eval_plan(loader)
+        if not micro:
+            return 0.0, 0.0
+        loss_sum, correct = self.evaluate_packed(micro, ref_sizes)
+        total = sum(ref_sizes)
         self.d2h_bytes += 12
         n_ds = max(len(loader.dataset), 1)
-        # mixed normalisation kept on purpose: sum of batch-mean losses / len(dataset) (server_IID_IMDB.py:133)
+        # sum of batch-mean losses / len(dataset), as the reference computes it (server_IID_IMDB.py:133)
         return float(loss_sum.item()) / n_ds, (int(correct.item()) / total if total else 0.0)

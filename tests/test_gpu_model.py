@@ -217,6 +217,11 @@ def test_fused_runner_interface_and_state_dict(cuda_lib, tmp_path):
     assert stats["steps"] == 8 and math.isfinite(stats["loss"])
     loss, acc = run.evaluate(BatchLoader(ds, 8))
     assert 0.0 <= acc <= 1.0 and math.isfinite(loss)
+    # packed evaluation == batch-by-batch evaluation with the reference's normalisation
+    want = sum(run.eval_step(b)[0].item() for b in BatchLoader(ds, 8).packed()) / len(ds)
+    assert abs(loss - want) < 2e-3 * max(1.0, abs(want)), (loss, want)
+    micro, sizes = run.eval_plan(BatchLoader(ds, 8))
+    assert sizes == [8] * 8 and len(micro) <= 8 and sum(int(m["labels"].numel()) for m in micro) == 64
     save_pretrained(run.state_dict(), fed.model, str(tmp_path / "ck"))
     sd = load_state(str(tmp_path / "ck"))
     assert list(sd.keys()) == sorted(run.state_dict().keys()) or set(sd.keys()) == set(run.state_dict().keys())
