@@ -47,7 +47,7 @@ def similarity_to_transition(gram: np.ndarray) -> np.ndarray:      # kept as the
     return gram_to_edge_weights(gram)
 
 
-def score_updates(gram: np.ndarray, k_sigma: float = 1.0, low_only: bool = True
+def score_updates(gram: np.ndarray, k_sigma: float = 1.0, low_only: bool = True, min_rel_gap: float = 0.1
                   ) -> Tuple[List[int], np.ndarray, Tuple[float, float]]:
     """PageRank over the similarity graph; peers whose rank falls below ``mean - k·sigma`` (or
     outside the band when ``low_only=False``, the reference's two-sided rule) are anomalous."""
@@ -56,6 +56,9 @@ def score_updates(gram: np.ndarray, k_sigma: float = 1.0, low_only: bool = True
     std = float(np.sqrt(((r - mean) ** 2).sum() / len(r)))
     lo, hi = mean - k_sigma * std, mean + k_sigma * std
     bad = (r < lo) if low_only else ((r < lo) | (r > hi))
+    # the reference's mean ± 1 sigma rule always flags ~1/6 of any population; on an all-honest round the ranks are
+    # nearly uniform, so additionally require a rank at least `min_rel_gap` below the mean before eliminating a peer
+    bad &= np.abs(r - mean) > min_rel_gap * mean
     if std < 1e-9:
         bad = np.zeros_like(bad)
     return [int(i) for i in np.flatnonzero(bad)], r, (float(lo), float(hi))

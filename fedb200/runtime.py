@@ -174,7 +174,8 @@ class FedRuntime:
                 ranks_d, mask_d, info_d = cuda_ops.pagerank(g[: self.N, : self.N].contiguous(), mode=1, low_only=True)
                 self.comm.launches += 1
                 ranks = ranks_d.cpu().numpy()
-                bad = [int(i) for i in np.flatnonzero(mask_d.cpu().numpy())]
+                mean_rank = float(ranks.mean())          # same guard as anomaly.cosine.score_updates(min_rel_gap=0.1)
+                bad = [int(i) for i in np.flatnonzero(mask_d.cpu().numpy()) if abs(ranks[i] - mean_rank) > 0.1 * mean_rank]
                 band = (float(info_d[1]), float(info_d[2]))
             else:
                 bad, ranks, band = score_updates(g.to(torch.float64).cpu().numpy()[: self.N, : self.N])

@@ -93,7 +93,8 @@ def main():
     mine = rt.slots[0].clone()
     gathered = [torch.empty_like(mine) for _ in range(world)]
     dist.all_gather(gathered, mine)
-    torch.testing.assert_close(rt.global_flat, torch.stack(gathered).mean(0), rtol=1e-5, atol=1e-6)
+    keep = [i for i in range(world) if i not in rt.masked]
+    torch.testing.assert_close(rt.global_flat, torch.stack([gathered[i] for i in keep]).mean(0), rtol=1e-5, atol=1e-6)
     chk = torch.tensor([float(rt.global_flat.double().sum())], device=dev, dtype=torch.float64)
     lo, hi = chk.clone(), chk.clone()
     dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
