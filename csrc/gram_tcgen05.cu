@@ -26,9 +26,15 @@ struct GramMaps {
     CUtensorMap map[FEDB200_MAX_RANKS];
 };
 
+// Segment stacking (S > 1): with few clients a [rows x 64] tile is tiny (8 clients = 1 KB per TMA box) and the kernel
+// becomes TMA-issue bound.  Each delta row is therefore cut into segments that are stacked as extra tile rows: the
+// buffer is viewed as [rows * nseg_total, seg_len], one box brings S segments of one client ([S x 64], 2 KB at S = 16),
+// the tile holds rows_total * S <= 128 rows, and the wanted Gram entry is the sum of the S "diagonal" products
+// G[a, b] = sum_s acc[a*S + s, b*S + s]; the off-diagonal products are free riders on a bandwidth-bound kernel.
 __global__ void __launch_bounds__(GR_THREADS, 1) gram_tcgen05_kernel(const __grid_constant__ GramMaps maps, int n_ranks,
-                                                                     int rows_per_rank, int n_pad, int kb_begin,
-                                                                     int kb_end, float* __restrict__ out, int n_out) {
+                                                                     int boxes_per_rank, int box_rows, int n_pad,
+                                                                     int kb_begin, int kb_end, float* __restrict__ out,
+                                                                     int n_out, int S, int nseg_total, int seg_begin) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     __shared__ __align__(8) uint64_t full_bar[GR_STAGES];
@@ -37,7 +43,7 @@ __global__ void __launch_bounds__(GR_THREADS, 1) gram_tcgen05_kernel(const __gri
     __shared__ uint32_t tmem_base_slot;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int rows_total = n_ranks * rows_per_rank;
+    const int rows_total = n_ranks * boxes_per_rank * box_rows;      // tile rows (clients x segments)
     const uint32_t tmem_cols = n_pad <= 32 ? 32u : (n_pad <= 64 ? 64u : 128u);
 
     // rows >= rows_total are never written by TMA: clear the ring once so the unused A rows are finite
@@ -69,7 +75,9 @@ __global__ void __launch_bounds__(GR_THREADS, 1) gram_tcgen05_kernel(const __gri
             mbar_expect_tx(&full_bar[s], stage_tx);
             const int kcol = (kb_begin + (int)blockIdx.x + it * (int)gridDim.x) * 64;
             for (int r = 0; r < n_ranks; ++r)
-                tma_load_2d(smem + s * GR_TILE_BYTES + r * rows_per_rank * 128, &maps.map[r], &full_bar[s], kcol, 0);
+                for (int pr = 0; pr < boxes_per_rank; ++pr)     // one box = all rows of a rank (S = 1) or S segments of one client
+                    tma_load_2d(smem + s * GR_TILE_BYTES + (r * boxes_per_rank + pr) * box_rows * 128, &maps.map[r], &full_bar[s],
+                                kcol, pr * nseg_total + seg_begin);
         }
     } else if (warp == 1 && lane == 0) {
         // ---------------- MMA issuer ----------------
@@ -95,15 +103,18 @@ __global__ void __launch_bounds__(GR_THREADS, 1) gram_tcgen05_kernel(const __gri
     if (n_kb > 0) {
         mbar_wait(&done_bar, 0);
         tc_fence_after_sync();
-        const int row = warp * 32 + lane;
+        const int row = warp * 32 + lane;                     // tile row = client * S + segment
+        const int a = row / S, sg = row % S;
         for (int c0 = 0; c0 < n_pad; c0 += 16) {
             uint32_t v[16];
             tmem_ld_32x16(tmem_d + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);
             tmem_ld_wait();
-            if (row < n_out) {
+            if (a < n_out) {
 #pragma unroll
-                for (int j = 0; j < 16; ++j)
-                    if (c0 + j < n_out) atomicAdd(out + (size_t)row * n_out + c0 + j, __uint_as_float(v[j]));
+                for (int j = 0; j < 16; ++j) {
+                    const int col = c0 + j;                   // keep only the same-segment ("diagonal") products
+                    if (col % S == sg && col / S < n_out) atomicAdd(out + (size_t)a * n_out + col / S, __uint_as_float(v[j]));
+                }
             }
         }
     }
@@ -116,9 +127,9 @@ __global__ void __launch_bounds__(GR_THREADS, 1) gram_tcgen05_kernel(const __gri
 
 using namespace fedb;
 
-// rows_ptrs[r]: base of rank r's [rows_per_rank, D] bf16 buffer (local or peer-mapped), row stride ld elements.
-// Accumulates G[i, j] (i, j < n_out = n_ranks * rows_per_rank) over columns [col_begin, col_end) into `out`
-// (fp32 [n_out, n_out], caller zeroes it).  col_begin must be a multiple of 64.
+// rows_ptrs[r]: base of rank r's [rows_per_rank, ld] bf16 buffer (local or peer-mapped).  Accumulates G[i, j]
+// (i, j < n_out = n_ranks * rows_per_rank) over columns [col_begin, col_end) into `out` (fp32 [n_out, n_out], caller
+// zeroes it).  col_begin must be a multiple of 64.
 extern "C" int fedb200_gram_bf16(const void* const* rows_ptrs, int n_ranks, int rows_per_rank, size_t D, size_t ld,
                                  size_t col_begin, size_t col_end, float* out, int max_ctas, void* stream) {
     FEDB_REQUIRE(n_ranks >= 1 && n_ranks <= FEDB200_MAX_RANKS, "gram: n_ranks=%d outside [1, %d]", n_ranks, FEDB200_MAX_RANKS);
@@ -140,8 +151,37 @@ extern "C" int fedb200_gram_bf16(const void* const* rows_ptrs, int n_ranks, int 
     if (grid > kb_end - kb_begin) grid = kb_end - kb_begin;
     const size_t smem = (size_t)GR_STAGES * GR_TILE_BYTES + 1024;
     FEDB_CHECK(cudaFuncSetAttribute(gram_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    gram_tcgen05_kernel<<<grid, GR_THREADS, smem, (cudaStream_t)stream>>>(maps, n_ranks, rows_per_rank, n_pad, kb_begin,
-                                                                         kb_end, out, rows_total);
+    // S = 1: every client row is one tile row; the single box per rank covers all of the rank's rows (row coordinate 0)
+    gram_tcgen05_kernel<<<grid, GR_THREADS, smem, (cudaStream_t)stream>>>(maps, n_ranks, 1, rows_per_rank, n_pad, kb_begin, kb_end, out,
+                                                                         rows_total, 1, 0, 0);
+    FEDB_LAUNCH_CHECK();
+    return 0;
+}
+
+// Segment-stacked form for few clients.  Every rank's buffer is [rows_per_rank, ld] bf16 with ld = nseg_total * seg_len
+// (zero padded past the real row length); this launch reduces segments [seg_begin, seg_begin + S) of every client, i.e.
+// columns [seg_begin * seg_len, (seg_begin + S) * seg_len).  n_ranks * rows_per_rank * S <= 128, seg_len % 64 == 0.
+extern "C" int fedb200_gram_bf16_seg(const void* const* rows_ptrs, int n_ranks, int rows_per_rank, size_t seg_len,
+                                     int nseg_total, int seg_begin, int S, float* out, int max_ctas, void* stream) {
+    FEDB_REQUIRE(n_ranks >= 1 && n_ranks <= FEDB200_MAX_RANKS, "gram_seg: n_ranks=%d outside [1, %d]", n_ranks, FEDB200_MAX_RANKS);
+    const int clients = n_ranks * rows_per_rank;
+    FEDB_REQUIRE(S >= 1 && clients >= 1 && clients * S <= 128, "gram_seg: %d clients x %d segments exceed the 128-row tile", clients, S);
+    FEDB_REQUIRE(seg_len % 64 == 0 && seg_begin >= 0 && seg_begin + S <= nseg_total, "gram_seg: bad segment layout");
+    GramMaps maps;
+    for (int r = 0; r < n_ranks; ++r) {
+        int e = make_tmap_bf16_2d(&maps.map[r], rows_ptrs[r], (uint64_t)rows_per_rank * nseg_total, (uint64_t)seg_len,
+                                  (uint64_t)seg_len, (uint32_t)S, 64);
+        if (e) return e;
+    }
+    const int n_pad = (clients * S + 15) / 16 * 16;
+    const int kb_end = (int)(seg_len / 64);
+    int grid = sm_count();
+    if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
+    if (grid > kb_end) grid = kb_end;
+    const size_t smem = (size_t)GR_STAGES * GR_TILE_BYTES + 1024;
+    FEDB_CHECK(cudaFuncSetAttribute(gram_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    gram_tcgen05_kernel<<<grid, GR_THREADS, smem, (cudaStream_t)stream>>>(maps, n_ranks, rows_per_rank, S, n_pad, 0, kb_end, out, clients,
+                                                                         S, nseg_total, seg_begin);
     FEDB_LAUNCH_CHECK();
     return 0;
 }

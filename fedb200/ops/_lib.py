@@ -36,6 +36,7 @@ _PROTOS = {
     "fedb200_attn_fwd": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, f32, u64, f32, vp, vp]),
     "fedb200_attn_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, u64, f32, vp, vp]),
     "fedb200_gram_bf16": (i32, [vp, i32, i32, sz, sz, sz, sz, vp, i32, vp]),
+    "fedb200_gram_bf16_seg": (i32, [vp, i32, i32, sz, i32, i32, i32, vp, i32, vp]),
     "fedb200_pagerank": (i32, [vp, i32, i32, f64, f64, i32, f64, i32, vp, vp, vp, vp]),
     "fedb200_sha256_leaves": (i32, [vp, vp, sz, u32, vp, vp]),
     "fedb200_merkle_root": (i32, [vp, vp, u32, vp, vp]),

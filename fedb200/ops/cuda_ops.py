@@ -172,6 +172,27 @@ def gram(deltas: torch.Tensor, col_begin: int = 0, col_end: Optional[int] = None
     return out
 
 
+def gram_layout(D: int, n_ranks: int, rows_per_rank: int) -> dict:
+    """Padded row layout for the segment-stacked Gram kernel: every client row is ``nseg_total`` segments of
+    ``seg_len`` elements (zero padded to ``D_pad``); rank r reduces segments ``[r*S, (r+1)*S)``."""
+    clients = max(1, n_ranks * rows_per_rank)
+    S = 1
+    while S * 2 * clients <= 128:
+        S *= 2
+    seg_len = (D + n_ranks * S * 64 - 1) // (n_ranks * S * 64) * 64
+    return {"S": S, "seg_len": seg_len, "nseg_total": n_ranks * S, "D_pad": n_ranks * S * seg_len}
+
+
+def gram_seg(ptrs: Sequence[int], rows_per_rank: int, layout: dict, seg_begin: int, out: torch.Tensor,
+             max_ctas: int = 0) -> torch.Tensor:
+    """Segment-stacked Gram over (peer) buffers laid out by :func:`gram_layout`; accumulates into ``out``."""
+    arr = (C.c_void_p * len(ptrs))(*[int(p) for p in ptrs])
+    call("fedb200_gram_bf16_seg", C.cast(arr, C.c_void_p), len(ptrs), rows_per_rank, layout["seg_len"], layout["nseg_total"],
+         seg_begin, layout["S"], _p(out), max_ctas, _stream())
+    count()
+    return out
+
+
 def pagerank(mat: torch.Tensor, mode: int = 0, alpha: float = 0.85, tol: float = 1e-6, max_iter: int = 100,
              k_sigma: float = 1.0, low_only: bool = False) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
     _chk(mat, torch.float32, "mat")

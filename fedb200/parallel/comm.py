@@ -51,6 +51,14 @@ class Comm:
         """Buffer every rank allocates identically (peer-mapped on the peer backend)."""
         return torch.zeros(numel, dtype=dtype, device=self.device)
 
+    def delta_buffer(self, rows: int, D: int, dtype=torch.float32) -> torch.Tensor:
+        """Zeroed ``[rows, D_pad]`` buffer for the update scorer; rows are padded to the segment layout of the Gram
+        kernel (:func:`fedb200.ops.cuda_ops.gram_layout`), the caller writes ``[:, :D]``."""
+        from ..ops.cuda_ops import gram_layout
+        self._gram_layout = gram_layout(D, self.world, rows)
+        Dp = self._gram_layout["D_pad"]
+        return self.alloc("deltas", rows * Dp, dtype).view(rows, Dp)
+
     # -- control ----------------------------------------------------------------------------
     def barrier(self) -> None:
         pass
@@ -126,6 +134,10 @@ class LoopbackComm(Comm):
         if deltas.is_cuda:
             from ..ops import cuda_ops
             self.launches += 1
+            lay = getattr(self, "_gram_layout", None)
+            if lay is not None and lay["S"] > 1 and deltas.shape[1] == lay["D_pad"]:
+                out = torch.zeros(deltas.shape[0], deltas.shape[0], dtype=torch.float32, device=deltas.device)
+                return cuda_ops.gram_seg([deltas.data_ptr()], deltas.shape[0], lay, 0, out)
             return cuda_ops.gram(deltas)
         d = deltas.to(torch.float32)
         return d @ d.T

@@ -182,15 +182,20 @@ class PeerComm(Comm):
         if self.gram_part is None or self.gram_part.numel() != n * n:
             self.gram_part = self.alloc(f"gram_part_{n}", n * n)
             self.gram_out = self.alloc(f"gram_out_{n}", n * n)
-        kb = (D + 63) // 64
-        per = (kb + self.world - 1) // self.world
-        lo, hi = min(D, self.rank * per * 64), min(D, (self.rank + 1) * per * 64)
         self.gram_part.zero_()
         self.device_barrier()                                   # all delta rows are written
-        ptrs = (C.c_void_p * self.world)(*[p + do for p in db.ptrs])
-        call("fedb200_gram_bf16", C.cast(ptrs, C.c_void_p), self.world, P, D, D, lo, hi, self.gram_part.data_ptr(), 0,
-             torch.cuda.current_stream().cuda_stream)
-        count()
+        lay = getattr(self, "_gram_layout", None)
+        if lay is not None and lay["S"] > 1 and D == lay["D_pad"]:
+            from ..ops import cuda_ops
+            cuda_ops.gram_seg([p + do for p in db.ptrs], P, lay, self.rank * lay["S"], self.gram_part)
+        else:
+            kb = (D + 63) // 64
+            per = (kb + self.world - 1) // self.world
+            lo, hi = min(D, self.rank * per * 64), min(D, (self.rank + 1) * per * 64)
+            ptrs = (C.c_void_p * self.world)(*[p + do for p in db.ptrs])
+            call("fedb200_gram_bf16", C.cast(ptrs, C.c_void_p), self.world, P, D, D, lo, hi, self.gram_part.data_ptr(), 0,
+                 torch.cuda.current_stream().cuda_stream)
+            count()
         self.launches += 1
         self.weighted_mean(self.gram_part, 1.0, self.gram_out, inv_total=1.0)
         return self.gram_out.view(n, n)

@@ -159,15 +159,14 @@ class FedRuntime:
             L = len(self.local_ids)
             on_gpu = self.device.type == "cuda"
             if self.deltas is None:
-                self.deltas = self.comm.alloc("deltas", self.P * self.D, torch.bfloat16 if on_gpu else torch.float32
-                                              ).view(self.P, self.D)
+                self.deltas = self.comm.delta_buffer(self.P, self.D, torch.bfloat16 if on_gpu else torch.float32)
             for li in range(L):
                 if on_gpu:
                     from .ops import cuda_ops
-                    cuda_ops.delta_bf16(self.slots[li], self.global_flat, self.deltas[li])
+                    cuda_ops.delta_bf16(self.slots[li], self.global_flat, self.deltas[li][: self.D])
                     self.comm.launches += 1
                 else:
-                    torch.sub(self.slots[li], self.global_flat, out=self.deltas[li])
+                    torch.sub(self.slots[li], self.global_flat, out=self.deltas[li][: self.D])
             g = self.comm.gram(self.deltas, self.N)
             if on_gpu and self.N <= 128:
                 from .ops import cuda_ops

@@ -141,6 +141,10 @@ int fedb200_bert_backward(const fedb200_bert_plan* plan, int T, int B, int max_l
 /* K4. Gram matrix of client updates over a column slice, tcgen05 + TMA straight from (peer) buffers. */
 int fedb200_gram_bf16(const void* const* rows_ptrs, int n_ranks, int rows_per_rank, size_t D, size_t ld,
                       size_t col_begin, size_t col_end, float* out, int max_ctas, void* stream);
+/* Few clients: segment-stacked form (rows cut into segments that fill the 128-row tile).  Buffers are [rows_per_rank, ld]
+ * with ld = nseg_total * seg_len, zero padded; reduces segments [seg_begin, seg_begin + S) of every client. */
+int fedb200_gram_bf16_seg(const void* const* rows_ptrs, int n_ranks, int rows_per_rank, size_t seg_len, int nseg_total,
+                          int seg_begin, int S, float* out, int max_ctas, void* stream);
 /* K5. PageRank power iteration + mean±k·sigma mask (reference: All_graphs_IMDB_dataset.ipynb:168-176). */
 int fedb200_pagerank(const float* mat, int n, int mode, double alpha, double tol, int max_iter, double k_sigma,
                      int low_only, double* ranks, int* mask, double* info, void* stream);

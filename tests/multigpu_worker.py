@@ -56,6 +56,18 @@ def main():
     err = (g - gref).abs().max().item()
     assert err < 2e-3 * gref.abs().max().item() + 1e-3, f"gram err {err}"
 
+    # same through the segment-stacked layout the runtime uses for few clients
+    dseg = comm.delta_buffer(P, D - 8, torch.bfloat16)
+    dseg[:, : D - 8].copy_((torch.randn(P, D - 8, device=dev) * 0.1).bfloat16())
+    g2 = comm.gram(dseg, world * P)
+    allseg = [torch.empty_like(dseg) for _ in range(world)]
+    dist.all_gather(allseg, dseg.contiguous())
+    f2 = torch.cat(allseg, 0).float()
+    torch.cuda.synchronize()
+    comm.check_errors()
+    err = (g2 - f2 @ f2.T).abs().max().item()
+    assert err < 2e-3 * (f2 @ f2.T).abs().max().item() + 1e-3, f"segmented gram err {err}"
+
     # ---- K2 routed mixing: out[i] = sum_j W[i, j] slot_j over peer memory ----------------------------------------
     N, Dm = world * 2, 500_000
     slots = comm.alloc("t_slots", 2 * Dm).view(2, Dm)

@@ -77,6 +77,23 @@ def test_gram_tcgen05(cuda_lib, N, D):
     assert err <= 2e-3 * ref.abs().max().item() + 1e-3, f"gram max err {err}"
 
 
+@pytest.mark.parametrize("N,D", [(2, 300_000), (8, 1_000_003 // 8 * 8), (20, 64 * 1000)])
+def test_gram_segment_stacked_for_few_clients(cuda_lib, N, D):
+    """Few clients: rows are cut into segments stacked in the 128-row tile; same Gram, full-size TMA boxes."""
+    ops = _ops()
+    torch.manual_seed(1)
+    lay = ops.gram_layout(D, 1, N)
+    assert lay["S"] * N <= 128 and lay["S"] >= 4 and lay["D_pad"] >= D
+    d = torch.zeros(N, lay["D_pad"], dtype=torch.bfloat16, device="cuda")
+    d[:, :D] = (torch.randn(N, D, device="cuda") * 0.1).bfloat16()
+    out = torch.zeros(N, N, device="cuda")
+    ops.gram_seg([d.data_ptr()], N, lay, 0, out)
+    ref = d.float() @ d.float().T
+    torch.cuda.synchronize()
+    err = (out - ref).abs().max().item()
+    assert err <= 2e-3 * ref.abs().max().item() + 1e-3, f"segmented gram max err {err}"
+
+
 def test_gram_pagerank_flags_poisoned_update(cuda_lib):
     from fedb200.anomaly import score_updates
     ops = _ops()
