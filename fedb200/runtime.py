@@ -258,9 +258,10 @@ class FedRuntime:
         self.masked = self._score(rnd)
         with self.timer.phase("aggregate"):
             ws = [0.0 if i["peer"] in self.masked else 1.0 for i in infos]          # unweighted mean (:269)
-            if len(ws) == 1 and self.P == 1:
-                # one peer per GPU: its slot IS the rank's accumulator (a masked peer contributes weight 0)
-                self.comm.weighted_mean(self.slots[0], ws[0], self.global_flat)
+            if len(ws) == 1 and self.P == 1 and ws[0] == 1.0:
+                # one unmasked peer per GPU: its slot IS the rank's accumulator (a masked peer takes the general path,
+                # where its accumulator is zero and its weight 0)
+                self.comm.weighted_mean(self.slots[0], 1.0, self.global_flat)
             else:
                 self._local_weighted_sum(ws)
                 self.comm.weighted_mean(self.acc, sum(ws), self.global_flat)         # consensus / global model
