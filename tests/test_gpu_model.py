@@ -227,3 +227,27 @@ def test_fused_runner_interface_and_state_dict(cuda_lib, tmp_path):
     assert list(sd.keys()) == sorted(run.state_dict().keys()) or set(sd.keys()) == set(run.state_dict().keys())
     for k, v in run.state_dict().items():
         torch.testing.assert_close(sd[k], v.cpu())
+
+
+def test_fused_bert_large_shape_matches_torch(cuda_lib):
+    """BERT-large layer shape (H 1024, 16 heads, I 4096) — the 64-peer scale-up config — on two layers."""
+    from fedb200.config import FedConfig, ModelConfig
+    from fedb200.models.fused_bert import FusedRunner
+    from fedb200.models.factory import build_model
+    fed = FedConfig()
+    fed.model = ModelConfig.preset("bert-large", num_labels=2, num_layers=2, vocab_size=4096, hidden_dropout=0.0,
+                                   attention_dropout=0.0)
+    fed.data.batch_size, fed.data.max_seq_len = 8, 384
+    run = FusedRunner(fed.model, fed, "cuda", seed=7)
+    ref = build_model(fed.model, "cuda", seed=7)
+    packed, padded = _batch(fed.model.vocab_size, [100, 384, 129, 17, 256, 300], 2, seed=3)
+    ref.train()
+    out = ref(**{k: v.cuda() for k, v in padded.items()})
+    out.loss.backward()
+    loss = run.train_step(packed, optimizer_step=False)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(run.logits[:6], out.logits, rtol=5e-2, atol=3e-2)
+    gmax = max(p.grad.norm().item() for p in ref.parameters())
+    for k, p in ref.named_parameters():
+        rel = (run.grads.views[k] - p.grad).norm().item() / max(p.grad.norm().item(), 1e-3 * gmax)
+        assert rel < 0.08, f"grad {k}: relative error {rel:.3f}"
