@@ -8,16 +8,18 @@
 
 namespace fedb {
 
-constexpr int LN_MAXV = 4;          // vectors of 8 bf16 per lane -> H <= 1024
+constexpr int LN_MAXV = 4;          // vectors of 8 bf16 per lane -> H <= 1024 (kernels are templated on the count actually needed)
 constexpr int LN_WARPS = 8;
 
+template <int NV>
 struct RowVec {
-    float x[LN_MAXV][8];
+    float x[NV][8];
 };
 
-__device__ __forceinline__ void load_row(const __nv_bfloat16* row, int nvec, int lane, RowVec& r) {
+template <int NV>
+__device__ __forceinline__ void load_row(const __nv_bfloat16* row, int nvec, int lane, RowVec<NV>& r) {
 #pragma unroll
-    for (int i = 0; i < LN_MAXV; ++i) {
+    for (int i = 0; i < NV; ++i) {
         const int v = lane + 32 * i;
         if (v < nvec) {
             const uint4 raw = *reinterpret_cast<const uint4*>(row + v * 8);
@@ -36,16 +38,17 @@ __device__ __forceinline__ void store_vec(__nv_bfloat16* row, int v, const float
     o.z = pack_bf16x2(y[4], y[5]); o.w = pack_bf16x2(y[6], y[7]);
     *reinterpret_cast<uint4*>(row + v * 8) = o;
 }
-__device__ __forceinline__ void row_stats(const RowVec& r, int nvec, int lane, int H, float eps, float& mean, float& rstd) {
+template <int NV>
+__device__ __forceinline__ void row_stats(const RowVec<NV>& r, int nvec, int lane, int H, float eps, float& mean, float& rstd) {
     float s = 0.f;
 #pragma unroll
-    for (int i = 0; i < LN_MAXV; ++i)
+    for (int i = 0; i < NV; ++i)
 #pragma unroll
         for (int k = 0; k < 8; ++k) s += r.x[i][k];
     mean = warp_sum(s) / (float)H;
     float q = 0.f;
 #pragma unroll
-    for (int i = 0; i < LN_MAXV; ++i) {
+    for (int i = 0; i < NV; ++i) {
         if (lane + 32 * i < nvec) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) { const float d = r.x[i][k] - mean; q += d * d; }
@@ -54,6 +57,7 @@ __device__ __forceinline__ void row_stats(const RowVec& r, int nvec, int lane, i
     rstd = rsqrtf(warp_sum(q) / (float)H + eps);
 }
 
+template <int NV>
 __global__ void __launch_bounds__(LN_WARPS * 32) ln_fwd_kernel(const __nv_bfloat16* __restrict__ z,
                                                                const float* __restrict__ gamma,
                                                                const float* __restrict__ beta,
@@ -62,12 +66,12 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_fwd_kernel(const __nv_bfloat
     const int lane = threadIdx.x & 31, nvec = H / 8;
     const int warp = blockIdx.x * LN_WARPS + (threadIdx.x >> 5), nwarps = gridDim.x * LN_WARPS;
     for (int row = warp; row < T; row += nwarps) {
-        RowVec r;
+        RowVec<NV> r;
         load_row(z + (size_t)row * H, nvec, lane, r);
         float mean, rstd;
         row_stats(r, nvec, lane, H, eps, mean, rstd);
 #pragma unroll
-        for (int i = 0; i < LN_MAXV; ++i) {
+        for (int i = 0; i < NV; ++i) {
             const int v = lane + 32 * i;
             if (v < nvec) {
                 float o[8];
@@ -85,7 +89,8 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_fwd_kernel(const __nv_bfloat
 }
 
 // dz = LN'(dy);   df = dz * dropmask (optional);   dgamma += sum dy*xhat;  dbeta += sum dy;  dbias += sum df
-__global__ void __launch_bounds__(LN_WARPS * 32) ln_bwd_kernel(
+template <int NV>
+__global__ void __launch_bounds__(LN_WARPS * 32, (NV <= 2) ? 2 : 1) ln_bwd_kernel(
     const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ z, const float* __restrict__ mean_in,
     const float* __restrict__ rstd_in, const float* __restrict__ gamma, __nv_bfloat16* __restrict__ dz,
     __nv_bfloat16* __restrict__ df, float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dbias,
@@ -93,26 +98,26 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_bwd_kernel(
     extern __shared__ float red[];        // [LN_WARPS][H]
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, nvec = H / 8;
     const int warp = blockIdx.x * LN_WARPS + wib, nwarps = gridDim.x * LN_WARPS;
-    float ag[LN_MAXV][8], ab[LN_MAXV][8], as[LN_MAXV][8];
+    float ag[NV][8], ab[NV][8], as[NV][8];
 #pragma unroll
-    for (int i = 0; i < LN_MAXV; ++i)
+    for (int i = 0; i < NV; ++i)
 #pragma unroll
         for (int k = 0; k < 8; ++k) ag[i][k] = ab[i][k] = as[i][k] = 0.f;
-    float gg[LN_MAXV][8];
+    float gg[NV][8];
 #pragma unroll
-    for (int i = 0; i < LN_MAXV; ++i) {
+    for (int i = 0; i < NV; ++i) {
         const int v = lane + 32 * i;
 #pragma unroll
         for (int k = 0; k < 8; ++k) gg[i][k] = v < nvec ? gamma[v * 8 + k] : 0.f;
     }
     for (int row = warp; row < T; row += nwarps) {
-        RowVec x, g;
+        RowVec<NV> x, g;
         load_row(z + (size_t)row * H, nvec, lane, x);
         load_row(dy + (size_t)row * H, nvec, lane, g);
         const float mean = mean_in[row], rstd = rstd_in[row];
         float s1 = 0.f, s2 = 0.f;
 #pragma unroll
-        for (int i = 0; i < LN_MAXV; ++i) {
+        for (int i = 0; i < NV; ++i) {
             if (lane + 32 * i < nvec) {
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
@@ -128,7 +133,7 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_bwd_kernel(
         }
         const float c1 = warp_sum(s1) / (float)H, c2 = warp_sum(s2) / (float)H;
 #pragma unroll
-        for (int i = 0; i < LN_MAXV; ++i) {
+        for (int i = 0; i < NV; ++i) {
             const int v = lane + 32 * i;
             if (v < nvec) {
                 float o[8];
@@ -153,7 +158,7 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_bwd_kernel(
         if (outs[q] == nullptr) continue;
         __syncthreads();
 #pragma unroll
-        for (int i = 0; i < LN_MAXV; ++i) {
+        for (int i = 0; i < NV; ++i) {
             const int v = lane + 32 * i;
             if (v < nvec) {
 #pragma unroll
@@ -184,8 +189,11 @@ extern "C" int fedb200_layernorm_fwd(const void* z, const float* gamma, const fl
                                      float* rstd, int T, int H, float eps, void* stream) {
     FEDB_REQUIRE(H % 8 == 0 && H <= 8 * 32 * LN_MAXV, "layernorm: H=%d must be a multiple of 8 and <= 1024", H);
     if (T <= 0) return 0;
-    ln_fwd_kernel<<<ln_grid(T), LN_WARPS * 32, 0, (cudaStream_t)stream>>>(
-        (const __nv_bfloat16*)z, gamma, beta, (__nv_bfloat16*)y, mean, rstd, T, H, eps);
+    const int nv = (H / 8 + 31) / 32;
+#define FEDB_LN_FWD(NVV) ln_fwd_kernel<NVV><<<ln_grid(T), LN_WARPS * 32, 0, (cudaStream_t)stream>>>( \
+        (const __nv_bfloat16*)z, gamma, beta, (__nv_bfloat16*)y, mean, rstd, T, H, eps)
+    if (nv == 1) FEDB_LN_FWD(1); else if (nv == 2) FEDB_LN_FWD(2); else if (nv == 3) FEDB_LN_FWD(3); else FEDB_LN_FWD(4);
+#undef FEDB_LN_FWD
     FEDB_LAUNCH_CHECK();
     return 0;
 }
@@ -201,9 +209,13 @@ extern "C" int fedb200_layernorm_bwd(const void* dy, const void* z, const float*
     if (dropout_p <= 0.f) df = nullptr;
     int blocks = ln_grid(T);
     if (blocks > sm_count() * 2) blocks = sm_count() * 2;
-    ln_bwd_kernel<<<blocks, LN_WARPS * 32, LN_WARPS * H * sizeof(float), (cudaStream_t)stream>>>(
-        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)z, mean, rstd, gamma, (__nv_bfloat16*)dz, (__nv_bfloat16*)df,
-        dgamma, dbeta, dbias, T, H, seed, thresh, 1.0f / keep);
+    const int nv = (H / 8 + 31) / 32;
+    if (nv <= 2 && blocks < ln_grid(T)) blocks = ln_grid(T) < sm_count() * 4 ? ln_grid(T) : sm_count() * 4;   // two blocks per SM fit
+#define FEDB_LN_BWD(NVV) ln_bwd_kernel<NVV><<<blocks, LN_WARPS * 32, LN_WARPS * H * sizeof(float), (cudaStream_t)stream>>>( \
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)z, mean, rstd, gamma, (__nv_bfloat16*)dz, (__nv_bfloat16*)df, \
+        dgamma, dbeta, dbias, T, H, seed, thresh, 1.0f / keep)
+    if (nv == 1) FEDB_LN_BWD(1); else if (nv == 2) FEDB_LN_BWD(2); else if (nv == 3) FEDB_LN_BWD(3); else FEDB_LN_BWD(4);
+#undef FEDB_LN_BWD
     FEDB_LAUNCH_CHECK();
     return 0;
 }
