@@ -128,7 +128,7 @@ def kernel_round(rt, staged, gtest):
             rt.slots[li].copy_(run.flat)
         run.evaluate_packed(*test_b)                    # local evaluation of the trained peer (results stay on device)
         ws.append(1.0)
-    if len(ws) == 1 and rt.P == 1:
+    if rt.P == 1 and rt.N == rt.world:
         rt.comm.weighted_mean(rt.slots[0], 1.0, rt.global_flat)
     else:
         rt._local_weighted_sum(ws)

@@ -152,6 +152,7 @@ def build_parser(defaults: Optional[FedConfig] = None, description: str = "") ->
     p.add_argument("--async", dest="asynchronous", action="store_true", default=d.asynchronous)
     p.add_argument("--async-scheduled", action="store_true", default=d.async_scheduled)
     p.add_argument("--async-fanout", type=int, default=d.async_fanout)
+    p.add_argument("--async-epoch-s", type=float, default=d.async_epoch_s)
     p.add_argument("--topology", default=d.topology)
     p.add_argument("--no-route-optimizer", dest="route_optimizer", action="store_false", default=d.route_optimizer)
     p.add_argument("--anomaly-detector", default=d.anomaly_detector)
@@ -186,7 +187,7 @@ def config_from_args(args: argparse.Namespace, defaults: Optional[FedConfig] = N
     cfg.num_clients, cfg.num_rounds, cfg.lr = args.clients, args.rounds, args.lr
     cfg.device, cfg.backend, cfg.comm = args.device, args.backend, args.comm
     cfg.serverless_semantics, cfg.asynchronous = args.semantics, args.asynchronous
-    cfg.async_scheduled, cfg.async_fanout = args.async_scheduled, args.async_fanout
+    cfg.async_scheduled, cfg.async_fanout, cfg.async_epoch_s = args.async_scheduled, args.async_fanout, args.async_epoch_s
     cfg.topology, cfg.route_optimizer = args.topology, args.route_optimizer
     cfg.anomaly_detector, cfg.inject_anomalies, cfg.inject_kind = (
         args.anomaly_detector, args.inject_anomalies, args.inject_kind)

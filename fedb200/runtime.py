@@ -65,6 +65,11 @@ class FedRuntime:
         self.timer = PhaseTimer(self.device.type == "cuda")
         self.topo = Topology.from_name(cfg.topology, self.N, cfg.seed)
         self.injector = AnomalyInjector(self.N, cfg.inject_anomalies, cfg.inject_kind, seed=cfg.seed)
+        if cfg.inject_kind == "slowlink" and cfg.inject_anomalies > 0:
+            # network-level fault: the targets' channels run at 5 % bandwidth; the graph detectors see it in the
+            # topology (the reference's anomaly notion: a node whose channel bandwidths are off)
+            self.topo = self.topo.slow_links(self.injector.targets(), 0.05)
+            self.injector.count = 0                      # no weight corruption for this kind
         self.ledger = Ledger(chunk_bytes=4096) if cfg.ledger else None
         self.strategy = FedAvg(fraction_fit=1.0, fraction_evaluate=1.0,
                                evaluate_metrics_aggregation_fn=weighted_average, seed=cfg.seed)
@@ -258,9 +263,9 @@ class FedRuntime:
         self.masked = self._score(rnd)
         with self.timer.phase("aggregate"):
             ws = [0.0 if i["peer"] in self.masked else 1.0 for i in infos]          # unweighted mean (:269)
-            if len(ws) == 1 and self.P == 1 and ws[0] == 1.0:
-                # one unmasked peer per GPU: its slot IS the rank's accumulator (a masked peer takes the general path,
-                # where its accumulator is zero and its weight 0)
+            if self.P == 1 and self.N == self.world and not self.masked:
+                # one peer per GPU and nobody masked anywhere: the slot IS the rank's accumulator.  Every rank must take
+                # the same branch — the fused reduce reads the SAME symmetric buffer on all peers.
                 self.comm.weighted_mean(self.slots[0], 1.0, self.global_flat)
             else:
                 self._local_weighted_sum(ws)
