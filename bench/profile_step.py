@@ -15,6 +15,7 @@ ap.add_argument("--warmup", type=int, default=3)
 ap.add_argument("--model", default="biobert")
 ap.add_argument("--dropout", type=float, default=0.1)
 ap.add_argument("--full-len", action="store_true", help="every sequence at 512 tokens")
+ap.add_argument("--batch", type=int, default=32)
 a = ap.parse_args()
 fed = FedConfig()
 fed.model = ModelConfig.preset(a.model, num_labels=2, hidden_dropout=a.dropout, attention_dropout=a.dropout)
@@ -24,7 +25,7 @@ if a.full_len:
     from fedb200.data.dataset import TokenDataset
     rng = np.random.default_rng(0)
     ds = TokenDataset.from_sequences([rng.integers(1000, 20000, size=512) for _ in range(32)], rng.integers(0, 2, size=32), 2)
-batch = collate_packed(ds, np.arange(32))
+batch = collate_packed(ds, np.arange(a.batch))
 dev_batch = {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in batch.items()}
 print("tokens", batch["num_tokens"], "max_len", batch["max_len"])
 for _ in range(a.warmup):

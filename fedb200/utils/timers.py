@@ -48,10 +48,12 @@ class PhaseTimer:
         if self.use_cuda:
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
+            torch.cuda.nvtx.range_push(name)          # NVTX range: phases show up in nsys / ncu timelines
         try:
             yield
         finally:
             if self.use_cuda:
+                torch.cuda.nvtx.range_pop()
                 b.record()
                 self._pending[name].append((a, b))
             self.wall[name] += (time.perf_counter() - t0) * 1e3

@@ -192,3 +192,17 @@ def test_ledger_chain_validation_and_tamper_detection(tmp_path):
     pow_led = Ledger(chunk_bytes=64, difficulty_bits=8)
     blk = pow_led.record_update(0, 0, 1, xs[0].tobytes())
     assert blk.hash()[0] == 0 and pow_led.validate() == -1
+
+
+def test_report_tables_match_detectors_and_timing_model(tmp_path):
+    from fedb200.utils import info_passing_table, sweep_table, write_csv
+    rows = info_passing_table()
+    by = {r["detector"]: r for r in rows}
+    assert by["pagerank"]["removed"] == [0, 4, 7, 9] and by["modz"]["removed"] == [8, 9] and by["dbscan"]["removed"] == []
+    assert all(r["async_s"] <= r["sync_s"] for r in rows)
+    assert by["pagerank"]["sync_s"] < by["none"]["sync_s"]          # fewer destinations after elimination
+    assert all(r["async_saving_pct"] > 50 for r in rows)            # async = max << sync = sum (README: -76 %)
+    write_csv(rows, str(tmp_path / "t.csv"))
+    assert (tmp_path / "t.csv").read_text().startswith("detector,removed,source,sync_s,async_s")
+    sw = sweep_table({5: {"latency_min": 1.0, "global_accuracies": [0.5, 0.6]}, 10: {"latency_min": 2.0, "global_accuracies": [0.7]}})
+    assert [r["workers"] for r in sw] == [5, 10] and sw[0]["final_accuracy"] == 0.6
