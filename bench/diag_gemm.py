@@ -52,7 +52,8 @@ if __name__ == "__main__":
       _lib.lib().fedb200_set_gemm_mode(mode)
       for T in T_list:
         print(f"--- gemm mode {mode} (0 auto/pairs, 1 single-CTA), tokens {T}")
-        for name, layout, M, N, K, epi, splits in [("fwd qkv", 0, T, 2304, 768, ops.EPI_BIAS, 1), ("fwd ffn-up", 0, T, 3072, 768, ops.EPI_BIAS, 1),
+        for name, layout, M, N, K, epi, splits in [("fwd qkv NO-EPILOGUE", 0, T, 2304, 768, 6, 1), ("fwd ffn-down NO-EPILOGUE", 0, T, 768, 3072, 6, 1),
+                                                   ("fwd ffn-up NO-EPILOGUE", 0, T, 3072, 768, 6, 1), ("fwd qkv", 0, T, 2304, 768, ops.EPI_BIAS, 1), ("fwd ffn-up", 0, T, 3072, 768, ops.EPI_BIAS, 1),
                                                    ("fwd ffn-down", 0, T, 768, 3072, ops.EPI_BIAS, 1), ("dgrad ffn-down", 1, T, 3072, 768, ops.EPI_ADD, 1),
                                                    ("fwd attn-out", 0, T, 768, 768, ops.EPI_BIAS, 1), ("dgrad qkv", 1, T, 768, 2304, ops.EPI_ADD, 1),
                                                    ("wgrad ffn-up", 2, 3072, 768, T, ops.EPI_ATOMIC_F32, 2), ("wgrad attn-out", 2, 768, 768, T, ops.EPI_ATOMIC_F32, 8)]:

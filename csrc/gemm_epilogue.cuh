@@ -103,7 +103,9 @@ __device__ __forceinline__ void gemm_epilogue_tile(const GemmParams& p, uint32_t
             float v[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = (has_k ? __uint_as_float(raw[j]) : 0.f) + bv[j];
-            if (p.epi == FEDB200_EPI_ATOMIC_F32) {
+            if (p.epi == FEDB200_EPI_DISCARD) {
+                if (v[0] == 123456.789f) reinterpret_cast<float*>(p.out)[0] = v[1];      // never true: keeps the loads alive
+            } else if (p.epi == FEDB200_EPI_ATOMIC_F32) {
                 float* o = reinterpret_cast<float*>(p.out) + (size_t)row * p.ldo + col0;
 #pragma unroll
                 for (int q = 0; q < 8; ++q)

@@ -201,7 +201,7 @@ extern "C" int fedb200_gemm_bf16(int layout, const void* A, int lda, const void*
     FEDB_REQUIRE(layout >= 0 && layout <= 2, "gemm: layout %d", layout);
     FEDB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
     FEDB_REQUIRE(N % 8 == 0 && ldo % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0, "gemm: N, ldo, lda, ldb must be multiples of 8");
-    FEDB_REQUIRE(epi >= 0 && epi <= FEDB200_EPI_ATOMIC_F32, "gemm: epilogue %d", epi);
+    FEDB_REQUIRE(epi >= 0 && epi <= FEDB200_EPI_DISCARD, "gemm: epilogue %d", epi);
     FEDB_REQUIRE(((uintptr_t)out & 15) == 0 && ((uintptr_t)out2 & 15) == 0 && ((uintptr_t)aux & 15) == 0 && ld_aux % 8 == 0,
                  "gemm: out/out2/aux must be 16-byte aligned");
     if (epi == FEDB200_EPI_BIAS_DROP_RES || epi == FEDB200_EPI_MUL_GELU_GRAD) FEDB_REQUIRE(aux != nullptr, "gemm: epilogue needs aux");

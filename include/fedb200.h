@@ -26,6 +26,7 @@ extern "C" {
 #define FEDB200_EPI_MUL_GELU_GRAD 3 /* out = acc * gelu'(aux)                            (dgrad through GELU)    */
 #define FEDB200_EPI_ADD 4           /* out = acc (+ aux)                                 (dgrad + residual grad) */
 #define FEDB200_EPI_ATOMIC_F32 5    /* out_f32 += acc (split-K)                          (wgrad)                 */
+#define FEDB200_EPI_DISCARD 6       /* drain TMEM, store nothing (profiling only: isolates the mainloop)          */
 
 const char* fedb200_last_error(void);
 int fedb200_abi_version(void);
