@@ -53,6 +53,7 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attn_fwd_kernel(const __grid_co
                                                                  float scale_log2, uint64_t seed, uint32_t keep_thresh,
                                                                  float inv_keep, int use_dropout,
                                                                  uint32_t* __restrict__ drop_bits, int bits_stride) {
+    pdl_sync();
     const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * 128;
     const int tok0 = cu_seqlens[b], len = cu_seqlens[b + 1] - tok0;
     if (q0 >= len) return;
@@ -239,6 +240,7 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attn_fwd_kernel(const __grid_co
 // delta[h*T + tok] = sum_d dctx[tok, h*64 + d] * ctx[tok, h*64 + d]
 __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __restrict__ ctx, const __nv_bfloat16* __restrict__ dctx,
                                                          float* __restrict__ delta, int T, int heads) {
+    pdl_sync();
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= T * heads) return;
     const int tok = idx / heads, h = idx % heads;
@@ -264,6 +266,7 @@ __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __
 __global__ void __launch_bounds__(256) attn_bwd_finish_kernel(const __nv_bfloat16* __restrict__ dq_part, __nv_bfloat16* __restrict__ dqkv,
                                                               float* __restrict__ dbias, const int* __restrict__ cu_seqlens,
                                                               int T, int H) {
+    pdl_sync();
     __shared__ float2 red[8][32];
     const int col = (blockIdx.x * 32 + threadIdx.x) * 2;          // column within [0, 3H)
     const int s0 = cu_seqlens[blockIdx.y], s1 = cu_seqlens[blockIdx.y + 1];
@@ -314,6 +317,7 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
                                                                  float scale, float scale_log2, uint64_t seed,
                                                                  uint32_t keep_thresh, float inv_keep, int use_dropout,
                                                                  const uint32_t* __restrict__ drop_bits, int bits_stride) {
+    pdl_sync();
     const int b = blockIdx.z, h = blockIdx.y, kv0 = blockIdx.x * 128;
     const int tok0 = cu_seqlens[b], len = cu_seqlens[b + 1] - tok0;
     if (kv0 >= len) return;
@@ -532,10 +536,9 @@ extern "C" int fedb200_attn_fwd(const void* qkv, void* ctx, float* lse, const in
         configured = true;
     }
     dim3 grid((max_seqlen + 127) / 128, heads, B);
-    attn_fwd_kernel<<<grid, AT_THREADS, smem, (cudaStream_t)stream>>>(
+    FEDB_CHECK(launch_pdl(attn_fwd_kernel, dim3(grid), dim3(AT_THREADS), smem, (cudaStream_t)stream, 
         tm, (__nv_bfloat16*)ctx, lse, cu_seqlens, T, H, scale * LOG2E, seed, dropout_thresh16(dropout_p),
-        1.0f / (1.0f - dropout_p), dropout_p > 0.f, (uint32_t*)drop_bits, (max_seqlen + 31) / 32);
-    FEDB_LAUNCH_CHECK();
+        1.0f / (1.0f - dropout_p), dropout_p > 0.f, (uint32_t*)drop_bits, (max_seqlen + 31) / 32));
     return 0;
 }
 
@@ -551,8 +554,7 @@ extern "C" int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dc
     if (e) return e;
     e = make_tmap_bf16_2d(&tmdo, dctx, (uint64_t)T, (uint64_t)H, (uint64_t)H, 128, 64);
     if (e) return e;
-    attn_delta_kernel<<<(T * heads + 255) / 256, 256, 0, s>>>((const __nv_bfloat16*)ctx, (const __nv_bfloat16*)dctx, delta, T, heads);
-    FEDB_LAUNCH_CHECK();
+    FEDB_CHECK(launch_pdl(attn_delta_kernel, dim3((T * heads + 255) / 256), dim3(256), 0, s, (const __nv_bfloat16*)ctx, (const __nv_bfloat16*)dctx, delta, T, heads));
     const size_t smem = 10 * AT_TILE + 1024;
     static bool configured = false;
     if (!configured) {
@@ -560,13 +562,11 @@ extern "C" int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dc
         configured = true;
     }
     dim3 grid((max_seqlen + 127) / 128, heads, B);
-    attn_bwd_kernel<<<grid, ATB_THREADS, smem, s>>>(tm, tmdo, lse, delta, (__nv_bfloat16*)dqkv, dq_accum, cu_seqlens, T, H,
+    FEDB_CHECK(launch_pdl(attn_bwd_kernel, dim3(grid), dim3(ATB_THREADS), smem, s, tm, tmdo, lse, delta, (__nv_bfloat16*)dqkv, dq_accum, cu_seqlens, T, H,
                                                    scale, scale * LOG2E, seed, dropout_thresh16(dropout_p),
                                                    1.0f / (1.0f - dropout_p), dropout_p > 0.f, (const uint32_t*)drop_bits,
-                                                   (max_seqlen + 31) / 32);
-    FEDB_LAUNCH_CHECK();
-    attn_bwd_finish_kernel<<<dim3((3 * H + 63) / 64, B, (max_seqlen + 63) / 64), dim3(32, 8), 0, s>>>(
-        (const __nv_bfloat16*)dq_accum, (__nv_bfloat16*)dqkv, dbias_qkv, cu_seqlens, T, H);
-    FEDB_LAUNCH_CHECK();
+                                                   (max_seqlen + 31) / 32));
+    FEDB_CHECK(launch_pdl(attn_bwd_finish_kernel, dim3(dim3((3 * H + 63) / 64, B, (max_seqlen + 63) / 64)), dim3(dim3(32, 8)), 0, s, 
+        (const __nv_bfloat16*)dq_accum, (__nv_bfloat16*)dqkv, dbias_qkv, cu_seqlens, T, H));
     return 0;
 }

@@ -39,6 +39,35 @@ void set_last_error(const char* fmt, ...);
 int sm_count();   // cached multiprocessor count of the current device
 
 // ---------------------------------------------------------------------------------------------
+// programmatic dependent launch (PDL)
+//   A kernel launched through launch_pdl() may be scheduled while its predecessor on the stream is still
+//   draining; it must execute pdl_wait() before its first global-memory access.  pdl_trigger() lets the NEXT kernel's
+//   CTAs be scheduled as soon as every CTA of this one has reached it (they then park in their own pdl_wait()).
+//   Both instructions are no-ops for a normal launch, so the same kernel works either way.
+// ---------------------------------------------------------------------------------------------
+int pdl_enabled();   // runtime.cu: FEDB200_PDL env (default on) / fedb200_set_pdl()
+
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_sync() { pdl_wait(); pdl_trigger(); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                              Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
+// ---------------------------------------------------------------------------------------------
 // small device utilities
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {

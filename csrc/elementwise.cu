@@ -22,6 +22,7 @@ __global__ void __launch_bounds__(256) adamw_flat_kernel(float* __restrict__ p, 
                                                          __nv_bfloat16* __restrict__ shadow, size_t n4, size_t n,
                                                          float step_size, float b1, float b2, float eps,
                                                          float lr_wd, float gscale, int zero_grad) {
+    pdl_sync();
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
         float4 pp = reinterpret_cast<float4*>(p)[i];
@@ -71,6 +72,7 @@ struct MixArgs {
 template <int UNROLL>
 __global__ void __launch_bounds__(256) mix_n_kernel(MixArgs a, float* __restrict__ out,
                                                     __nv_bfloat16* __restrict__ shadow, size_t n4, size_t n) {
+    pdl_sync();
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -111,6 +113,7 @@ __global__ void __launch_bounds__(256) mix_n_kernel(MixArgs a, float* __restrict
 // a warp-row covers 64 contiguous columns (bf16x2 per lane); rows are strided over y and blockIdx.y.
 __global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out,
                                                           int M, int N, int ld, int rows_per_block) {
+    pdl_sync();
     __shared__ float2 red[8][32];
     const int col = (blockIdx.x * 32 + threadIdx.x) * 2;
     const int r0 = blockIdx.y * rows_per_block;
@@ -135,6 +138,7 @@ __global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* _
 
 __global__ void __launch_bounds__(256) cast_f32_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out,
                                                             size_t n4, size_t n) {
+    pdl_sync();
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
         const float4 t = reinterpret_cast<const float4*>(in)[i];
@@ -150,6 +154,7 @@ __global__ void __launch_bounds__(256) cast_f32_bf16_kernel(const float* __restr
 // delta_bf16 = a - b (fp32 in), the operand of the cosine-Gram scorer
 __global__ void __launch_bounds__(256) delta_bf16_kernel(const float* __restrict__ a, const float* __restrict__ b,
                                                          __nv_bfloat16* __restrict__ out, size_t n4, size_t n) {
+    pdl_sync();
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
         const float4 x = __ldcs(reinterpret_cast<const float4*>(a) + i);
@@ -176,10 +181,9 @@ extern "C" int fedb200_adamw_flat(float* p, float* g, float* m, float* v, void* 
     const double bc1 = 1.0 - pow((double)beta1, step), bc2 = 1.0 - pow((double)beta2, step);
     const float step_size = (float)((double)lr * sqrt(bc2) / bc1);
     const size_t n4 = n / 4;
-    adamw_flat_kernel<<<stream_grid(n4 ? n4 : 1, 256, 8), 256, 0, (cudaStream_t)stream>>>(
+    FEDB_CHECK(launch_pdl(adamw_flat_kernel, dim3(stream_grid(n4 ? n4 : 1, 256, 8)), dim3(256), 0, (cudaStream_t)stream, 
         p, g, m, v, (__nv_bfloat16*)shadow_bf16, n4, n, step_size, beta1, beta2, eps, lr * weight_decay, grad_scale,
-        zero_grad);
-    FEDB_LAUNCH_CHECK();
+        zero_grad));
     return 0;
 }
 
@@ -196,9 +200,8 @@ extern "C" int fedb200_mix_n(const float* const* srcs, const float* weights, int
     }
     FEDB_REQUIRE(((uintptr_t)out & 15) == 0, "mix_n: out not 16-byte aligned");
     const size_t n4 = n / 4;
-    mix_n_kernel<4><<<stream_grid(n4 ? n4 : 1, 256, 8), 256, 0, (cudaStream_t)stream>>>(
-        a, out, (__nv_bfloat16*)shadow_bf16, n4, n);
-    FEDB_LAUNCH_CHECK();
+    FEDB_CHECK(launch_pdl(mix_n_kernel<4>, dim3(stream_grid(n4 ? n4 : 1, 256, 8)), dim3(256), 0, (cudaStream_t)stream, 
+        a, out, (__nv_bfloat16*)shadow_bf16, n4, n));
     return 0;
 }
 
@@ -210,24 +213,21 @@ extern "C" int fedb200_colsum_bf16(const void* x, float* out, int M, int N, int 
     if (row_blocks > (M + 63) / 64) row_blocks = (M + 63) / 64;
     if (row_blocks < 1) row_blocks = 1;
     const int rpb = (M + row_blocks - 1) / row_blocks;
-    colsum_bf16_kernel<<<dim3(col_blocks, row_blocks), dim3(32, 8), 0, (cudaStream_t)stream>>>(
-        (const __nv_bfloat16*)x, out, M, N, ld, rpb);
-    FEDB_LAUNCH_CHECK();
+    FEDB_CHECK(launch_pdl(colsum_bf16_kernel, dim3(dim3(col_blocks, row_blocks)), dim3(dim3(32, 8)), 0, (cudaStream_t)stream, 
+        (const __nv_bfloat16*)x, out, M, N, ld, rpb));
     return 0;
 }
 
 extern "C" int fedb200_cast_f32_bf16(const float* in, void* out, size_t n, void* stream) {
     const size_t n4 = (((uintptr_t)in & 15) == 0 && ((uintptr_t)out & 7) == 0) ? n / 4 : 0;
-    cast_f32_bf16_kernel<<<stream_grid(n4 ? n4 : n, 256, 8), 256, 0, (cudaStream_t)stream>>>(
-        in, (__nv_bfloat16*)out, n4, n);
-    FEDB_LAUNCH_CHECK();
+    FEDB_CHECK(launch_pdl(cast_f32_bf16_kernel, dim3(stream_grid(n4 ? n4 : n, 256, 8)), dim3(256), 0, (cudaStream_t)stream, 
+        in, (__nv_bfloat16*)out, n4, n));
     return 0;
 }
 
 extern "C" int fedb200_delta_bf16(const float* a, const float* b, void* out, size_t n, void* stream) {
     const size_t n4 = ((((uintptr_t)a | (uintptr_t)b) & 15) == 0 && ((uintptr_t)out & 7) == 0) ? n / 4 : 0;
-    delta_bf16_kernel<<<stream_grid(n4 ? n4 : n, 256, 8), 256, 0, (cudaStream_t)stream>>>(
-        a, b, (__nv_bfloat16*)out, n4, n);
-    FEDB_LAUNCH_CHECK();
+    FEDB_CHECK(launch_pdl(delta_bf16_kernel, dim3(stream_grid(n4 ? n4 : n, 256, 8)), dim3(256), 0, (cudaStream_t)stream, 
+        a, b, (__nv_bfloat16*)out, n4, n));
     return 0;
 }

@@ -26,6 +26,7 @@ __global__ void __launch_bounds__(EM_WARPS * 32) embed_fwd_kernel(
     const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ out,
     float* __restrict__ mean_out, float* __restrict__ rstd_out, int T, int H, float eps, uint64_t seed,
     uint32_t keep_thresh, float inv_keep, int use_dropout) {
+    pdl_sync();
     const int lane = threadIdx.x & 31, nvec = H / 8;
     const int warp = blockIdx.x * EM_WARPS + (threadIdx.x >> 5), nwarps = gridDim.x * EM_WARPS;
     for (int row = warp; row < T; row += nwarps) {
@@ -77,6 +78,7 @@ __global__ void __launch_bounds__(EM_WARPS * 32) embed_bwd_kernel(
     const float* __restrict__ rstd_in, float* __restrict__ gword, float* __restrict__ gpos, float* __restrict__ gtype,
     float* __restrict__ dgamma, float* __restrict__ dbeta, int T, int H, uint64_t seed, uint32_t keep_thresh,
     float inv_keep, int use_dropout) {
+    pdl_sync();
     extern __shared__ float red[];        // [EM_WARPS][H]
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, nvec = H / 8;
     const int warp = blockIdx.x * EM_WARPS + wib, nwarps = gridDim.x * EM_WARPS;
@@ -173,10 +175,9 @@ extern "C" int fedb200_embed_fwd(const int* ids, const int* pos, const int* tt, 
     int blocks = (T + EM_WARPS - 1) / EM_WARPS;
     const int cap = sm_count() * 4;
     if (blocks > cap) blocks = cap;
-    embed_fwd_kernel<<<blocks, EM_WARPS * 32, 0, (cudaStream_t)stream>>>(
+    FEDB_CHECK(launch_pdl(embed_fwd_kernel, dim3(blocks), dim3(EM_WARPS * 32), 0, (cudaStream_t)stream, 
         ids, pos, tt, word, posw, typew, gamma, beta, (__nv_bfloat16*)out, mean, rstd, T, H, eps, seed, th, ik,
-        dropout_p > 0.f);
-    FEDB_LAUNCH_CHECK();
+        dropout_p > 0.f));
     return 0;
 }
 
@@ -193,9 +194,8 @@ extern "C" int fedb200_embed_bwd(const void* dx, const int* ids, const int* pos,
     int blocks = (T + EM_WARPS - 1) / EM_WARPS;
     const int cap = sm_count() * 2;
     if (blocks > cap) blocks = cap;
-    embed_bwd_kernel<<<blocks, EM_WARPS * 32, EM_WARPS * H * sizeof(float), (cudaStream_t)stream>>>(
+    FEDB_CHECK(launch_pdl(embed_bwd_kernel, dim3(blocks), dim3(EM_WARPS * 32), EM_WARPS * H * sizeof(float), (cudaStream_t)stream, 
         (const __nv_bfloat16*)dx, ids, pos, tt, word, posw, typew, gamma, mean, rstd, gword, gpos, gtype, dgamma,
-        dbeta, T, H, seed, th, ik, dropout_p > 0.f);
-    FEDB_LAUNCH_CHECK();
+        dbeta, T, H, seed, th, ik, dropout_p > 0.f));
     return 0;
 }

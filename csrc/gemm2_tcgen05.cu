@@ -62,6 +62,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) gemm2_tcgen05_kernel(const __gr
     if (warp == 1) tmem_alloc_pair(&tmem_base_slot, Cfg::TMEM_COLS);
     tc_fence_before_sync();
     cluster_sync_all();                                     // barriers + TMEM of BOTH CTAs are ready
+    pdl_sync();                                             // everything above overlaps the previous kernel's tail
     tc_fence_after_sync();
     const uint32_t tmem_base = tmem_base_slot;
 
@@ -172,13 +173,15 @@ static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const Gemm
     cfg.blockDim = dim3(G2_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = s;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = pdl_enabled() ? 2 : 1;
     FEDB_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p));
     return 0;
 }

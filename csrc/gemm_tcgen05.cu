@@ -59,6 +59,7 @@ __global__ void __launch_bounds__(GM_THREADS, 1) gemm_tcgen05_kernel(const __gri
     if (warp == 1) tmem_alloc(&tmem_base_slot, TMEM_COLS);
     tc_fence_before_sync();
     __syncthreads();
+    pdl_sync();                                             // everything above overlaps the previous kernel's tail
     tc_fence_after_sync();
     const uint32_t tmem_base = tmem_base_slot;
 
@@ -164,8 +165,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
     int cap = sm_count();
     if (max_ctas > 0 && cap > max_ctas) cap = max_ctas;
     if (grid > cap) grid = cap;
-    kern<<<grid, GM_THREADS, smem, s>>>(ta, tb, p);
-    FEDB_LAUNCH_CHECK();
+    FEDB_CHECK(launch_pdl(kern, dim3(grid), dim3(GM_THREADS), smem, s, ta, tb, p));
     return 0;
 }
 

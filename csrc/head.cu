@@ -13,6 +13,7 @@ __global__ void __launch_bounds__(256) head_pool_kernel(const __nv_bfloat16* __r
                                                         float* __restrict__ pooled, float* __restrict__ pooled_drop,
                                                         int H, uint64_t seed, uint32_t keep_thresh, float inv_keep,
                                                         int use_dropout) {
+    pdl_sync();
     const int b = blockIdx.x, lane = threadIdx.x & 31;
     const int o = blockIdx.y * 8 + (threadIdx.x >> 5);
     if (o >= H) return;
@@ -39,6 +40,7 @@ __global__ void __launch_bounds__(128) head_cls_kernel(const float* __restrict__
                                                        float* __restrict__ logits, float* __restrict__ loss,
                                                        int* __restrict__ pred, float* __restrict__ dlogits, int H, int C,
                                                        float grad_scale) {
+    pdl_sync();
     extern __shared__ float sl[];      // [C]
     const int b = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int c = warp; c < C; c += 4) {
@@ -72,6 +74,7 @@ __global__ void __launch_bounds__(128) head_bwd_cls_kernel(const float* __restri
                                                            float* __restrict__ gWc, float* __restrict__ gbc,
                                                            float* __restrict__ dpre, int B, int H, int C, uint64_t seed,
                                                            uint32_t keep_thresh, float inv_keep, int use_dropout) {
+    pdl_sync();
     const int h = blockIdx.x * blockDim.x + threadIdx.x;
     if (h < H) {
         for (int c = 0; c < C; ++c) {
@@ -100,6 +103,7 @@ __global__ void __launch_bounds__(128) head_bwd_cls_kernel(const float* __restri
 __global__ void __launch_bounds__(256) head_bwd_pool_w_kernel(const float* __restrict__ dpre, const __nv_bfloat16* __restrict__ x,
                                                               const int* __restrict__ first, float* __restrict__ gWp,
                                                               float* __restrict__ gbp, int B, int H) {
+    pdl_sync();
     extern __shared__ float sd[];      // dpre[:, o]
     const int o = blockIdx.x;
     for (int b = threadIdx.x; b < B; b += blockDim.x) sd[b] = dpre[(size_t)b * H + o];
@@ -120,6 +124,7 @@ __global__ void __launch_bounds__(256) head_bwd_pool_w_kernel(const float* __res
 __global__ void __launch_bounds__(256) head_bwd_pool_x_kernel(const float* __restrict__ dpre, const float* __restrict__ Wp,
                                                               const int* __restrict__ first, __nv_bfloat16* __restrict__ dx,
                                                               int H) {
+    pdl_sync();
     extern __shared__ float sd[];      // dpre[b, :]
     const int b = blockIdx.x;
     for (int o = threadIdx.x; o < H; o += blockDim.x) sd[o] = dpre[(size_t)b * H + o];
@@ -144,12 +149,10 @@ extern "C" int fedb200_head_fwd(const void* x, const int* first_tok, const float
     if (B <= 0) return 0;
     const float keep = 1.0f - dropout_p;
     const uint32_t th = dropout_thresh16(dropout_p);
-    head_pool_kernel<<<dim3(B, (H + 7) / 8), 256, 0, (cudaStream_t)stream>>>(
-        (const __nv_bfloat16*)x, first_tok, Wp, bp, pooled, pooled_drop, H, seed, th, 1.0f / keep, dropout_p > 0.f);
-    FEDB_LAUNCH_CHECK();
-    head_cls_kernel<<<B, 128, C * sizeof(float), (cudaStream_t)stream>>>(pooled_drop, Wc, bc, labels, logits, loss, pred,
-                                                                       dlogits, H, C, grad_scale);
-    FEDB_LAUNCH_CHECK();
+    FEDB_CHECK(launch_pdl(head_pool_kernel, dim3(dim3(B, (H + 7) / 8)), dim3(256), 0, (cudaStream_t)stream, 
+        (const __nv_bfloat16*)x, first_tok, Wp, bp, pooled, pooled_drop, H, seed, th, 1.0f / keep, dropout_p > 0.f));
+    FEDB_CHECK(launch_pdl(head_cls_kernel, dim3(B), dim3(128), C * sizeof(float), (cudaStream_t)stream, pooled_drop, Wc, bc, labels, logits, loss, pred,
+                                                                       dlogits, H, C, grad_scale));
     return 0;
 }
 
@@ -162,12 +165,9 @@ extern "C" int fedb200_head_bwd(const void* x, const int* first_tok, const float
     const float keep = 1.0f - dropout_p;
     const uint32_t th = dropout_thresh16(dropout_p);
     cudaStream_t s = (cudaStream_t)stream;
-    head_bwd_cls_kernel<<<(H + 127) / 128, 128, 0, s>>>(dlogits, pooled, pooled_drop, Wc, gWc, gbc, dpre, B, H, C, seed,
-                                                       th, 1.0f / keep, dropout_p > 0.f);
-    FEDB_LAUNCH_CHECK();
-    head_bwd_pool_w_kernel<<<H, 256, B * sizeof(float), s>>>(dpre, (const __nv_bfloat16*)x, first_tok, gWp, gbp, B, H);
-    FEDB_LAUNCH_CHECK();
-    head_bwd_pool_x_kernel<<<B, 256, H * sizeof(float), s>>>(dpre, Wp, first_tok, (__nv_bfloat16*)dx, H);
-    FEDB_LAUNCH_CHECK();
+    FEDB_CHECK(launch_pdl(head_bwd_cls_kernel, dim3((H + 127) / 128), dim3(128), 0, s, dlogits, pooled, pooled_drop, Wc, gWc, gbc, dpre, B, H, C, seed,
+                                                       th, 1.0f / keep, dropout_p > 0.f));
+    FEDB_CHECK(launch_pdl(head_bwd_pool_w_kernel, dim3(H), dim3(256), B * sizeof(float), s, dpre, (const __nv_bfloat16*)x, first_tok, gWp, gbp, B, H));
+    FEDB_CHECK(launch_pdl(head_bwd_pool_x_kernel, dim3(B), dim3(256), H * sizeof(float), s, dpre, Wp, first_tok, (__nv_bfloat16*)dx, H));
     return 0;
 }

@@ -63,6 +63,7 @@ __global__ void __launch_bounds__(LN_WARPS * 32) ln_fwd_kernel(const __nv_bfloat
                                                                const float* __restrict__ beta,
                                                                __nv_bfloat16* __restrict__ y, float* __restrict__ mean_out,
                                                                float* __restrict__ rstd_out, int T, int H, float eps) {
+    pdl_sync();
     const int lane = threadIdx.x & 31, nvec = H / 8;
     const int warp = blockIdx.x * LN_WARPS + (threadIdx.x >> 5), nwarps = gridDim.x * LN_WARPS;
     for (int row = warp; row < T; row += nwarps) {
@@ -95,6 +96,7 @@ __global__ void __launch_bounds__(LN_WARPS * 32, (NV <= 2) ? 2 : 1) ln_bwd_kerne
     const float* __restrict__ rstd_in, const float* __restrict__ gamma, __nv_bfloat16* __restrict__ dz,
     __nv_bfloat16* __restrict__ df, float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dbias,
     int T, int H, uint64_t seed, uint32_t keep_thresh, float inv_keep) {
+    pdl_sync();
     extern __shared__ float red[];        // [LN_WARPS][H]
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, nvec = H / 8;
     const int warp = blockIdx.x * LN_WARPS + wib, nwarps = gridDim.x * LN_WARPS;
@@ -190,11 +192,12 @@ extern "C" int fedb200_layernorm_fwd(const void* z, const float* gamma, const fl
     FEDB_REQUIRE(H % 8 == 0 && H <= 8 * 32 * LN_MAXV, "layernorm: H=%d must be a multiple of 8 and <= 1024", H);
     if (T <= 0) return 0;
     const int nv = (H / 8 + 31) / 32;
-#define FEDB_LN_FWD(NVV) ln_fwd_kernel<NVV><<<ln_grid(T), LN_WARPS * 32, 0, (cudaStream_t)stream>>>( \
+    cudaError_t le;
+#define FEDB_LN_FWD(NVV) le = launch_pdl(ln_fwd_kernel<NVV>, dim3(ln_grid(T)), dim3(LN_WARPS * 32), 0, (cudaStream_t)stream, \
         (const __nv_bfloat16*)z, gamma, beta, (__nv_bfloat16*)y, mean, rstd, T, H, eps)
     if (nv == 1) FEDB_LN_FWD(1); else if (nv == 2) FEDB_LN_FWD(2); else if (nv == 3) FEDB_LN_FWD(3); else FEDB_LN_FWD(4);
 #undef FEDB_LN_FWD
-    FEDB_LAUNCH_CHECK();
+    FEDB_CHECK(le);
     return 0;
 }
 
@@ -211,11 +214,12 @@ extern "C" int fedb200_layernorm_bwd(const void* dy, const void* z, const float*
     if (blocks > sm_count() * 2) blocks = sm_count() * 2;
     const int nv = (H / 8 + 31) / 32;
     if (nv <= 2 && blocks < ln_grid(T)) blocks = ln_grid(T) < sm_count() * 4 ? ln_grid(T) : sm_count() * 4;   // two blocks per SM fit
-#define FEDB_LN_BWD(NVV) ln_bwd_kernel<NVV><<<blocks, LN_WARPS * 32, LN_WARPS * H * sizeof(float), (cudaStream_t)stream>>>( \
-        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)z, mean, rstd, gamma, (__nv_bfloat16*)dz, (__nv_bfloat16*)df, \
-        dgamma, dbeta, dbias, T, H, seed, thresh, 1.0f / keep)
+    cudaError_t le;
+#define FEDB_LN_BWD(NVV) le = launch_pdl(ln_bwd_kernel<NVV>, dim3(blocks), dim3(LN_WARPS * 32), LN_WARPS * H * sizeof(float), \
+        (cudaStream_t)stream, (const __nv_bfloat16*)dy, (const __nv_bfloat16*)z, mean, rstd, gamma, (__nv_bfloat16*)dz, \
+        (__nv_bfloat16*)df, dgamma, dbeta, dbias, T, H, seed, thresh, 1.0f / keep)
     if (nv == 1) FEDB_LN_BWD(1); else if (nv == 2) FEDB_LN_BWD(2); else if (nv == 3) FEDB_LN_BWD(3); else FEDB_LN_BWD(4);
 #undef FEDB_LN_BWD
-    FEDB_LAUNCH_CHECK();
+    FEDB_CHECK(le);
     return 0;
 }

@@ -4,6 +4,7 @@
 #include "../include/fedb200.h"
 #include <stdarg.h>
 #include <string.h>
+#include <stdlib.h>
 #include <mutex>
 
 namespace fedb {
@@ -27,6 +28,15 @@ int sm_count() {
         cached[dev] = n;
     }
     return cached[dev];
+}
+
+static int g_pdl = -1;
+int pdl_enabled() {
+    if (g_pdl < 0) {
+        const char* e = getenv("FEDB200_PDL");
+        g_pdl = (e && e[0] == '0') ? 0 : 1;
+    }
+    return g_pdl;
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -83,3 +93,4 @@ int make_tmap_bf16_3d(CUtensorMap* out, const void* base, uint64_t d0, uint64_t 
 extern "C" const char* fedb200_last_error(void) { return fedb::g_err; }
 extern "C" int fedb200_abi_version(void) { return FEDB200_ABI_VERSION; }
 extern "C" int fedb200_sm_count(void) { return fedb::sm_count(); }
+extern "C" int fedb200_set_pdl(int on) { fedb::g_pdl = on ? 1 : 0; return 0; }

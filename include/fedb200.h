@@ -31,6 +31,8 @@ extern "C" {
 const char* fedb200_last_error(void);
 int fedb200_abi_version(void);
 int fedb200_sm_count(void);
+/* programmatic dependent launch between this library's kernels (default on; FEDB200_PDL=0 also disables) */
+int fedb200_set_pdl(int on);
 
 /* ---- flat-arena kernels ------------------------------------------------------------------------------------ */
 /* K13. One pass of HF-semantics AdamW over the whole flat arena (reference: transformers.AdamW python loop,
