@@ -166,11 +166,11 @@ __device__ __forceinline__ float gelu_erf_grad(float x) {
 }
 __device__ __forceinline__ float gelu_tanh(float x) {
     const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
-    return 0.5f * x * (1.0f + tanhf(u));
+    return 0.5f * x * (1.0f + tanh_fast(u));          // MUFU.TANH: branch-free, error far below bf16 resolution
 }
 __device__ __forceinline__ float gelu_tanh_grad(float x) {
     const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
-    const float t = tanhf(u);
+    const float t = tanh_fast(u);
     const float du = 0.7978845608028654f * (1.0f + 3.0f * 0.044715f * x * x);
     return 0.5f * (1.0f + t) + 0.5f * x * (1.0f - t * t) * du;
 }
@@ -237,6 +237,22 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
         : "memory");
+}
+// TMA store (shared::cta -> global, bulk-group completion).  The issuing thread owns the bulk group: it commits and later
+// waits (".read" = the shared-memory source has been read and may be overwritten; the global write may still be in flight,
+// kernel completion makes it visible).
+__device__ __forceinline__ void tma_store_smem_2d(const CUtensorMap* m, uint32_t smem_src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_src), "r"(c0), "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
     asm volatile(

@@ -224,6 +224,7 @@ extern "C" int fedb200_gemm_bf16(int layout, const void* A, int lda, const void*
         pp.keep_thresh = dropout_thresh16(dropout_p);
         pp.inv_keep = 1.0f / (1.0f - dropout_p);
         pp.use_dropout = dropout_p > 0.f;
+        pp.tma_store = gemm_mode() == 4 ? 0 : (gemm_mode() == 5 ? 2 : 1);
         return gemm2_dispatch(layout, A, lda, B, ldb, pp, BN, max_ctas, (cudaStream_t)stream);
     }
     CUtensorMap ta, tb;
@@ -241,6 +242,7 @@ extern "C" int fedb200_gemm_bf16(int layout, const void* A, int lda, const void*
     p.keep_thresh = dropout_thresh16(dropout_p);
     p.inv_keep = 1.0f / (1.0f - dropout_p);
     p.use_dropout = dropout_p > 0.f;
+    p.tma_store = 0;
     cudaStream_t s = (cudaStream_t)stream;
 
 #define FEDB_GEMM_CASE(AM, BM, BNV) if (a_mn == AM && b_mn == BM && BN == BNV) return launch_gemm<AM, BM, BNV>(ta, tb, p, max_ctas, s);
