@@ -21,6 +21,7 @@
 // reads one word per q row instead of re-hashing every element (13 -> 4 instructions per element).
 // lse is stored in base-2 units of the scaled scores: lse2 = max2 + log2(sum), p = exp2(s*scale*log2e - lse2).
 #include "common.cuh"
+#include <type_traits>
 #include "../include/fedb200.h"
 
 namespace fedb {
@@ -83,49 +84,64 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attn_fwd_kernel(const __grid_co
     const uint32_t tmem_s = tmem_slot, tmem_o = tmem_slot + 128;
 
     if (warp == 0) {
-        if (lane == 0) {
+        // warp-uniform loops, one elected lane issues (operands stay in uniform registers; see gemm2_tcgen05.cu)
+        if (elect_one()) {
             mbar_expect_tx(&q_full, AT_TILE);
             tma_load_2d(sQ, &tm_qkv, &q_full, h * 64, tok0 + q0);
-            for (int j = 0; j < n_kv; ++j) {
-                const uint32_t ph = ((uint32_t)j & 1u) ^ 1u;
-                mbar_wait(&k_empty, ph);
+        }
+        __syncwarp();
+        for (int j = 0; j < n_kv; ++j) {
+            const uint32_t ph = ((uint32_t)j & 1u) ^ 1u;
+            mbar_wait(&k_empty, ph);
+            if (elect_one()) {
                 mbar_expect_tx(&k_full, AT_TILE);
                 tma_load_2d(sK, &tm_qkv, &k_full, H + h * 64, tok0 + j * 128);
-                mbar_wait(&v_empty, ph);
+            }
+            __syncwarp();
+            mbar_wait(&v_empty, ph);
+            if (elect_one()) {
                 mbar_expect_tx(&v_full, AT_TILE);
                 tma_load_2d(sV, &tm_qkv, &v_full, 2 * H + h * 64, tok0 + j * 128);
             }
+            __syncwarp();
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
-            constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
-            const uint32_t aQ = smem_u32(sQ), aP = smem_u32(sP);
-            const uint32_t aK = smem_u32(sK), aV = smem_u32(sV);
-            mbar_wait(&q_full, 0);
-            mbar_wait(&k_full, 0);
-            tc_fence_after_sync();
+        constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
+        constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
+        const uint32_t aQ = smem_u32(sQ), aP = smem_u32(sP);
+        const uint32_t aK = smem_u32(sK), aV = smem_u32(sV);
+        mbar_wait(&q_full, 0);
+        mbar_wait(&k_full, 0);
+        tc_fence_after_sync();
+        if (elect_one()) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) umma_bf16(tmem_s, desc_kmajor(aQ, k), desc_kmajor(aK, k), idesc_s, k > 0);
             umma_commit(&s_full);
             umma_commit(&k_empty);
-            for (int j = 0; j < n_kv; ++j) {
-                mbar_wait(&p_ready, (uint32_t)j & 1u);
-                mbar_wait(&v_full, (uint32_t)j & 1u);
-                tc_fence_after_sync();
+        }
+        __syncwarp();
+        for (int j = 0; j < n_kv; ++j) {
+            mbar_wait(&p_ready, (uint32_t)j & 1u);
+            mbar_wait(&v_full, (uint32_t)j & 1u);
+            tc_fence_after_sync();
+            if (elect_one()) {
 #pragma unroll
                 for (int k = 0; k < 8; ++k)
                     umma_bf16(tmem_o, desc_kmajor(aP + (k >> 2) * AT_TILE, k & 3), desc_mnmajor(aV, k, 8192), idesc_o, k > 0);
                 umma_commit(&o_full);
                 umma_commit(&v_empty);
-                if (j + 1 < n_kv) {
-                    mbar_wait(&k_full, (uint32_t)(j + 1) & 1u);
-                    tc_fence_after_sync();
+            }
+            __syncwarp();
+            if (j + 1 < n_kv) {
+                mbar_wait(&k_full, (uint32_t)(j + 1) & 1u);
+                tc_fence_after_sync();
+                if (elect_one()) {
 #pragma unroll
                     for (int k = 0; k < 4; ++k) umma_bf16(tmem_s, desc_kmajor(aQ, k), desc_kmajor(aK, k), idesc_s, k > 0);
                     umma_commit(&s_full);
                     umma_commit(&k_empty);
                 }
+                __syncwarp();
             }
         }
     } else {
@@ -353,53 +369,66 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
                    tm_dq = tmem_slot + 384;
 
     if (warp == 0) {
-        if (lane == 0) {
+        // warp-uniform loops, one elected lane issues (operands stay in uniform registers; see gemm2_tcgen05.cu)
+        if (elect_one()) {
             mbar_expect_tx(&kv_full, 2 * AT_TILE);
             tma_load_2d(sK, &tm_qkv, &kv_full, H + h * 64, tok0 + kv0);
             tma_load_2d(sV, &tm_qkv, &kv_full, 2 * H + h * 64, tok0 + kv0);
-            for (int i = 0; i < n_q; ++i) {
-                const int s = i & 1;
-                mbar_wait(&qdo_empty[s], ((uint32_t)(i >> 1) & 1u) ^ 1u);
+        }
+        __syncwarp();
+        for (int i = 0; i < n_q; ++i) {
+            const int s = i & 1;
+            mbar_wait(&qdo_empty[s], ((uint32_t)(i >> 1) & 1u) ^ 1u);
+            if (elect_one()) {
                 mbar_expect_tx(&qdo_full[s], 2 * AT_TILE);
                 tma_load_2d(sQ + s * AT_TILE, &tm_qkv, &qdo_full[s], h * 64, tok0 + i * 128);
                 tma_load_2d(sdO + s * AT_TILE, &tm_do, &qdo_full[s], h * 64, tok0 + i * 128);
             }
+            __syncwarp();
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            constexpr uint32_t idesc_nn = umma_idesc_bf16(128, 128, 0, 0);     // S^T, dP^T
-            constexpr uint32_t idesc_kmn = umma_idesc_bf16(128, 64, 0, 1);     // dV, dK
-            constexpr uint32_t idesc_mnmn = umma_idesc_bf16(128, 64, 1, 1);    // dQ
-            const uint32_t aK = smem_u32(sK), aV = smem_u32(sV), aP = smem_u32(sP), aS = smem_u32(sdS);
-            mbar_wait(&kv_full, 0);
-            for (int i = 0; i < n_q; ++i) {
-                const int s = i & 1;
-                const uint32_t aQ = smem_u32(sQ + s * AT_TILE), aO = smem_u32(sdO + s * AT_TILE);
-                mbar_wait(&qdo_full[s], (uint32_t)(i >> 1) & 1u);
-                tc_fence_after_sync();
+        constexpr uint32_t idesc_nn = umma_idesc_bf16(128, 128, 0, 0);     // S^T, dP^T
+        constexpr uint32_t idesc_kmn = umma_idesc_bf16(128, 64, 0, 1);     // dV, dK
+        constexpr uint32_t idesc_mnmn = umma_idesc_bf16(128, 64, 1, 1);    // dQ
+        const uint32_t aK = smem_u32(sK), aV = smem_u32(sV), aP = smem_u32(sP), aS = smem_u32(sdS);
+        mbar_wait(&kv_full, 0);
+        for (int i = 0; i < n_q; ++i) {
+            const int s = i & 1;
+            const uint32_t aQ = smem_u32(sQ + s * AT_TILE), aO = smem_u32(sdO + s * AT_TILE);
+            mbar_wait(&qdo_full[s], (uint32_t)(i >> 1) & 1u);
+            tc_fence_after_sync();
+            if (elect_one()) {
 #pragma unroll
                 for (int k = 0; k < 4; ++k) umma_bf16(tm_st, desc_kmajor(aK, k), desc_kmajor(aQ, k), idesc_nn, k > 0);
 #pragma unroll
                 for (int k = 0; k < 4; ++k) umma_bf16(tm_dpt, desc_kmajor(aV, k), desc_kmajor(aO, k), idesc_nn, k > 0);
                 umma_commit(&sdp_full);
-                mbar_wait(&pds_ready, (uint32_t)i & 1u);
-                tc_fence_after_sync();
+            }
+            __syncwarp();
+            mbar_wait(&pds_ready, (uint32_t)i & 1u);
+            tc_fence_after_sync();
+            if (elect_one()) {
 #pragma unroll
                 for (int k = 0; k < 8; ++k)      // dV += Pd^T dO_i   (reduction over q)
                     umma_bf16(tm_dv, desc_kmajor(aP + (k >> 2) * AT_TILE, k & 3), desc_mnmajor(aO, k, 8192), idesc_kmn, (i | k) != 0);
 #pragma unroll
                 for (int k = 0; k < 8; ++k)      // dK += dS^T Q_i
                     umma_bf16(tm_dk, desc_kmajor(aS + (k >> 2) * AT_TILE, k & 3), desc_mnmajor(aQ, k, 8192), idesc_kmn, (i | k) != 0);
-                mbar_wait(&dq_empty, ((uint32_t)i & 1u) ^ 1u);
-                tc_fence_after_sync();
+            }
+            __syncwarp();
+            mbar_wait(&dq_empty, ((uint32_t)i & 1u) ^ 1u);
+            tc_fence_after_sync();
+            if (elect_one()) {
 #pragma unroll
                 for (int k = 0; k < 8; ++k)      // dQ_i = dS K   (A = dS^T buffer read MN-major, reduction over kv)
                     umma_bf16(tm_dq, desc_mnmajor(aS, k, AT_TILE), desc_mnmajor(aK, k, 8192), idesc_mnmn, k > 0);
                 umma_commit(&dq_full);
                 umma_commit(&qdo_empty[s]);
             }
-            umma_commit(&dkv_full);
+            __syncwarp();
         }
+        if (elect_one()) umma_commit(&dkv_full);
+        __syncwarp();
     } else {
         // Sixteen compute warps: the four warps of a TMEM lane quadrant (rows) take one 32-column group of
         // S^T / dP^T each; column groups 0-1 / 2-3 are the two 64-column smem tiles of Pd^T / dS^T.
@@ -433,6 +462,7 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
             mbar_wait(&sdp_full, (uint32_t)i & 1u);
             tc_fence_after_sync();
             const bool full_tile = kv0 + 128 <= len && qb + 128 <= len;       // no masking needed (block-uniform)
+            const int drop_mode = !use_dropout ? 0 : (drop_bits != nullptr ? 1 : 2);
 #pragma unroll 1
             for (int hc = 0; hc < 2; ++hc) {                                   // two 16-column halves of the group
                 const int c0 = cg * 32 + hc * 16;
@@ -441,22 +471,38 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
                 tmem_ld_32x16(tm_dpt + lane_addr + c0, rp);
                 tmem_ld_wait();
                 float pd[16], ds[16];
+                // The element loop is instantiated per (dropout source, masking) combination and selected by one
+                // warp-uniform switch: with the conditions inside the loop every element carried its own branches
+                // (and the unused hash path), which serialised the 16 independent chains.
+                auto elems = [&](auto drop_c, auto full_c) {
+                    constexpr int DROP = decltype(drop_c)::value;       // 0 none, 1 stored keep-bits, 2 recompute the hash
+                    constexpr bool FULL = decltype(full_c)::value;
 #pragma unroll
-                for (int jq = 0; jq < 16; ++jq) {
-                    const int ql = c0 + jq, q = qb + ql;
-                    float p = exp2f(__uint_as_float(rs[jq]) * scale_log2 - s_lse[sl][ql]);
-                    if (!full_tile) p = (kv_ok && q < len) ? p : 0.f;
-                    float mk = 1.f;
-                    if (use_dropout) {
-                        if (drop_bits != nullptr) {
+                    for (int jq = 0; jq < 16; ++jq) {
+                        const int ql = c0 + jq, q = qb + ql;
+                        float p = exp2f(__uint_as_float(rs[jq]) * scale_log2 - s_lse[sl][ql]);
+                        if (!FULL) p = (kv_ok && q < len) ? p : 0.f;
+                        float mk = 1.f;
+                        if (DROP == 1) {
                             const uint32_t w = __shfl_sync(0xffffffffu, my_bits, hc * 16 + jq);
                             mk = (w >> lane) & 1u ? inv_keep : 0.f;
-                        } else {
+                        } else if (DROP == 2) {
                             mk = dropout_lane(hash32(drop_col ^ ((drop_row0 + (uint32_t)q) * 0x9E3779B1U)), drop_lane, keep_thresh, inv_keep);
                         }
+                        pd[jq] = p * mk;
+                        ds[jq] = p * (__uint_as_float(rp[jq]) * mk - s_delta[sl][ql]) * scale;
                     }
-                    pd[jq] = p * mk;
-                    ds[jq] = p * (__uint_as_float(rp[jq]) * mk - s_delta[sl][ql]) * scale;
+                };
+                using I0 = std::integral_constant<int, 0>; using I1 = std::integral_constant<int, 1>;
+                using I2 = std::integral_constant<int, 2>;
+                if (full_tile) {
+                    if (drop_mode == 1) elems(I1{}, std::true_type{});
+                    else if (drop_mode == 0) elems(I0{}, std::true_type{});
+                    else elems(I2{}, std::true_type{});
+                } else {
+                    if (drop_mode == 1) elems(I1{}, std::false_type{});
+                    else if (drop_mode == 0) elems(I0{}, std::false_type{});
+                    else elems(I2{}, std::false_type{});
                 }
 #pragma unroll
                 for (int g = 0; g < 2; ++g) {

@@ -65,15 +65,15 @@ __global__ void __launch_bounds__(GM_THREADS, 1) gemm_tcgen05_kernel(const __gri
 
     if (warp == 0) {
         // =============================== TMA producer ===============================
-        if (lane == 0) {
-            uint32_t it = 0;
-            for (int w = blockIdx.x; w < total; w += gridDim.x) {
-                const int split = w % p.splits, tile = w / p.splits;
-                const int n_blk = tile % n_tiles, m_blk = tile / n_tiles;
-                const int kb0 = split * kb_per_split, kb1 = min(k_blocks, kb0 + kb_per_split);
-                for (int kb = kb0; kb < kb1; ++kb, ++it) {
-                    const int s = it % GM_STAGES;
-                    mbar_wait(&empty_bar[s], ((it / GM_STAGES) & 1u) ^ 1u);
+        // warp-uniform loop, one elected lane issues (see gemm2_tcgen05.cu for why)
+        uint32_t s = 0, ph = 0;
+        for (int w = blockIdx.x; w < total; w += gridDim.x) {
+            const int split = w % p.splits, tile = w / p.splits;
+            const int n_blk = tile % n_tiles, m_blk = tile / n_tiles;
+            const int kb0 = split * kb_per_split, kb1 = min(k_blocks, kb0 + kb_per_split);
+            for (int kb = kb0; kb < kb1; ++kb) {
+                mbar_wait(&empty_bar[s], ph ^ 1u);
+                if (elect_one()) {
                     mbar_expect_tx(&full_bar[s], STAGE_BYTES);
                     uint8_t* sa = smem + s * STAGE_BYTES;
                     uint8_t* sb = sa + GM_A_BYTES;
@@ -92,37 +92,39 @@ __global__ void __launch_bounds__(GM_THREADS, 1) gemm_tcgen05_kernel(const __gri
                             tma_load_2d(sb + j * 8192, &tmB, &full_bar[s], n_blk * BN + j * 64, kb * GM_BK);
                     }
                 }
+                __syncwarp();
+                if (++s == (uint32_t)GM_STAGES) { s = 0; ph ^= 1u; }
             }
         }
     } else if (warp == 1) {
         // =============================== MMA issuer ===============================
-        if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(GM_BM, BN, A_MN, B_MN);
-            uint32_t it = 0, local = 0;
-            for (int w = blockIdx.x; w < total; w += gridDim.x, ++local) {
-                const int split = w % p.splits;
-                const int kb0 = split * kb_per_split, kb1 = min(k_blocks, kb0 + kb_per_split);
-                const uint32_t buf = local & 1u;
-                mbar_wait(&acc_empty[buf], ((local >> 1) & 1u) ^ 1u);
+        constexpr uint32_t idesc = umma_idesc_bf16(GM_BM, BN, A_MN, B_MN);
+        uint32_t s = 0, ph = 0, local = 0;
+        for (int w = blockIdx.x; w < total; w += gridDim.x, ++local) {
+            const int split = w % p.splits;
+            const int kb0 = split * kb_per_split, kb1 = min(k_blocks, kb0 + kb_per_split);
+            const uint32_t buf = local & 1u;
+            mbar_wait(&acc_empty[buf], ((local >> 1) & 1u) ^ 1u);
+            tc_fence_after_sync();
+            const uint32_t tmem_d = tmem_base + buf * BN;
+            for (int kb = kb0; kb < kb1; ++kb) {
+                mbar_wait(&full_bar[s], ph);
                 tc_fence_after_sync();
-                const uint32_t tmem_d = tmem_base + buf * BN;
-                for (int kb = kb0; kb < kb1; ++kb, ++it) {
-                    const int s = it % GM_STAGES;
-                    mbar_wait(&full_bar[s], (it / GM_STAGES) & 1u);
-                    tc_fence_after_sync();
-                    const uint32_t sa = smem_u32(smem + s * STAGE_BYTES), sb = sa + GM_A_BYTES;
+                const uint32_t sa = smem_u32(smem + s * STAGE_BYTES), sb = sa + GM_A_BYTES;
+                const uint64_t da0 = A_MN ? umma_smem_desc(sa, 8192, 1024) : umma_smem_desc(sa, 16, 1024);
+                const uint64_t db0 = B_MN ? umma_smem_desc(sb, 8192, 1024) : umma_smem_desc(sb, 16, 1024);
+                if (elect_one()) {
 #pragma unroll
-                    for (int k = 0; k < GM_BK / 16; ++k) {
-                        const uint64_t da = A_MN ? umma_smem_desc(sa + k * 2048, 8192, 1024)
-                                                 : umma_smem_desc(sa + k * 32, 16, 1024);
-                        const uint64_t db = B_MN ? umma_smem_desc(sb + k * 2048, 8192, 1024)
-                                                 : umma_smem_desc(sb + k * 32, 16, 1024);
-                        umma_bf16(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-                    }
+                    for (int k = 0; k < GM_BK / 16; ++k)
+                        umma_bf16(tmem_d, da0 + (uint64_t)(k * ((A_MN ? 2048 : 32) >> 4)),
+                                  db0 + (uint64_t)(k * ((B_MN ? 2048 : 32) >> 4)), idesc, (kb > kb0 || k > 0) ? 1u : 0u);
                     umma_commit(&empty_bar[s]);
                 }
-                umma_commit(&acc_full[buf]);
+                __syncwarp();
+                if (++s == (uint32_t)GM_STAGES) { s = 0; ph ^= 1u; }
             }
+            if (elect_one()) umma_commit(&acc_full[buf]);
+            __syncwarp();
         }
     } else {
         // =============================== epilogue warps ===============================

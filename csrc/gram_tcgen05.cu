@@ -66,36 +66,39 @@ __global__ void __launch_bounds__(GR_THREADS, 1) gram_tcgen05_kernel(const __gri
     const int n_kb = (kb_end - kb_begin - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;   // this CTA's k-blocks
     const uint32_t stage_tx = (uint32_t)rows_total * 128u;
 
-    if (warp == 0 && lane == 0) {
-        // ---------------- TMA producer ----------------
+    if (warp == 0) {
+        // ---------------- TMA producer (warp-uniform loop, one elected lane issues) ----------------
+        uint32_t s = 0, ph = 0;
         for (int it = 0; it < n_kb; ++it) {
-            const int s = it % GR_STAGES;
-            const uint32_t ph = (uint32_t)(it / GR_STAGES) & 1u;
             mbar_wait(&empty_bar[s], ph ^ 1u);
-            mbar_expect_tx(&full_bar[s], stage_tx);
-            const int kcol = (kb_begin + (int)blockIdx.x + it * (int)gridDim.x) * 64;
-            for (int r = 0; r < n_ranks; ++r)
-                for (int pr = 0; pr < boxes_per_rank; ++pr)     // one box = all rows of a rank (S = 1) or S segments of one client
-                    tma_load_2d(smem + s * GR_TILE_BYTES + (r * boxes_per_rank + pr) * box_rows * 128, &maps.map[r], &full_bar[s],
-                                kcol, pr * nseg_total + seg_begin);
+            if (elect_one()) {
+                mbar_expect_tx(&full_bar[s], stage_tx);
+                const int kcol = (kb_begin + (int)blockIdx.x + it * (int)gridDim.x) * 64;
+                for (int r = 0; r < n_ranks; ++r)
+                    for (int pr = 0; pr < boxes_per_rank; ++pr)     // one box = all rows of a rank (S = 1) or S segments of one client
+                        tma_load_2d(smem + s * GR_TILE_BYTES + (r * boxes_per_rank + pr) * box_rows * 128, &maps.map[r],
+                                    &full_bar[s], kcol, pr * nseg_total + seg_begin);
+            }
+            __syncwarp();
+            if (++s == (uint32_t)GR_STAGES) { s = 0; ph ^= 1u; }
         }
-    } else if (warp == 1 && lane == 0) {
+    } else if (warp == 1) {
         // ---------------- MMA issuer ----------------
         const uint32_t idesc = umma_idesc_bf16(128, n_pad, 0, 0);
+        uint32_t s = 0, ph = 0;
         for (int it = 0; it < n_kb; ++it) {
-            const int s = it % GR_STAGES;
-            const uint32_t ph = (uint32_t)(it / GR_STAGES) & 1u;
             mbar_wait(&full_bar[s], ph);
             tc_fence_after_sync();
-            const uint32_t base = smem_u32(smem + s * GR_TILE_BYTES);
+            const uint64_t d0 = umma_smem_desc(smem_u32(smem + s * GR_TILE_BYTES), 16, 1024);
+            if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const uint64_t d = umma_smem_desc(base + k * 32, 16, 1024);
-                umma_bf16(tmem_d, d, d, idesc, (it | k) != 0);
+                for (int k = 0; k < 4; ++k) umma_bf16(tmem_d, d0 + (uint64_t)(k * 2), d0 + (uint64_t)(k * 2), idesc, (it | k) != 0);
+                umma_commit(&empty_bar[s]);          // frees the slot once these MMAs have read it
             }
-            umma_commit(&empty_bar[s]);          // frees the slot once these MMAs have read it
+            __syncwarp();
+            if (++s == (uint32_t)GR_STAGES) { s = 0; ph ^= 1u; }
         }
-        umma_commit(&done_bar);
+        if (elect_one()) umma_commit(&done_bar);
     }
     __syncwarp();
 

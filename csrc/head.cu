@@ -120,20 +120,28 @@ __global__ void __launch_bounds__(256) head_bwd_pool_w_kernel(const float* __res
     }
 }
 
-// block per sample: dx[first[b], :] = sum_o dpre[b, o] * Wp[o, :]
+// dx[first[b], :] = sum_o dpre[b, o] * Wp[o, :].  Grid (sample, 64-column slab); the four 64-thread groups of a block split
+// the reduction over o and combine through shared memory (one block per sample was a 250 us latency-bound tail).
 __global__ void __launch_bounds__(256) head_bwd_pool_x_kernel(const float* __restrict__ dpre, const float* __restrict__ Wp,
                                                               const int* __restrict__ first, __nv_bfloat16* __restrict__ dx,
                                                               int H) {
     pdl_sync();
-    extern __shared__ float sd[];      // dpre[b, :]
-    const int b = blockIdx.x;
+    extern __shared__ float sd[];      // dpre[b, :] followed by 4 x 64 partial sums
+    float* part = sd + H;
+    const int b = blockIdx.x, il = threadIdx.x & 63, grp = threadIdx.x >> 6;
+    const int i = blockIdx.y * 64 + il;
     for (int o = threadIdx.x; o < H; o += blockDim.x) sd[o] = dpre[(size_t)b * H + o];
     __syncthreads();
-    for (int i = threadIdx.x; i < H; i += blockDim.x) {
-        float s = 0.f;
-        for (int o = 0; o < H; ++o) s += sd[o] * Wp[(size_t)o * H + i];
-        dx[(size_t)first[b] * H + i] = __float2bfloat16_rn(s);
+    float s = 0.f;
+    if (i < H) {
+        const int per = (H + 3) / 4, o0 = grp * per, o1 = min(H, o0 + per);
+#pragma unroll 8
+        for (int o = o0; o < o1; ++o) s = fmaf(sd[o], __ldg(Wp + (size_t)o * H + i), s);
     }
+    part[grp * 64 + il] = s;
+    __syncthreads();
+    if (grp == 0 && i < H)
+        dx[(size_t)first[b] * H + i] = __float2bfloat16_rn(part[il] + part[64 + il] + part[128 + il] + part[192 + il]);
 }
 
 }  // namespace fedb
@@ -168,6 +176,7 @@ extern "C" int fedb200_head_bwd(const void* x, const int* first_tok, const float
     FEDB_CHECK(launch_pdl(head_bwd_cls_kernel, dim3((H + 127) / 128), dim3(128), 0, s, dlogits, pooled, pooled_drop, Wc, gWc, gbc, dpre, B, H, C, seed,
                                                        th, 1.0f / keep, dropout_p > 0.f));
     FEDB_CHECK(launch_pdl(head_bwd_pool_w_kernel, dim3(H), dim3(256), B * sizeof(float), s, dpre, (const __nv_bfloat16*)x, first_tok, gWp, gbp, B, H));
-    FEDB_CHECK(launch_pdl(head_bwd_pool_x_kernel, dim3(B), dim3(256), H * sizeof(float), s, dpre, Wp, first_tok, (__nv_bfloat16*)dx, H));
+    FEDB_CHECK(launch_pdl(head_bwd_pool_x_kernel, dim3(B, (H + 63) / 64), dim3(256), (H + 256) * sizeof(float), s, dpre, Wp, first_tok,
+                          (__nv_bfloat16*)dx, H));
     return 0;
 }
