@@ -345,11 +345,10 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
     uint8_t* sV = sK + AT_TILE;
     uint8_t* sQ = sV + AT_TILE;              // 2 stages
     uint8_t* sdO = sQ + 2 * AT_TILE;         // 2 stages
-    uint8_t* sP = sdO + 2 * AT_TILE;         // Pd^T : 2 tiles (q 0-63 | 64-127), rows = kv
-    uint8_t* sdS = sP + 2 * AT_TILE;         // dS^T : 2 tiles
+    uint8_t* sP = sdO + 2 * AT_TILE;         // Pd^T : 2 buffers x 2 tiles (q 0-63 | 64-127), rows = kv
+    uint8_t* sdS = sP + 4 * AT_TILE;         // dS^T : 2 buffers x 2 tiles
     __shared__ __align__(8) uint64_t kv_full, qdo_full[2], qdo_empty[2], sdp_full, pds_ready, dq_full, dq_empty, dkv_full;
     __shared__ uint32_t tmem_slot;
-    __shared__ float s_lse[2][128], s_delta[2][128];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp == 0 && lane == 0) {
@@ -391,37 +390,57 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
         constexpr uint32_t idesc_kmn = umma_idesc_bf16(128, 64, 0, 1);     // dV, dK
         constexpr uint32_t idesc_mnmn = umma_idesc_bf16(128, 64, 1, 1);    // dQ
         const uint32_t aK = smem_u32(sK), aV = smem_u32(sV), aP = smem_u32(sP), aS = smem_u32(sdS);
+        // Software pipeline: S^T/dP^T of q tile i+1 are issued BEFORE the dV/dK/dQ products of tile i, so the compute
+        // warps start on tile i+1 after ~512 tensor cycles while the 24 gradient MMAs of tile i run underneath.  That is
+        // safe because Pd^T/dS^T are double-buffered in shared memory (buffer i & 1) and every later commit covers the
+        // earlier MMAs (in-order completion): sdp_full(i+2) implies the MMAs that read buffer i & 1 have finished.
         mbar_wait(&kv_full, 0);
+        mbar_wait(&qdo_full[0], 0);
+        tc_fence_after_sync();
+        if (elect_one()) {
+            const uint32_t aQ = smem_u32(sQ), aO = smem_u32(sdO);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) umma_bf16(tm_st, desc_kmajor(aK, k), desc_kmajor(aQ, k), idesc_nn, k > 0);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) umma_bf16(tm_dpt, desc_kmajor(aV, k), desc_kmajor(aO, k), idesc_nn, k > 0);
+            umma_commit(&sdp_full);
+        }
+        __syncwarp();
         for (int i = 0; i < n_q; ++i) {
             const int s = i & 1;
             const uint32_t aQ = smem_u32(sQ + s * AT_TILE), aO = smem_u32(sdO + s * AT_TILE);
-            mbar_wait(&qdo_full[s], (uint32_t)(i >> 1) & 1u);
-            tc_fence_after_sync();
-            if (elect_one()) {
+            const uint32_t aPb = aP + s * 2 * AT_TILE, aSb = aS + s * 2 * AT_TILE;
+            mbar_wait(&pds_ready, (uint32_t)i & 1u);          // tile i: S^T/dP^T consumed, Pd^T/dS^T written
+            if (i + 1 < n_q) {
+                const int s1 = s ^ 1;
+                mbar_wait(&qdo_full[s1], (uint32_t)((i + 1) >> 1) & 1u);
+                tc_fence_after_sync();
+                if (elect_one()) {
+                    const uint32_t aQ1 = smem_u32(sQ + s1 * AT_TILE), aO1 = smem_u32(sdO + s1 * AT_TILE);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) umma_bf16(tm_st, desc_kmajor(aK, k), desc_kmajor(aQ, k), idesc_nn, k > 0);
+                    for (int k = 0; k < 4; ++k) umma_bf16(tm_st, desc_kmajor(aK, k), desc_kmajor(aQ1, k), idesc_nn, k > 0);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) umma_bf16(tm_dpt, desc_kmajor(aV, k), desc_kmajor(aO, k), idesc_nn, k > 0);
-                umma_commit(&sdp_full);
+                    for (int k = 0; k < 4; ++k) umma_bf16(tm_dpt, desc_kmajor(aV, k), desc_kmajor(aO1, k), idesc_nn, k > 0);
+                    umma_commit(&sdp_full);
+                }
+                __syncwarp();
             }
-            __syncwarp();
-            mbar_wait(&pds_ready, (uint32_t)i & 1u);
             tc_fence_after_sync();
             if (elect_one()) {
 #pragma unroll
                 for (int k = 0; k < 8; ++k)      // dV += Pd^T dO_i   (reduction over q)
-                    umma_bf16(tm_dv, desc_kmajor(aP + (k >> 2) * AT_TILE, k & 3), desc_mnmajor(aO, k, 8192), idesc_kmn, (i | k) != 0);
+                    umma_bf16(tm_dv, desc_kmajor(aPb + (k >> 2) * AT_TILE, k & 3), desc_mnmajor(aO, k, 8192), idesc_kmn, (i | k) != 0);
 #pragma unroll
                 for (int k = 0; k < 8; ++k)      // dK += dS^T Q_i
-                    umma_bf16(tm_dk, desc_kmajor(aS + (k >> 2) * AT_TILE, k & 3), desc_mnmajor(aQ, k, 8192), idesc_kmn, (i | k) != 0);
+                    umma_bf16(tm_dk, desc_kmajor(aSb + (k >> 2) * AT_TILE, k & 3), desc_mnmajor(aQ, k, 8192), idesc_kmn, (i | k) != 0);
             }
             __syncwarp();
-            mbar_wait(&dq_empty, ((uint32_t)i & 1u) ^ 1u);
+            mbar_wait(&dq_empty, ((uint32_t)i & 1u) ^ 1u);    // dQ of tile i-1 drained (the compute warps do it after tile i's math)
             tc_fence_after_sync();
             if (elect_one()) {
 #pragma unroll
                 for (int k = 0; k < 8; ++k)      // dQ_i = dS K   (A = dS^T buffer read MN-major, reduction over kv)
-                    umma_bf16(tm_dq, desc_mnmajor(aS, k, AT_TILE), desc_mnmajor(aK, k, 8192), idesc_mnmn, k > 0);
+                    umma_bf16(tm_dq, desc_mnmajor(aSb, k, AT_TILE), desc_mnmajor(aK, k, 8192), idesc_mnmn, k > 0);
                 umma_commit(&dq_full);
                 umma_commit(&qdo_empty[s]);
             }
@@ -443,26 +462,56 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
         const uint32_t drop_lane = (uint32_t)kv & 1u;
         const uint32_t drop_row0 = (uint32_t)(h * T + tok0);
         const int kv_chunk = kv >> 5;                         // warp-uniform (kv0 and quad*32 are multiples of 32)
-        uint8_t* tp = sP + (cg >> 1) * AT_TILE;
-        uint8_t* td = sdS + (cg >> 1) * AT_TILE;
+        // Per-q-row inputs of this warp's 32 q columns live in registers (lane l <-> q = qb + cg*32 + l) and are broadcast
+        // with shuffles; they are fetched one tile ahead so their global-memory latency is off the critical path.
+        auto fetch_rows = [&](int qb, float& lse_q, float& delta_q, uint32_t& bits_q) {
+            const int q = qb + cg * 32 + lane;
+            lse_q = 0.f; delta_q = 0.f; bits_q = 0xFFFFFFFFu;
+            if (q < len) {
+                lse_q = __ldg(lse + (size_t)h * T + tok0 + q);
+                delta_q = __ldg(delta + (size_t)h * T + tok0 + q);
+                if (use_dropout && drop_bits != nullptr && kv_chunk < bits_stride)
+                    bits_q = __ldg(drop_bits + ((size_t)h * T + tok0 + q) * bits_stride + kv_chunk);
+            }
+        };
+        // dQ tile of q tile `it`: lanes are q rows now; each column group drains 16 of the 64 head-dim columns into
+        // slot blockIdx.x of the partial buffer (plain bf16 stores, summed by attn_bwd_finish_kernel)
+        auto drain_dq = [&](int it) {
+            mbar_wait(&dq_full, (uint32_t)it & 1u);
+            tc_fence_after_sync();
+            const int q = it * 128 + r;
+            uint32_t raw[16];
+            tmem_ld_32x16(tm_dq + lane_addr + cg * 16, raw);
+            tmem_ld_wait();
+            if (q < len) {
+                __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(dq_accum) + ((size_t)blockIdx.x * T + tok0 + q) * H + h * 64 + cg * 16;
+#pragma unroll
+                for (int g = 0; g < 2; ++g) {
+                    uint4 pk;
+                    pk.x = pack_bf16x2(__uint_as_float(raw[g * 8 + 0]), __uint_as_float(raw[g * 8 + 1]));
+                    pk.y = pack_bf16x2(__uint_as_float(raw[g * 8 + 2]), __uint_as_float(raw[g * 8 + 3]));
+                    pk.z = pack_bf16x2(__uint_as_float(raw[g * 8 + 4]), __uint_as_float(raw[g * 8 + 5]));
+                    pk.w = pack_bf16x2(__uint_as_float(raw[g * 8 + 6]), __uint_as_float(raw[g * 8 + 7]));
+                    __stcs(reinterpret_cast<uint4*>(dst + g * 8), pk);
+                }
+            }
+            tc_fence_before_sync();
+            mbar_arrive(&dq_empty);
+        };
+        float my_lse, my_delta;
+        uint32_t my_bits;
+        fetch_rows(0, my_lse, my_delta, my_bits);
+        const int drop_mode = !use_dropout ? 0 : (drop_bits != nullptr ? 1 : 2);
         for (int i = 0; i < n_q; ++i) {
-            const int qb = i * 128, sl = i & 1;
-            {   // stage lse / delta of this q tile (double-buffered by i parity; published by the named barrier)
-                const int q = qb + (tid & 127);
-                if (tid < 128) s_lse[sl][tid] = q < len ? lse[(size_t)h * T + tok0 + q] : 0.f;
-                else if (tid < 256) s_delta[sl][tid - 128] = q < len ? delta[(size_t)h * T + tok0 + q] : 0.f;
-            }
-            // keep-bits of this warp's 32 q rows for its kv chunk: lane l holds the word of q = qb + cg*32 + l
-            uint32_t my_bits = 0xFFFFFFFFu;
-            if (use_dropout && drop_bits != nullptr) {
-                const int q = qb + cg * 32 + lane;
-                if (q < len && kv_chunk < bits_stride) my_bits = __ldg(drop_bits + ((size_t)h * T + tok0 + q) * bits_stride + kv_chunk);
-            }
-            asm volatile("bar.sync 1, 512;" ::: "memory");
+            const int qb = i * 128;
+            uint8_t* tp = sP + ((i & 1) * 2 + (cg >> 1)) * AT_TILE;
+            uint8_t* td = sdS + ((i & 1) * 2 + (cg >> 1)) * AT_TILE;
+            float nx_lse = 0.f, nx_delta = 0.f;
+            uint32_t nx_bits = 0xFFFFFFFFu;
+            if (i + 1 < n_q) fetch_rows(qb + 128, nx_lse, nx_delta, nx_bits);
             mbar_wait(&sdp_full, (uint32_t)i & 1u);
             tc_fence_after_sync();
             const bool full_tile = kv0 + 128 <= len && qb + 128 <= len;       // no masking needed (block-uniform)
-            const int drop_mode = !use_dropout ? 0 : (drop_bits != nullptr ? 1 : 2);
 #pragma unroll 1
             for (int hc = 0; hc < 2; ++hc) {                                   // two 16-column halves of the group
                 const int c0 = cg * 32 + hc * 16;
@@ -479,8 +528,10 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
                     constexpr bool FULL = decltype(full_c)::value;
 #pragma unroll
                     for (int jq = 0; jq < 16; ++jq) {
-                        const int ql = c0 + jq, q = qb + ql;
-                        float p = exp2f(__uint_as_float(rs[jq]) * scale_log2 - s_lse[sl][ql]);
+                        const int q = qb + c0 + jq;
+                        const float lse_q = __shfl_sync(0xffffffffu, my_lse, hc * 16 + jq);
+                        const float delta_q = __shfl_sync(0xffffffffu, my_delta, hc * 16 + jq);
+                        float p = exp2f(__uint_as_float(rs[jq]) * scale_log2 - lse_q);
                         if (!FULL) p = (kv_ok && q < len) ? p : 0.f;
                         float mk = 1.f;
                         if (DROP == 1) {
@@ -490,7 +541,7 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
                             mk = dropout_lane(hash32(drop_col ^ ((drop_row0 + (uint32_t)q) * 0x9E3779B1U)), drop_lane, keep_thresh, inv_keep);
                         }
                         pd[jq] = p * mk;
-                        ds[jq] = p * (__uint_as_float(rp[jq]) * mk - s_delta[sl][ql]) * scale;
+                        ds[jq] = p * (__uint_as_float(rp[jq]) * mk - delta_q) * scale;
                     }
                 };
                 using I0 = std::integral_constant<int, 0>; using I1 = std::integral_constant<int, 1>;
@@ -513,30 +564,10 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
             fence_async_smem();
             tc_fence_before_sync();
             mbar_arrive(&pds_ready);
-            // dQ tile: lanes are q rows now; each column group drains 16 of the 64 head-dim columns
-            mbar_wait(&dq_full, (uint32_t)i & 1u);
-            tc_fence_after_sync();
-            const int q = qb + r;
-            {
-                uint32_t raw[16];
-                tmem_ld_32x16(tm_dq + lane_addr + cg * 16, raw);
-                tmem_ld_wait();
-                if (q < len) {       // this kv tile's partial of dQ: plain bf16 stores into slot blockIdx.x
-                    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(dq_accum) + ((size_t)blockIdx.x * T + tok0 + q) * H + h * 64 + cg * 16;
-#pragma unroll
-                    for (int g = 0; g < 2; ++g) {
-                        uint4 pk;
-                        pk.x = pack_bf16x2(__uint_as_float(raw[g * 8 + 0]), __uint_as_float(raw[g * 8 + 1]));
-                        pk.y = pack_bf16x2(__uint_as_float(raw[g * 8 + 2]), __uint_as_float(raw[g * 8 + 3]));
-                        pk.z = pack_bf16x2(__uint_as_float(raw[g * 8 + 4]), __uint_as_float(raw[g * 8 + 5]));
-                        pk.w = pack_bf16x2(__uint_as_float(raw[g * 8 + 6]), __uint_as_float(raw[g * 8 + 7]));
-                        __stcs(reinterpret_cast<uint4*>(dst + g * 8), pk);
-                    }
-                }
-            }
-            tc_fence_before_sync();
-            mbar_arrive(&dq_empty);
+            if (i > 0) drain_dq(i - 1);          // overlaps the S^T/dP^T MMAs of the next tile
+            my_lse = nx_lse; my_delta = nx_delta; my_bits = nx_bits;
         }
+        drain_dq(n_q - 1);
         mbar_wait(&dkv_full, 0);
         tc_fence_after_sync();
         {   // column groups 0-1 write dK (32 columns each) into the K block of dqkv, groups 2-3 write dV
@@ -601,7 +632,7 @@ extern "C" int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dc
     e = make_tmap_bf16_2d(&tmdo, dctx, (uint64_t)T, (uint64_t)H, (uint64_t)H, 128, 64);
     if (e) return e;
     FEDB_CHECK(launch_pdl(attn_delta_kernel, dim3((T * heads + 255) / 256), dim3(256), 0, s, (const __nv_bfloat16*)ctx, (const __nv_bfloat16*)dctx, delta, T, heads));
-    const size_t smem = 10 * AT_TILE + 1024;
+    const size_t smem = 14 * AT_TILE + 1024;
     static bool configured = false;
     if (!configured) {
         FEDB_CHECK(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
