@@ -283,41 +283,48 @@ __global__ void __launch_bounds__(256) attn_bwd_finish_kernel(const __nv_bfloat1
                                                               float* __restrict__ dbias, const int* __restrict__ cu_seqlens,
                                                               int T, int H) {
     pdl_sync();
-    __shared__ float2 red[8][32];
-    const int col = (blockIdx.x * 32 + threadIdx.x) * 2;          // column within [0, 3H)
+    // blockDim = (8, 32): 8 threads x 8 columns = one 64-column slab, 32 token rows per sweep; one block per
+    // (slab, sequence) so each bias-gradient column receives one atomic per sequence
+    __shared__ float red[32][65];
+    const int col = blockIdx.x * 64 + threadIdx.x * 8;            // column within [0, 3H)
     const int s0 = cu_seqlens[blockIdx.y], s1 = cu_seqlens[blockIdx.y + 1];
     const int n_kv = (s1 - s0 + 127) / 128;
-    const int r0 = s0 + blockIdx.z * 64, r1 = min(s1, r0 + 64);          // 64-token slice of the sequence
-    if (r0 >= s1) return;
-    float2 acc = make_float2(0.f, 0.f);
+    float acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+    auto add8 = [](float (&a)[8], const uint4& u) {
+        const float2 p0 = unpack_bf16x2(u.x), p1 = unpack_bf16x2(u.y), p2 = unpack_bf16x2(u.z), p3 = unpack_bf16x2(u.w);
+        a[0] += p0.x; a[1] += p0.y; a[2] += p1.x; a[3] += p1.y; a[4] += p2.x; a[5] += p2.y; a[6] += p3.x; a[7] += p3.y;
+    };
     if (col < 3 * H) {
         if (col < H) {
-            for (int r = r0 + threadIdx.y; r < r1; r += 8) {
-                float2 v = make_float2(0.f, 0.f);
-                for (int j = 0; j < n_kv; ++j) {
-                    const float2 t = unpack_bf16x2(__ldcs(reinterpret_cast<const unsigned int*>(dq_part + ((size_t)j * T + r) * H + col)));
-                    v.x += t.x; v.y += t.y;
-                }
-                const uint32_t pk = pack_bf16x2(v.x, v.y);
-                *reinterpret_cast<uint32_t*>(dqkv + (size_t)r * 3 * H + col) = pk;
-                const float2 f = unpack_bf16x2(pk);               // sum what the GEMMs will consume
-                acc.x += f.x; acc.y += f.y;
+            for (int r = s0 + threadIdx.y; r < s1; r += 32) {
+                float v[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) v[k] = 0.f;
+                for (int j = 0; j < n_kv; ++j)
+                    add8(v, *reinterpret_cast<const uint4*>(dq_part + ((size_t)j * T + r) * H + col));
+                uint4 pk;
+                pk.x = pack_bf16x2(v[0], v[1]); pk.y = pack_bf16x2(v[2], v[3]);
+                pk.z = pack_bf16x2(v[4], v[5]); pk.w = pack_bf16x2(v[6], v[7]);
+                *reinterpret_cast<uint4*>(dqkv + (size_t)r * 3 * H + col) = pk;
+                add8(acc, pk);                                    // sum what the GEMMs will consume
             }
         } else if (dbias != nullptr) {
-            for (int r = r0 + threadIdx.y; r < r1; r += 8) {
-                const float2 f = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(dqkv + (size_t)r * 3 * H + col));
-                acc.x += f.x; acc.y += f.y;
-            }
+            for (int r = s0 + threadIdx.y; r < s1; r += 32)
+                add8(acc, *reinterpret_cast<const uint4*>(dqkv + (size_t)r * 3 * H + col));
         }
     }
     if (dbias == nullptr) return;
-    red[threadIdx.y][threadIdx.x] = acc;
-    __syncthreads();
-    if (threadIdx.y == 0 && col < 3 * H) {
 #pragma unroll
-        for (int y = 1; y < 8; ++y) { acc.x += red[y][threadIdx.x].x; acc.y += red[y][threadIdx.x].y; }
-        atomicAdd(dbias + col, acc.x);
-        atomicAdd(dbias + col + 1, acc.y);
+    for (int k = 0; k < 8; ++k) red[threadIdx.y][threadIdx.x * 8 + k] = acc[k];
+    __syncthreads();
+    const int t = threadIdx.y * 8 + threadIdx.x;
+    if (t < 64 && blockIdx.x * 64 + t < 3 * H) {
+        float sum = 0.f;
+#pragma unroll 8
+        for (int y = 0; y < 32; ++y) sum += red[y][t];
+        atomicAdd(dbias + blockIdx.x * 64 + t, sum);
     }
 }
 
@@ -492,7 +499,7 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
                     pk.y = pack_bf16x2(__uint_as_float(raw[g * 8 + 2]), __uint_as_float(raw[g * 8 + 3]));
                     pk.z = pack_bf16x2(__uint_as_float(raw[g * 8 + 4]), __uint_as_float(raw[g * 8 + 5]));
                     pk.w = pack_bf16x2(__uint_as_float(raw[g * 8 + 6]), __uint_as_float(raw[g * 8 + 7]));
-                    __stcs(reinterpret_cast<uint4*>(dst + g * 8), pk);
+                    *reinterpret_cast<uint4*>(dst + g * 8) = pk;      // default policy: the finish kernel re-reads it from L2
                 }
             }
             tc_fence_before_sync();
@@ -643,7 +650,7 @@ extern "C" int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dc
                                                    scale, scale * LOG2E, seed, dropout_thresh16(dropout_p),
                                                    1.0f / (1.0f - dropout_p), dropout_p > 0.f, (const uint32_t*)drop_bits,
                                                    (max_seqlen + 31) / 32));
-    FEDB_CHECK(launch_pdl(attn_bwd_finish_kernel, dim3(dim3((3 * H + 63) / 64, B, (max_seqlen + 63) / 64)), dim3(dim3(32, 8)), 0, s, 
-        (const __nv_bfloat16*)dq_accum, (__nv_bfloat16*)dqkv, dbias_qkv, cu_seqlens, T, H));
+    FEDB_CHECK(launch_pdl(attn_bwd_finish_kernel, dim3((3 * H + 63) / 64, B), dim3(8, 32), 0, s, (const __nv_bfloat16*)dq_accum,
+                          (__nv_bfloat16*)dqkv, dbias_qkv, cu_seqlens, T, H));
     return 0;
 }

@@ -32,6 +32,27 @@ __device__ __forceinline__ void load_row(const __nv_bfloat16* row, int nvec, int
         }
     }
 }
+template <int NV>
+struct RawRow {
+    uint4 v[NV];
+};
+template <int NV>
+__device__ __forceinline__ void load_raw(const __nv_bfloat16* row, int nvec, int lane, RawRow<NV>& r) {
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        const int v = lane + 32 * i;
+        r.v[i] = v < nvec ? *reinterpret_cast<const uint4*>(row + v * 8) : make_uint4(0u, 0u, 0u, 0u);
+    }
+}
+template <int NV>
+__device__ __forceinline__ void unpack_row(const RawRow<NV>& raw, RowVec<NV>& r) {
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        const float2 a = unpack_bf16x2(raw.v[i].x), b = unpack_bf16x2(raw.v[i].y), c = unpack_bf16x2(raw.v[i].z), d = unpack_bf16x2(raw.v[i].w);
+        r.x[i][0] = a.x; r.x[i][1] = a.y; r.x[i][2] = b.x; r.x[i][3] = b.y;
+        r.x[i][4] = c.x; r.x[i][5] = c.y; r.x[i][6] = d.x; r.x[i][7] = d.y;
+    }
+}
 __device__ __forceinline__ void store_vec(__nv_bfloat16* row, int v, const float (&y)[8]) {
     uint4 o;
     o.x = pack_bf16x2(y[0], y[1]); o.y = pack_bf16x2(y[2], y[3]);
@@ -112,11 +133,26 @@ __global__ void __launch_bounds__(LN_WARPS * 32, (NV <= 2) ? 2 : 1) ln_bwd_kerne
 #pragma unroll
         for (int k = 0; k < 8; ++k) gg[i][k] = v < nvec ? gamma[v * 8 + k] : 0.f;
     }
+    // one row ahead: with ~200 registers per thread only eight warps fit on an SM, so the next row's loads are issued
+    // before this row's math to keep enough bytes in flight
+    RawRow<NV> xr, gr;
+    float mean_n = 0.f, rstd_n = 0.f;
+    if (warp < T) {
+        load_raw(z + (size_t)warp * H, nvec, lane, xr);
+        load_raw(dy + (size_t)warp * H, nvec, lane, gr);
+        mean_n = mean_in[warp]; rstd_n = rstd_in[warp];
+    }
     for (int row = warp; row < T; row += nwarps) {
         RowVec<NV> x, g;
-        load_row(z + (size_t)row * H, nvec, lane, x);
-        load_row(dy + (size_t)row * H, nvec, lane, g);
-        const float mean = mean_in[row], rstd = rstd_in[row];
+        unpack_row(xr, x);
+        unpack_row(gr, g);
+        const float mean = mean_n, rstd = rstd_n;
+        const int nrow = row + nwarps;
+        if (nrow < T) {
+            load_raw(z + (size_t)nrow * H, nvec, lane, xr);
+            load_raw(dy + (size_t)nrow * H, nvec, lane, gr);
+            mean_n = mean_in[nrow]; rstd_n = rstd_in[nrow];
+        }
         float s1 = 0.f, s2 = 0.f;
 #pragma unroll
         for (int i = 0; i < NV; ++i) {
@@ -211,8 +247,9 @@ extern "C" int fedb200_layernorm_bwd(const void* dy, const void* z, const float*
     const uint32_t thresh = dropout_thresh16(dropout_p);
     if (dropout_p <= 0.f) df = nullptr;
     int blocks = ln_grid(T);
-    if (blocks > sm_count() * 2) blocks = sm_count() * 2;
     const int nv = (H / 8 + 31) / 32;
+    const int cap = nv <= 2 ? sm_count() * 2 : sm_count();       // resident blocks (register-limited); one wave
+    if (blocks > cap) blocks = cap;
     if (nv <= 2 && blocks < ln_grid(T)) blocks = ln_grid(T) < sm_count() * 4 ? ln_grid(T) : sm_count() * 4;   // two blocks per SM fit
     cudaError_t le;
 #define FEDB_LN_BWD(NVV) le = launch_pdl(ln_bwd_kernel<NVV>, dim3(blocks), dim3(LN_WARPS * 32), LN_WARPS * H * sizeof(float), \
