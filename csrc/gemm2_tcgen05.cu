@@ -36,6 +36,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) gemm2_tcgen05_kernel(const __gr
                                                                       const __grid_constant__ CUtensorMap tmB,
                                                                       const __grid_constant__ CUtensorMap tmC,
                                                                       const __grid_constant__ CUtensorMap tmC2,
+                                                                      const __grid_constant__ CUtensorMap tmAux,
                                                                       const GemmParams p) {
     using Cfg = G2Cfg<BN>;
     constexpr int STAGES = Cfg::STAGES;
@@ -45,6 +46,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) gemm2_tcgen05_kernel(const __gr
     __shared__ __align__(8) uint64_t empty_bar[STAGES];
     __shared__ __align__(8) uint64_t acc_full[2];
     __shared__ __align__(8) uint64_t acc_empty[2];
+    __shared__ __align__(8) uint64_t aux_bar[G2_EPI_WARPS][2];      // per epilogue warp and staging slot: aux tile landed
     __shared__ uint32_t tmem_base_slot;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -60,6 +62,8 @@ __global__ void __launch_bounds__(G2_THREADS, 1) gemm2_tcgen05_kernel(const __gr
         tma_prefetch_desc(&tmB);
         tma_prefetch_desc(&tmC);
         tma_prefetch_desc(&tmC2);
+        tma_prefetch_desc(&tmAux);
+        for (int w = 0; w < G2_EPI_WARPS; ++w) { mbar_init(&aux_bar[w][0], 1); mbar_init(&aux_bar[w][1], 1); }
         for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
         for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], 2 * G2_EPI_WARPS); }
         mbar_fence_init();
@@ -146,7 +150,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) gemm2_tcgen05_kernel(const __gr
         const int quad = warp & 3;
         const int half = (warp - 2) >> 2;
         const uint32_t stage = smem_u32(smem + STAGES * Cfg::STAGE_BYTES) + (uint32_t)(warp - 2) * G2_EPI_STAGE_BYTES;
-        uint32_t local = 0, slot_it = 0;
+        uint32_t local = 0, slot_it = 0, aux_phase = 0;
         for (int w = pair; w < total; w += n_pairs, ++local) {
             const int tile = w / p.splits;
             const int n_blk = tile % n_tiles, m_blk = tile / n_tiles;
@@ -154,8 +158,9 @@ __global__ void __launch_bounds__(G2_THREADS, 1) gemm2_tcgen05_kernel(const __gr
             const int split = w % p.splits;
             const bool has_k = split * kb_per_split < k_blocks;
             const int row = m_blk * 2 * G2_BM + (int)rank * G2_BM + quad * 32 + lane;
-            gemm_epilogue_tile_tma<BN, EPI>(p, &tmC, &tmC2, stage, slot_it, tmem_base + ((uint32_t)(quad * 32) << 16) + buf * BN,
-                                       row, n_blk * BN, half, has_k, &acc_full[buf], (local >> 1) & 1u);
+            gemm_epilogue_tile_tma<BN, EPI>(p, &tmC, &tmC2, &tmAux, stage, slot_it, aux_bar[warp - 2], aux_phase,
+                                            tmem_base + ((uint32_t)(quad * 32) << 16) + buf * BN, row, n_blk * BN, half, has_k,
+                                            &acc_full[buf], (local >> 1) & 1u);
             tc_fence_before_sync();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(&acc_empty[buf], 0);        // the leader's MMA warp owns this barrier
@@ -169,7 +174,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) gemm2_tcgen05_kernel(const __gr
 
 template <int A_MN, int B_MN, int BN, int EPI>
 static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& tc2,
-                        const GemmParams& p, int max_ctas, cudaStream_t s) {
+                        const CUtensorMap& taux, const GemmParams& p, int max_ctas, cudaStream_t s) {
     using Cfg = G2Cfg<BN>;
     const size_t smem = (size_t)Cfg::STAGES * Cfg::STAGE_BYTES + (size_t)G2_EPI_WARPS * G2_EPI_STAGE_BYTES + 1024;
     auto kern = gemm2_tcgen05_kernel<A_MN, B_MN, BN, EPI>;
@@ -197,7 +202,7 @@ static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const CUte
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl_enabled() ? 2 : 1;
-    FEDB_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, tc2, p));
+    FEDB_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, tc2, taux, p));
     return 0;
 }
 
@@ -215,8 +220,12 @@ int gemm2_dispatch(int layout, const void* A, int lda, const void* B, int ldb, c
     else       e = make_tmap_bf16_2d(&tb, B, (uint64_t)p.K, (uint64_t)p.N, (uint64_t)ldb, G2_BK, 64);
     if (e) return e;
     // output maps for the epilogue's TMA stores ([32 rows x 64 cols] boxes, 128B swizzle); unused outputs alias A's map
-    CUtensorMap tc = ta, tc2 = ta;
+    CUtensorMap tc = ta, tc2 = ta, taux = ta;
     if (p.epi != FEDB200_EPI_ATOMIC_F32 && p.epi != FEDB200_EPI_DISCARD) {
+        if (p.aux != nullptr) {
+            e = make_tmap_bf16_2d(&taux, p.aux, (uint64_t)p.M, (uint64_t)p.N, (uint64_t)p.ld_aux, 32, 64);
+            if (e) return e;
+        }
         if (p.out != nullptr) {
             e = make_tmap_bf16_2d(&tc, p.out, (uint64_t)p.M, (uint64_t)p.N, (uint64_t)p.ldo, 32, 64);
             if (e) return e;
@@ -230,7 +239,7 @@ int gemm2_dispatch(int layout, const void* A, int lda, const void* B, int ldb, c
     // that dispatches on p.epi at run time (its per-element branches cost ~20 % on these shapes).
 #define FEDB_G2_CASE(AM, BM, BNV, EP)                                                          \
     if (a_mn == AM && b_mn == BM && BN == BNV && (EP < 0 || p.epi == EP))                      \
-        return launch_gemm2<AM, BM, BNV, EP>(ta, tb, tc, tc2, p, max_ctas, s);
+        return launch_gemm2<AM, BM, BNV, EP>(ta, tb, tc, tc2, taux, p, max_ctas, s);
 #define FEDB_G2_LAYOUTS(BNV)                                                                   \
     FEDB_G2_CASE(0, 0, BNV, FEDB200_EPI_BIAS) FEDB_G2_CASE(0, 0, BNV, FEDB200_EPI_BIAS_DROP_RES) \
     FEDB_G2_CASE(0, 0, BNV, FEDB200_EPI_BIAS_GELU) FEDB_G2_CASE(0, 0, BNV, -1)                 \

@@ -182,7 +182,8 @@ __device__ __forceinline__ void stage_bf16x32(uint32_t slot, int lane, int sub, 
 
 template <int BN, int EPI = -1>
 __device__ __forceinline__ void gemm_epilogue_tile_tma(const GemmParams& p, const CUtensorMap* tm_out,
-                                                       const CUtensorMap* tm_out2, uint32_t stage, uint32_t& slot_it,
+                                                       const CUtensorMap* tm_out2, const CUtensorMap* tm_aux, uint32_t stage,
+                                                       uint32_t& slot_it, uint64_t* aux_bar, uint32_t& aux_phase,
                                                        uint32_t tmem_acc, int row, int col_base, int half, bool has_k,
                                                        uint64_t* acc_full, uint32_t parity) {
     const int epi = EPI >= 0 ? EPI : p.epi;      // compile-time in the specialised kernels: the dispatch below folds away
@@ -198,16 +199,30 @@ __device__ __forceinline__ void gemm_epilogue_tile_tma(const GemmParams& p, cons
     const bool two_out = epi == FEDB200_EPI_BIAS_GELU && p.out != nullptr;
     uint4 aux_raw[4];
     float bias_lane = 0.f;
+    // Residual / pre-activation tiles arrive by TMA into the SAME swizzled slots the result is later stored from (each
+    // thread reads its row's 16-byte chunks and overwrites them in place), issued for the whole tile before the
+    // accumulator is even complete; row-per-thread global loads were the epilogue's main stall (long scoreboard).
+    const bool aux_tma = needs_aux;
     auto fetch_aux = [&](int c) {
         const int col0 = col_base + c * 32;
         bias_lane = (p.bias != nullptr && c < N_CHUNKS && col0 + lane_id < p.N) ? __ldg(p.bias + col0 + lane_id) : 0.f;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            aux_raw[q] = make_uint4(0u, 0u, 0u, 0u);
-            if (needs_aux && row_ok && c < N_CHUNKS && col0 + q * 8 < p.N)
-                aux_raw[q] = __ldg(reinterpret_cast<const uint4*>(p.aux + (size_t)row * p.ld_aux + col0) + q);
-        }
+        for (int q = 0; q < 4; ++q) aux_raw[q] = make_uint4(0u, 0u, 0u, 0u);
     };
+    if (aux_tma) {
+        if (lane_id == 0) {
+            tma_store_wait_read<0>();            // both slots: last tile's stores have been read out
+            uint32_t k = 0;
+            for (int g = half; g < N_CHUNKS / 2; g += 2, ++k) {
+                const int gcol0 = col_base + g * 64;
+                if (gcol0 >= p.N) break;
+                const uint32_t sl = (slot_it + k) & 1u;
+                mbar_expect_tx(&aux_bar[sl], 4096u);
+                tma_load_smem_2d(stage + sl * 4096u, tm_aux, &aux_bar[sl], gcol0, row);
+            }
+        }
+        __syncwarp();
+    }
     fetch_aux(2 * half);
     mbar_wait(acc_full, parity);
     tc_fence_after_sync();
@@ -221,9 +236,14 @@ __device__ __forceinline__ void gemm_epilogue_tile_tma(const GemmParams& p, cons
             if (lane_id == 0) tma_store_wait_read<0>();
             slot_a = stage; slot_b = stage + 4096u;
         } else {
-            if (lane_id == 0) tma_store_wait_read<1>();
-            slot_a = stage + (slot_it & 1u) * 4096u;
+            if (!aux_tma && lane_id == 0) tma_store_wait_read<1>();
+            const uint32_t sl = slot_it & 1u;
+            slot_a = stage + sl * 4096u;
             ++slot_it;
+            if (aux_tma) {
+                mbar_wait(&aux_bar[sl], (aux_phase >> sl) & 1u);
+                aux_phase ^= 1u << sl;
+            }
         }
         __syncwarp();
 #pragma unroll
@@ -235,6 +255,13 @@ __device__ __forceinline__ void gemm_epilogue_tile_tma(const GemmParams& p, cons
             tmem_ld_32x32(tmem_acc + c * 32, raw);
             float r[32];
             if (epi == FEDB200_EPI_BIAS_DROP_RES || epi == FEDB200_EPI_MUL_GELU_GRAD || epi == FEDB200_EPI_ADD) {
+                if (aux_tma) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const uint32_t j = (uint32_t)(sub * 4 + q);
+                        aux_raw[q] = ld_shared_v4(slot_a + (uint32_t)lane_id * 128u + ((j ^ ((uint32_t)lane_id & 7u)) << 4));
+                    }
+                }
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const float2 a0 = unpack_bf16x2(aux_raw[q].x), a1 = unpack_bf16x2(aux_raw[q].y);
