@@ -206,3 +206,26 @@ def test_report_tables_match_detectors_and_timing_model(tmp_path):
     assert (tmp_path / "t.csv").read_text().startswith("detector,removed,source,sync_s,async_s")
     sw = sweep_table({5: {"latency_min": 1.0, "global_accuracies": [0.5, 0.6]}, 10: {"latency_min": 2.0, "global_accuracies": [0.7]}})
     assert [r["workers"] for r in sw] == [5, 10] and sw[0]["final_accuracy"] == 0.6
+
+
+def test_result_figures_svg(tmp_path):
+    """C26: the notebooks' figure set is written as SVG from computed tables (no matplotlib in the image)."""
+    import json
+    import xml.etree.ElementTree as ET
+    from fedb200.utils import plots
+    sweeps = {"centralised": {5: {"latency_min": 1.0, "global_accuracies": [0.5, 0.8], "memory_growth_gb": 0.2},
+                              10: {"latency_min": 2.0, "global_accuracies": [0.6, 0.85], "memory_growth_gb": 0.3}},
+              "decentralised": {5: {"latency_min": 0.7, "global_accuracies": [0.55, 0.82], "memory_growth_gb": 0.1}}}
+    curves = {"serverless-IID": {"global_accuracies": [0.5, 0.7, 0.8]}, "server-IID": {"global_accuracies": [0.5, 0.6, 0.75]}}
+    (tmp_path / "s.json").write_text(json.dumps(sweeps))
+    (tmp_path / "c.json").write_text(json.dumps(curves))
+    written = plots.main(["--out", str(tmp_path / "fig"), "--results", str(tmp_path / "s.json"), "--curves", str(tmp_path / "c.json")])
+    assert len(written) == 5
+    for p in written:
+        root = ET.parse(p).getroot()                      # well-formed XML
+        assert root.tag.endswith("svg")
+    info = ET.parse(written[0]).getroot()
+    bars = [e for e in info.iter() if e.tag.endswith("rect") and e.find("{http://www.w3.org/2000/svg}title") is not None]
+    assert len(bars) == 8                                 # 4 detector settings x (sync, async)
+    lines = [e for e in ET.parse(written[-1]).getroot().iter() if e.tag.endswith("polyline")]
+    assert len(lines) == 2
