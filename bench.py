@@ -195,7 +195,7 @@ def run_fedb200(args):
     e2e_s = time.perf_counter() - t0
     clocks = sampler.stop() if rank == 0 else None
     h2d = (rt.runner.h2d_bytes - h2d0) / K
-    d2h = (rt.runner.d2h_bytes - d2h0) / K + (32 * len(rt.local_ids) if rt.ledger is not None else 0)
+    d2h = (rt.runner.d2h_bytes - d2h0) / K        # loss + Merkle root + evaluation sums, one synchronisation per round
 
     # max over ranks / sums over ranks
     t = torch.tensor([dev_ms, e2e_s], dtype=torch.float64, device=dev)

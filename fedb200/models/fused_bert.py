@@ -435,13 +435,17 @@ class FusedRunner:
         return self.logits[:B].clone()
 
     # ---- runner interface (same as TorchRunner) ------------------------------------------------------------------------------
-    def train_epochs(self, loader, epochs: int = 1) -> Dict[str, float]:
+    def train_epochs(self, loader, epochs: int = 1, lazy: bool = False) -> Dict[str, float]:
+        """``lazy``: return the last loss as a device scalar (the caller reads it back with the round's other
+        results in one synchronisation, :class:`fedb200.utils.readback.HostReadback`)."""
         self.opt.reset()                          # fresh optimizer per call (server_IID_IMDB.py:109)
         loss, n = None, 0
         for _ in range(epochs):
             for idx in loader.batch_indices():
                 loss = self.train_step(collate_packed(loader.dataset, idx))
                 n += 1
+        if lazy:
+            return {"loss": loss if loss is not None else torch.full((), float("nan"), device=self.device), "steps": n}
         out = float(loss.item()) if loss is not None else float("nan")     # one D2H read per local epoch
         self.d2h_bytes += 4
         return {"loss": out, "steps": n}
@@ -480,6 +484,16 @@ class FusedRunner:
             loss_sum += per_sample[o:o + n].mean()
             o += n
         return loss_sum, correct
+
+    def evaluate_lazy(self, loader):
+        """Like :meth:`evaluate` without the host read: (loss_sum, correct) device scalars + (n_dataset, n_evaluated)."""
+        micro, ref_sizes = self.eval_plan(loader)
+        n_ds = max(len(loader.dataset), 1)
+        if not micro:
+            z = torch.zeros((), device=self.device)
+            return z, z.to(torch.int64), n_ds, 0
+        loss_sum, correct = self.evaluate_packed(micro, ref_sizes)
+        return loss_sum, correct, n_ds, sum(ref_sizes)
 
     def evaluate(self, loader) -> Tuple[float, float]:
         micro, ref_sizes = self.eval_plan(loader)

@@ -234,8 +234,9 @@ def merkle_root(leaves: torch.Tensor, scratch: Optional[torch.Tensor] = None, ro
 _SHA_WS = {}
 
 
-def sha256_copy_root(src: torch.Tensor, dst: Optional[torch.Tensor], chunk_bytes: int = 4096) -> bytes:
-    """Copy ``src`` -> ``dst`` hashing on the way; returns the Merkle root (host bytes, syncs the stream)."""
+def sha256_copy_root(src: torch.Tensor, dst: Optional[torch.Tensor], chunk_bytes: int = 4096, to_host: bool = True):
+    """Copy ``src`` -> ``dst`` hashing on the way; returns the Merkle root as host bytes (syncs the stream) or, with
+    ``to_host=False``, as a fresh 32-byte device tensor (no sync)."""
     nbytes = src.numel() * src.element_size()
     n_chunks = (nbytes + chunk_bytes - 1) // chunk_bytes
     key = (src.device, n_chunks)
@@ -246,6 +247,8 @@ def sha256_copy_root(src: torch.Tensor, dst: Optional[torch.Tensor], chunk_bytes
     leaves, scratch, root = _SHA_WS[key]
     sha256_leaves(src, dst, chunk_bytes, leaves)
     merkle_root(leaves, scratch, root)
+    if not to_host:
+        return root.clone()
     return bytes(root.cpu().numpy().tobytes())
 
 

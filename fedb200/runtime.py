@@ -36,6 +36,7 @@ from .parallel import init_distributed, local_peer_ids, make_comm, peers_per_ran
 from .server.fedavg import FedAvg, weighted_average
 from .trainer.local import make_runner, resolve_device
 from .utils import MetricsLogger, OverheadMeter, PhaseTimer
+from .utils.readback import HostReadback
 
 
 class FedRuntime:
@@ -63,6 +64,8 @@ class FedRuntime:
         self.acc = self.comm.alloc("acc", self.D)
         self.deltas = None
         self.timer = PhaseTimer(self.device.type == "cuda")
+        self.readback = HostReadback(self.device)
+        self._loader_cache: Dict = {}
         self.topo = Topology.from_name(cfg.topology, self.N, cfg.seed)
         self.injector = AnomalyInjector(self.N, cfg.inject_anomalies, cfg.inject_kind, seed=cfg.seed)
         if cfg.inject_kind == "slowlink" and cfg.inject_anomalies > 0:
@@ -128,22 +131,25 @@ class FedRuntime:
         return size
 
     # ---- one client visit ----------------------------------------------------------------------
-    def _train_peer(self, li: int, k: int, rnd: int, start: torch.Tensor) -> Dict:
+    def _train_peer(self, li: int, k: int, rnd: int, start: torch.Tensor, lazy: bool = False) -> Dict:
+        """``lazy``: ``loss`` and ``root`` stay device tensors (resolved by the caller with one synchronisation per round)."""
         pin = self.device.type == "cuda"
-        tr, te = client_loaders(self.corpus, self.cfg.data, k, rnd, pin=pin)
+        tr, te = self._loader_cache.pop((k, rnd), None) or client_loaders(self.corpus, self.cfg.data, k, rnd, pin=pin)
         with self.timer.phase("train"):
             self.runner.load_flat(start)
             self.runner.sync_shadow()
-            stats = self.runner.train_epochs(tr, self.cfg.local_epochs)
+            stats = self.runner.train_epochs(tr, self.cfg.local_epochs, lazy=lazy) if lazy else \
+                self.runner.train_epochs(tr, self.cfg.local_epochs)
         corrupted = self.injector.maybe_corrupt(k, self.runner.flat, start, rnd)
         with self.timer.phase("publish"):
-            root = self._publish(li)
+            root = self._publish(li, lazy=lazy)
         return {"peer": k, "batches": len(tr), "samples": tr.num_samples, "tokens": tr.num_tokens(),
                 "loss": stats["loss"], "root": root, "corrupted": corrupted, "testloader": te}
 
-    def _publish(self, li: int) -> Optional[bytes]:
+    def _publish(self, li: int, lazy: bool = False):
         """Copy the trained weights into the peer-visible slot; hash them on the way if the ledger
-        is on (fused ``sha256_copy`` kernel on a GPU)."""
+        is on (fused ``sha256_copy`` kernel on a GPU).  Returns the Merkle root (bytes, or a 32-byte device tensor when
+        ``lazy`` on a GPU) or None without a ledger."""
         src, dst = self.runner.flat, self.slots[li]
         if self.ledger is None:
             dst.copy_(src)
@@ -151,7 +157,7 @@ class FedRuntime:
         if src.is_cuda:
             from .ops import cuda_ops
             self.comm.launches += 2
-            return cuda_ops.sha256_copy_root(src, dst, self.ledger.chunk_bytes)
+            return cuda_ops.sha256_copy_root(src, dst, self.ledger.chunk_bytes, to_host=not lazy)
         dst.copy_(src)
         from .ledger.merkle import merkle_root
         return merkle_root(src.detach().numpy().tobytes(), self.ledger.chunk_bytes)
@@ -253,13 +259,25 @@ class FedRuntime:
         else:
             for li, k in enumerate(self.local_ids):
                 start = self.global_flat if self.peer_state is None else self.peer_state[li]
-                infos.append(self._train_peer(li, k, rnd, start))
-        local_acc = []
+                infos.append(self._train_peer(li, k, rnd, start, lazy=True))
+        # Device results of this round (last training loss, Merkle root, evaluation sums) are queued on the readback and
+        # resolved by ONE stream synchronisation after the global evaluation has been issued; the ledger bookkeeping and
+        # the cross-rank gather then run on the host while the GPU finishes that evaluation.
+        rb = self.readback
+        rb.reset()
+        rb_bytes0 = rb.bytes_read
+        for i in infos:
+            if isinstance(i["loss"], torch.Tensor):
+                i["loss"] = rb.push(i["loss"].to(torch.float32))
+            if isinstance(i["root"], torch.Tensor):
+                i["root"] = rb.push(i["root"])
+        local_ev = []
         with self.timer.phase("evaluate_local"):
             for li, i in enumerate(infos):                   # client.evaluate_model() after training (:264)
                 self.runner.load_flat(self.slots[li])
                 self.runner.sync_shadow()
-                local_acc.append(self.runner.evaluate(i["testloader"])[1])
+                ls, co, n_ds, tot = self.runner.evaluate_lazy(i["testloader"])
+                local_ev.append((rb.push(co.to(torch.int64)), tot))
         self.masked = self._score(rnd)
         with self.timer.phase("aggregate"):
             ws = [0.0 if i["peer"] in self.masked else 1.0 for i in infos]          # unweighted mean (:269)
@@ -280,14 +298,30 @@ class FedRuntime:
         if cfg.route_optimizer and self.ledger is not None:
             for i in infos:
                 routes[i["peer"]] = optimise_route(self.topo, self.nbytes, i["peer"], removed=self.masked)
-        self._ledger_append(rnd, infos, (lambda p: []) if not routes else
-                            (lambda p: routes[p].routes[max(routes[p].routes, key=lambda j: routes[p].latency[j])]
-                             if p in routes and routes[p].routes else []))
         with self.timer.phase("evaluate_global"):
             self.runner.load_flat(self.global_flat)
             self.runner.sync_shadow()
             te = global_test_loader(self.corpus, cfg.data, rnd, pin=self.device.type == "cuda")
-            gl, ga = self.runner.evaluate(te)
+            g_ls, g_co, g_nds, g_tot = self.runner.evaluate_lazy(te)
+            h_gl, h_gc = rb.push(g_ls.to(torch.float32)), rb.push(g_co.to(torch.int64))
+        # next round's loaders are built now, while the GPU is still busy with the global evaluation
+        self._loader_cache.clear()
+        if rnd + 1 < cfg.num_rounds:
+            for k in self.local_ids:
+                self._loader_cache[(k, rnd + 1)] = client_loaders(self.corpus, cfg.data, k, rnd + 1, pin=self.device.type == "cuda")
+        rb.sync()                                            # the round's only device -> host synchronisation
+        self.runner.d2h_bytes = getattr(self.runner, "d2h_bytes", 0) + (rb.bytes_read - rb_bytes0)
+        for i in infos:
+            if isinstance(i["loss"], tuple):
+                i["loss"] = float(rb.get(i["loss"]))
+            if isinstance(i["root"], tuple):
+                i["root"] = bytes(rb.get(i["root"]).numpy().tobytes())
+        local_acc = [(int(rb.get(h)) / tot if tot else 0.0) for h, tot in local_ev]
+        gl = float(rb.get(h_gl)) / g_nds
+        ga = int(rb.get(h_gc)) / g_tot if g_tot else 0.0
+        self._ledger_append(rnd, infos, (lambda p: []) if not routes else
+                            (lambda p: routes[p].routes[max(routes[p].routes, key=lambda j: routes[p].latency[j])]
+                             if p in routes and routes[p].routes else []))
         self.global_accuracies.append(float(ga))
         locs = sum(self.comm.all_gather_object([float(a) for a in local_acc]), [])
         return {"accuracy": float(ga), "loss": float(gl), "local_accuracy": locs,

@@ -68,7 +68,7 @@ class TorchRunner:
         pass
 
     # ---- loops ------------------------------------------------------------------------
-    def train_epochs(self, loader, epochs: int = 1) -> Dict[str, float]:
+    def train_epochs(self, loader, epochs: int = 1, lazy: bool = False) -> Dict[str, float]:
         self.opt.reset()                      # AdamW(...) re-created each call (:109)
         self.module.train()
         last, n_steps = float("nan"), 0
@@ -82,7 +82,16 @@ class TorchRunner:
                 n_steps += 1
                 self.samples_seen += int(batch["labels"].numel())
                 self.tokens_seen += int(batch["attention_mask"].sum())
+        if lazy:                              # same contract as FusedRunner: a tensor the caller reads back later
+            return {"loss": torch.tensor(last, dtype=torch.float32), "steps": n_steps}
         return {"loss": last, "steps": n_steps}
+
+    def evaluate_lazy(self, loader):
+        loss, acc = self.evaluate(loader)
+        n_ds = max(len(loader.dataset), 1)
+        total = sum(len(i) for i in loader.batch_indices())
+        return (torch.tensor(loss * n_ds, dtype=torch.float32), torch.tensor(int(round(acc * total)), dtype=torch.int64),
+                n_ds, total)
 
     @torch.no_grad()
     def evaluate(self, loader) -> Tuple[float, float]:
