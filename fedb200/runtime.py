@@ -192,19 +192,24 @@ class FedRuntime:
         self.log.log("score", round=rnd, masked=bad, ranks=[round(float(x), 6) for x in ranks], band=band)
         return bad
 
-    def _ledger_append(self, rnd: int, infos: List[Dict], route_of=None) -> None:
+    def _ledger_append(self, rnd: int, infos: List[Dict], route_of=None, extra=None):
+        """Append this round's blocks on every rank.  ``extra`` (any picklable) rides on the same cross-rank gather; the
+        list of all ranks' extras is returned (one host collective per round instead of two)."""
         if self.ledger is None:
-            return
+            return self.comm.all_gather_object(extra) if extra is not None else None
         with self.timer.phase("ledger"):
             # every rank contributes (peer, root, n_k, route) of its own peers; all ranks append the same blocks
             mine = [(i["peer"], i["root"].hex(), i["batches"], list(route_of(i["peer"])) if route_of else [])
                     for i in infos]
-            every = sorted(sum(self.comm.all_gather_object(mine), []))
+            gathered = self.comm.all_gather_object((mine, extra))
+            every = sorted(sum((g[0] for g in gathered), []))
+            extras = [g[1] for g in gathered]
             for peer, root_hex, n, route in every:
                 self.ledger.append(rnd, peer, BROADCAST, bytes.fromhex(root_hex), self.nbytes, n, route,
                                    timestamp_ns=rnd * 1_000_000 + peer)
             if self.cfg.num_rounds <= 4 or rnd % 5 == 0:
                 self.ledger.assert_valid()
+        return extras if extra is not None else None
 
     # ---- server mode -----------------------------------------------------------------------------
     def round_server(self, rnd: int) -> Dict:
@@ -319,11 +324,11 @@ class FedRuntime:
         local_acc = [(int(rb.get(h)) / tot if tot else 0.0) for h, tot in local_ev]
         gl = float(rb.get(h_gl)) / g_nds
         ga = int(rb.get(h_gc)) / g_tot if g_tot else 0.0
-        self._ledger_append(rnd, infos, (lambda p: []) if not routes else
-                            (lambda p: routes[p].routes[max(routes[p].routes, key=lambda j: routes[p].latency[j])]
-                             if p in routes and routes[p].routes else []))
+        locs = self._ledger_append(rnd, infos, (lambda p: []) if not routes else
+                                   (lambda p: routes[p].routes[max(routes[p].routes, key=lambda j: routes[p].latency[j])]
+                                    if p in routes and routes[p].routes else []), extra=[float(a) for a in local_acc])
+        locs = sum(locs, [])
         self.global_accuracies.append(float(ga))
-        locs = sum(self.comm.all_gather_object([float(a) for a in local_acc]), [])
         return {"accuracy": float(ga), "loss": float(gl), "local_accuracy": locs,
                 "train_loss": float(np.mean([i["loss"] for i in infos])) if infos else None,
                 "samples": sum(i["samples"] for i in infos), "tokens": sum(i["tokens"] for i in infos)}

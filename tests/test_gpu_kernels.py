@@ -234,3 +234,32 @@ def test_head_fwd_bwd(cuda_lib, C):
     torch.testing.assert_close(gbp, bpr.grad, rtol=1e-3, atol=1e-4)
     torch.testing.assert_close(dx[first.long()].float(), h0.grad, rtol=2e-2, atol=1e-4)
     assert torch.count_nonzero(dx) <= B * H
+
+
+def test_gemm_pdl_and_store_modes_agree(cuda_lib):
+    """The same GEMM through (PDL on/off) x (TMA-store / direct-store epilogue) gives identical bits."""
+    from fedb200.ops import _lib
+    ops = _ops()
+    torch.manual_seed(3)
+    M, N, K = 1000, 768, 512
+    A = torch.randn(M, K, device="cuda").bfloat16()
+    B = (torch.randn(N, K, device="cuda") * 0.05).bfloat16()
+    bias = torch.randn(N, device="cuda")
+    res = torch.randn(M, N, device="cuda").bfloat16()
+    outs = []
+    try:
+        for pdl in (1, 0):
+            for mode in (0, 4):
+                _lib.lib().fedb200_set_pdl(pdl)
+                _lib.lib().fedb200_set_gemm_mode(mode)
+                out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+                ops.gemm(0, A, B, out, M, N, K, epi=ops.EPI_BIAS_DROP_RES, bias=bias, aux=res, seed=5, dropout_p=0.0)
+                torch.cuda.synchronize()
+                outs.append(out)
+    finally:
+        _lib.lib().fedb200_set_pdl(1)
+        _lib.lib().fedb200_set_gemm_mode(0)
+    ref = (A.float() @ B.float().T + bias + res.float())
+    assert (outs[0].float() - ref).abs().max().item() < 0.06 * ref.abs().max().item() + 0.05
+    for o in outs[1:]:
+        assert torch.equal(o, outs[0])

@@ -167,3 +167,21 @@ def test_scheduled_async_executor_matches_schedule_and_ledger():
                                  cfg.staleness_decay)
     assert [(e.peer, e.epoch, e.sources, e.slot) for e in again.events] == [(e.peer, e.epoch, e.sources, e.slot) for e in sched.events]
     rt.close()
+
+
+def test_host_readback_roundtrip():
+    """HostReadback: queued tensors of mixed dtype/shape come back bit-exact after one sync; reset() recycles the buffer."""
+    import torch
+    from fedb200.utils.readback import HostReadback
+    rb = HostReadback("cpu", capacity=256)
+    a, b, c = torch.tensor(3.25), torch.arange(32, dtype=torch.uint8), torch.tensor(-7, dtype=torch.int64)
+    ha, hb, hc = rb.push(a), rb.push(b), rb.push(c)
+    rb.sync()
+    assert float(rb.get(ha)) == 3.25 and int(rb.get(hc)) == -7 and torch.equal(rb.get(hb), b)
+    assert rb.bytes_read == 4 + 32 + 8
+    rb.reset()
+    assert rb.off == 0
+    import pytest
+    with pytest.raises(RuntimeError):
+        for _ in range(20):
+            rb.push(b)
