@@ -178,8 +178,11 @@ int gemm2_dispatch(int layout, const void* A, int lda, const void* B, int ldb, c
 
 using namespace fedb;
 
-// 0 = auto (CTA pairs whenever the shape allows), 1 = force the 1-CTA kernel, 2 = force pairs.  Also settable through
-// the FEDB200_GEMM_MODE environment variable (read once); used by the A/B benchmark in bench/diag_gemm.py.
+// Diagnostic switch (production = 0), also settable through the FEDB200_GEMM_MODE environment variable (read once); used
+// by the A/B benchmarks bench/diag_gemm.py and bench/diag_epi.py:
+//   0 auto (CTA pairs whenever N >= 128)      1 force the 1-CTA kernel        3 pair kernel with 128-wide tiles
+//   4 pair kernel with direct row-per-thread stores / loads instead of the TMA-staged epilogue
+//   5 pair kernel, epilogue stages the tile but skips the global store (isolates store traffic; results are garbage)
 static int g_gemm_mode = -1;
 extern "C" int fedb200_set_gemm_mode(int mode) {
     g_gemm_mode = mode;

@@ -213,23 +213,41 @@ class FedRuntime:
 
     # ---- server mode -----------------------------------------------------------------------------
     def round_server(self, rnd: int) -> Dict:
-        infos = [self._train_peer(li, k, rnd, self.global_flat) for li, k in enumerate(self.local_ids)]
+        infos = [self._train_peer(li, k, rnd, self.global_flat, lazy=True) for li, k in enumerate(self.local_ids)]
+        rb = self.readback                               # one device -> host synchronisation per round (see round_serverless)
+        rb.reset()
+        rb_bytes0 = rb.bytes_read
+        for i in infos:
+            if isinstance(i["loss"], torch.Tensor):
+                i["loss"] = rb.push(i["loss"].to(torch.float32))
+            if isinstance(i["root"], torch.Tensor):
+                i["root"] = rb.push(i["root"])
         self.masked = self._score(rnd)
         with self.timer.phase("aggregate"):
             ws = [0.0 if i["peer"] in self.masked else float(i["batches"]) for i in infos]   # n_k = len(trainloader)
             self._local_weighted_sum(ws)
             self.comm.weighted_mean(self.acc, sum(ws), self.global_flat)
-        self._ledger_append(rnd, infos)
         with self.timer.phase("evaluate"):
-            ev = []
+            pend = []
             self.runner.load_flat(self.global_flat)
             self.runner.sync_shadow()
             for i in infos:
                 te = i["testloader"]
-                loss, acc = self.runner.evaluate(te)
-                ev.append((float(loss), len(te), {"accuracy": float(acc), "loss": float(loss)}))
-            ev = sum(self.comm.all_gather_object(ev), [])
-            loss, metrics = self.strategy.aggregate_evaluate(rnd, ev)
+                ls, co, n_ds, tot = self.runner.evaluate_lazy(te)
+                pend.append((rb.push(ls.to(torch.float32)), rb.push(co.to(torch.int64)), n_ds, tot, len(te)))
+        rb.sync()
+        self.runner.d2h_bytes = getattr(self.runner, "d2h_bytes", 0) + (rb.bytes_read - rb_bytes0)
+        for i in infos:
+            if isinstance(i["loss"], tuple):
+                i["loss"] = float(rb.get(i["loss"]))
+            if isinstance(i["root"], tuple):
+                i["root"] = bytes(rb.get(i["root"]).numpy().tobytes())
+        ev = []
+        for h_l, h_c, n_ds, tot, n_batches in pend:
+            loss, acc = float(rb.get(h_l)) / n_ds, (int(rb.get(h_c)) / tot if tot else 0.0)
+            ev.append((float(loss), n_batches, {"accuracy": float(acc), "loss": float(loss)}))
+        ev = sum(self._ledger_append(rnd, infos, extra=ev), [])
+        loss, metrics = self.strategy.aggregate_evaluate(rnd, ev)
         self.global_accuracies.append(metrics.get("accuracy", float("nan")))
         return {"loss_distributed": loss, **metrics, "train_loss": float(np.mean([i["loss"] for i in infos])) if infos else None,
                 "samples": sum(i["samples"] for i in infos), "tokens": sum(i["tokens"] for i in infos)}
