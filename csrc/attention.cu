@@ -354,7 +354,7 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
     uint8_t* sdO = sQ + 2 * AT_TILE;         // 2 stages
     uint8_t* sP = sdO + 2 * AT_TILE;         // Pd^T : 2 buffers x 2 tiles (q 0-63 | 64-127), rows = kv
     uint8_t* sdS = sP + 4 * AT_TILE;         // dS^T : 2 buffers x 2 tiles
-    __shared__ __align__(8) uint64_t kv_full, qdo_full[2], qdo_empty[2], sdp_full, pds_ready, dq_full, dq_empty, dkv_full;
+    __shared__ __align__(8) uint64_t kv_full, qdo_full[2], qdo_empty[2], sdp_full, pds_ready, dq_full, dq_empty, dkv_full, sdp_free;
     __shared__ uint32_t tmem_slot;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -364,7 +364,7 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
         mbar_init(&kv_full, 1);
         for (int s = 0; s < 2; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_empty[s], 1); }
         mbar_init(&sdp_full, 1); mbar_init(&pds_ready, ATB_CTHREADS); mbar_init(&dq_full, 1); mbar_init(&dq_empty, ATB_CTHREADS);
-        mbar_init(&dkv_full, 1);
+        mbar_init(&dkv_full, 1); mbar_init(&sdp_free, ATB_CTHREADS);
         mbar_fence_init();
     }
     if (warp == 1) tmem_alloc(&tmem_slot, 512);
@@ -417,7 +417,7 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
             const int s = i & 1;
             const uint32_t aQ = smem_u32(sQ + s * AT_TILE), aO = smem_u32(sdO + s * AT_TILE);
             const uint32_t aPb = aP + s * 2 * AT_TILE, aSb = aS + s * 2 * AT_TILE;
-            mbar_wait(&pds_ready, (uint32_t)i & 1u);          // tile i: S^T/dP^T consumed, Pd^T/dS^T written
+            mbar_wait(&sdp_free, (uint32_t)i & 1u);           // tile i: S^T/dP^T are in the compute warps' registers
             if (i + 1 < n_q) {
                 const int s1 = s ^ 1;
                 mbar_wait(&qdo_full[s1], (uint32_t)((i + 1) >> 1) & 1u);
@@ -432,6 +432,7 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
                 }
                 __syncwarp();
             }
+            mbar_wait(&pds_ready, (uint32_t)i & 1u);          // tile i: Pd^T/dS^T written
             tc_fence_after_sync();
             if (elect_one()) {
 #pragma unroll
@@ -526,6 +527,10 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
                 tmem_ld_32x16(tm_st + lane_addr + c0, rs);
                 tmem_ld_32x16(tm_dpt + lane_addr + c0, rp);
                 tmem_ld_wait();
+                if (hc == 1) {                   // S^T/dP^T fully read: the MMA warp may overwrite them with tile i+1 now
+                    tc_fence_before_sync();
+                    mbar_arrive(&sdp_free);
+                }
                 float pd[16], ds[16];
                 // The element loop is instantiated per (dropout source, masking) combination and selected by one
                 // warp-uniform switch: with the conditions inside the loop every element carried its own branches
