@@ -246,8 +246,15 @@ class FusedRunner:
         return self.arena.state_dict()
 
     def load_flat(self, flat: torch.Tensor) -> None:
+        """Overwrite the fp32 master with ``flat``.  The copy also writes the bf16 shadow in the same pass (one read of
+        the source instead of copy + cast); the ``sync_shadow()`` that callers issue right after is then a no-op."""
         if flat.data_ptr() != self.arena.flat.data_ptr():
-            self.arena.flat.copy_(flat)
+            if flat.is_cuda and flat.dtype == torch.float32 and flat.is_contiguous() and flat.numel() == self.arena.flat.numel():
+                self.ops.mix_n([flat], [1.0], self.arena.flat, self.shadow.flat)
+                self._shadow_fresh = True
+            else:
+                self.arena.flat.copy_(flat)
+                self._shadow_fresh = False
 
     def load_state_dict(self, state: Dict[str, torch.Tensor]) -> None:
         missing = set(self.arena.views) ^ set(state)
@@ -257,6 +264,9 @@ class FusedRunner:
 
     def sync_shadow(self) -> None:
         """Refresh the bf16 tensor-core copy after the fp32 master was overwritten (load / aggregation)."""
+        if getattr(self, "_shadow_fresh", False):      # load_flat() just wrote it; anything else since must call us again
+            self._shadow_fresh = False
+            return
         self.ops.cast_bf16(self.arena.flat, self.shadow.flat)
 
     # ---- helpers -----------------------------------------------------------------------------------------------
