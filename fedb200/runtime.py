@@ -297,8 +297,9 @@ class FedRuntime:
         local_ev = []
         with self.timer.phase("evaluate_local"):
             for li, i in enumerate(infos):                   # client.evaluate_model() after training (:264)
-                self.runner.load_flat(self.slots[li])
-                self.runner.sync_shadow()
+                if not (len(infos) == 1 and not i["corrupted"] and cfg.serverless_semantics != "handoff"):
+                    self.runner.load_flat(self.slots[li])    # with one local peer the runner still holds exactly these
+                    self.runner.sync_shadow()                # weights (and AdamW kept the bf16 shadow current)
                 ls, co, n_ds, tot = self.runner.evaluate_lazy(i["testloader"])
                 local_ev.append((rb.push(co.to(torch.int64)), tot))
         self.masked = self._score(rnd)
