@@ -107,3 +107,75 @@ def build_async_schedule(topo: Topology, nbytes: float, epochs_per_peer: int, du
                           sorted(eng.masked))
     sched._slot = slot_of
     return sched
+
+
+def verify_schedule(sched: AsyncSchedule, num_peers: int, world: int, trials: int = 16, seed: int = 0) -> Dict[str, int]:
+    """Protocol-level check of the flag handshake the executor (``FedRuntime.run_async_scheduled``) performs.
+
+    (A) *Ordering*: every wait of an event — ``pub[s] >= e`` for each mixed source version, ``done[c] >= ce`` for each
+    consumer of the version its outbox slot still holds — targets an event with a smaller global index, and each rank
+    runs its own events in index order; by induction no rank can wait forever.
+    (B) *Safety under any interleaving*: ranks are simulated as independent state machines that advance in a random
+    order (``trials`` different interleavings), blocking exactly where the executor blocks.  Whenever a mix reads version
+    ``(s, e)`` the simulated outbox slot must hold exactly that version (published, and not yet overwritten); a violation
+    means a missing or insufficient wait.  Returns counters; raises ``AssertionError`` with the offending event otherwise.
+    """
+    from ..parallel.placement import owner_of
+    by_version = {(ev.peer, ev.epoch): ev for ev in sched.events}
+    # ---- (A) every wait points backwards in the one global order ----
+    n_waits = 0
+    for ev in sched.events:
+        for s, e in zip(ev.sources, ev.source_epochs):
+            src = by_version.get((s, e))
+            assert src is not None, f"event {ev.index} mixes version {(s, e)} that nobody publishes"
+            assert src.index < ev.index, f"event {ev.index} waits on pub{(s, e)} published later (event {src.index})"
+            n_waits += 1
+        for c, ce in ev.overwrite_waits:
+            con = by_version.get((c, ce))
+            assert con is not None and con.index < ev.index, f"event {ev.index} waits on done{(c, ce)} that is not earlier"
+            n_waits += 1
+    per_rank: List[List[ScheduledEvent]] = [[] for _ in range(world)]
+    for ev in sched.events:
+        per_rank[owner_of(ev.peer, num_peers, world)[0]].append(ev)
+    for evs in per_rank:
+        assert all(a.index < b.index for a, b in zip(evs, evs[1:])), "a rank's events are not in global order"
+    # ---- (B) randomised interleavings of the per-rank state machines ----
+    rng = np.random.default_rng(seed)
+    reads = 0
+    for _ in range(trials):
+        pub = [0] * num_peers
+        done = [0] * num_peers
+        slots: Dict[Tuple[int, int], Tuple[int, int]] = {}        # (peer, slot) -> version held
+        pc = [[0, 0] for _ in range(world)]                       # per rank: [event cursor, phase 0 = mix, 1 = publish]
+        remaining = sum(len(e) for e in per_rank)
+        while remaining:
+            runnable = []
+            for r in range(world):
+                i, ph = pc[r]
+                if i >= len(per_rank[r]):
+                    continue
+                ev = per_rank[r][i]
+                if ph == 0:
+                    ok = all(pub[s] >= e for s, e in zip(ev.sources, ev.source_epochs))
+                else:
+                    ok = all(done[c] >= ce for c, ce in ev.overwrite_waits)
+                if ok:
+                    runnable.append(r)
+            assert runnable, f"deadlock: cursors {pc}"
+            r = int(runnable[rng.integers(len(runnable))])
+            i, ph = pc[r]
+            ev = per_rank[r][i]
+            if ph == 0:
+                for s, e in zip(ev.sources, ev.source_epochs):
+                    held = slots.get((s, sched.slot_of(s, e)))
+                    assert held == (s, e), (f"event {ev.index} (peer {ev.peer} epoch {ev.epoch}) reads version {(s, e)} "
+                                            f"but slot {sched.slot_of(s, e)} of peer {s} holds {held}")
+                    reads += 1
+                done[ev.peer] = ev.epoch
+                pc[r][1] = 1
+            else:
+                slots[(ev.peer, ev.slot)] = (ev.peer, ev.epoch)
+                pub[ev.peer] = ev.epoch
+                pc[r] = [i + 1, 0]
+                remaining -= 1
+    return {"events": len(sched.events), "waits": n_waits, "reads_checked": reads, "interleavings": trials}

@@ -229,3 +229,27 @@ def test_result_figures_svg(tmp_path):
     assert len(bars) == 8                                 # 4 detector settings x (sync, async)
     lines = [e for e in ET.parse(written[-1]).getroot().iter() if e.tag.endswith("polyline")]
     assert len(lines) == 2
+
+
+def test_async_schedule_protocol_check():
+    """protocol-level check of the pub/done flag handshake — all waits point backwards in the global order and,
+    under random interleavings of the ranks, every mix reads exactly the version it was scheduled to read."""
+    import numpy as np
+    from fedb200.p2p import Topology
+    from fedb200.p2p.schedule import build_async_schedule, model_durations, verify_schedule
+    cases = [(Topology.reference10(), 10, 5, None, 20.0), (Topology.full(8), 8, 8, None, 0.05), (Topology.full(16), 16, 8, 3, 0.02),
+             (Topology.ring(6), 6, 3, None, 0.2)]
+    for topo, n, world, fanout, base in cases:
+        for seed in range(3):
+            sched = build_async_schedule(topo, 433e6, 4, model_durations(n, base_s=base, seed=seed), fanout=fanout)
+            out = verify_schedule(sched, n, world, trials=8, seed=seed)
+            assert out["events"] == 4 * n - 4 * len(sched.masked) and out["reads_checked"] > 0
+    # a broken schedule must be caught: drop the overwrite waits of a slot-reusing publish
+    sched = build_async_schedule(Topology.full(8), 433e6, 6, model_durations(8, seed=1))
+    victims = [ev for ev in sched.events if ev.overwrite_waits]
+    if victims:
+        import pytest
+        for ev in victims:
+            ev.overwrite_waits = []
+        with pytest.raises(AssertionError):
+            verify_schedule(sched, 8, 8, trials=64, seed=0)
