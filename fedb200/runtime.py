@@ -565,8 +565,16 @@ class FedRuntime:
             wall = time.perf_counter() - t0
             tot = self.comm.reduce_scalars([last.get("samples", 0), last.get("tokens", 0)], "sum")
             mx = self.comm.reduce_scalars([wall], "max")[0]
+            # bytes this rank moves over NVLink in the fused two-shot FedAvg (reduce-scatter reads + all-gather pushes) and
+            # the fraction of the link roofline (770 GB/s per direction, measured) the aggregate phase reached; the phase
+            # also contains the wait for the slowest rank, so the fraction is a lower bound
+            W = self.world
+            comm_bytes = int(2 * (W - 1) / W * self.nbytes) if W > 1 else 0
+            agg_ms = dev.get("aggregate", 0.0)
+            nvlink_frac = (comm_bytes / 2 / 770e9 * 1e3) / agg_ms if comm_bytes and agg_ms > 0 else None
             self.log.log("round", round=rnd, wall_s=mx, samples_per_s=tot[0] / mx if mx else None,
                          tokens_per_s=tot[1] / mx if mx else None, phases_ms=dev, model_size_gib=size,
+                         comm_bytes_per_rank=comm_bytes, aggregate_nvlink_frac=nvlink_frac,
                          masked=self.masked, ledger_height=self.ledger.height if self.ledger else 0,
                          **{k: v for k, v in last.items() if k not in ("samples", "tokens")})
         return self._finish(last)
