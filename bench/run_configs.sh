@@ -9,4 +9,4 @@ run c2_serverless_IID_sync $TR --master-port 29551 serverless_IID.py --model $M 
 run c3_serverless_NonIID_async_pagerank $TR --master-port 29552 serverless_NonIID.py --model $M --dataset medical_transcriptions --clients $N --rounds 3 --async \
     --topology reference10 --inject-anomalies 2 --inject-kind slowlink --anomaly-detector pagerank --ledger --async-epoch-s 20 --metrics $OUT/c3.jsonl --quiet
 run c4_server_NonIID_32clients_ledger $TR --master-port 29553 server_NonIID.py --model $M --clients $((4*N)) --rounds 2 --split dirichlet --ledger --metrics $OUT/c4.jsonl --quiet
-run c5_serverless_async_large_64peers $TR --master-port 29554 serverless_IID.py --model $ML --clients $((8*N)) --rounds 2 --async --topology full --ledger --metrics $OUT/c5.jsonl --quiet
+run c5_serverless_async_large_64peers $TR --master-port 29554 serverless_IID.py --model $ML --clients $((8*N)) --rounds 2 --async --topology full --ledger --async-min-latency-s 0.05 --metrics $OUT/c5.jsonl --quiet

@@ -109,6 +109,7 @@ class FedConfig:
     async_epoch_s: float = 0.05        # modelled local-epoch duration of the schedule's virtual clock
     async_spread: float = 0.5          # peer heterogeneity of the modelled durations
     async_fanout: Optional[int] = None # destinations per publish (None = every reachable peer)
+    async_min_latency_s: float = 0.0   # visibility lag of a publish in the schedule's virtual time (see AsyncGossipEngine)
     topology: str = "full"             # full | ring | reference10 | random
     route_optimizer: bool = True
     anomaly_detector: str = "none"     # none | pagerank | modz | dbscan | community | cosine_pagerank
@@ -153,6 +154,7 @@ def build_parser(defaults: Optional[FedConfig] = None, description: str = "") ->
     p.add_argument("--async-scheduled", action="store_true", default=d.async_scheduled)
     p.add_argument("--async-fanout", type=int, default=d.async_fanout)
     p.add_argument("--async-epoch-s", type=float, default=d.async_epoch_s)
+    p.add_argument("--async-min-latency-s", type=float, default=d.async_min_latency_s)
     p.add_argument("--topology", default=d.topology)
     p.add_argument("--no-route-optimizer", dest="route_optimizer", action="store_false", default=d.route_optimizer)
     p.add_argument("--anomaly-detector", default=d.anomaly_detector)
@@ -188,6 +190,7 @@ def config_from_args(args: argparse.Namespace, defaults: Optional[FedConfig] = N
     cfg.device, cfg.backend, cfg.comm = args.device, args.backend, args.comm
     cfg.serverless_semantics, cfg.asynchronous = args.semantics, args.asynchronous
     cfg.async_scheduled, cfg.async_fanout, cfg.async_epoch_s = args.async_scheduled, args.async_fanout, args.async_epoch_s
+    cfg.async_min_latency_s = args.async_min_latency_s
     cfg.topology, cfg.route_optimizer = args.topology, args.route_optimizer
     cfg.anomaly_detector, cfg.inject_anomalies, cfg.inject_kind = (
         args.anomaly_detector, args.inject_anomalies, args.inject_kind)

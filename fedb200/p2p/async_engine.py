@@ -66,8 +66,12 @@ class AsyncGossipEngine:
                  mix_fn: Callable[[int, List[int], List[float], float], None],
                  publish_fn: Optional[Callable[[int, int], None]] = None, decay: float = 0.5,
                  fanout: Optional[int] = None, masked: Sequence[int] = (), route_optimizer: bool = True,
-                 mix_rate: float = 0.5):
+                 mix_rate: float = 0.5, min_latency: float = 0.0):
         self.topo, self.nbytes, self.decay, self.mix_rate = topo, nbytes, decay, mix_rate
+        # visibility lag: a published version is never mixable earlier than this after its publish, whatever the link
+        # model says.  On one NVSwitch box the modelled link latencies are ~1 ms against ~100 ms epochs, so without a lag
+        # every mix depends on the publish just before it and the real execution serialises across GPUs.
+        self.min_latency = float(min_latency)
         self.train_fn, self.mix_fn, self.publish_fn = train_fn, mix_fn, publish_fn
         self.masked = set(int(m) for m in masked)
         n = topo.n
@@ -139,7 +143,7 @@ class AsyncGossipEngine:
                     if self.publish_fn is not None:
                         self.publish_fn(i, j)
                     seq += 1
-                    heapq.heappush(heap, _Event(ev.time + t, seq, "landed", j, src=i, epoch=int(ev.epoch)))
+                    heapq.heappush(heap, _Event(ev.time + max(t, self.min_latency), seq, "landed", j, src=i, epoch=int(ev.epoch)))
                 self.comm_time[i] += max(lat.values(), default=0.0)
                 self.sync_equiv_time[i] += sum(lat.values())
             done[i] += 1

@@ -62,10 +62,11 @@ def model_durations(n: int, base_s: float = 0.05, spread: float = 0.5, seed: int
 
 def build_async_schedule(topo: Topology, nbytes: float, epochs_per_peer: int, durations: Sequence[float],
                          decay: float = 0.5, mix_rate: float = 0.5, fanout: Optional[int] = None,
-                         masked: Sequence[int] = (), route_optimizer: bool = True, max_slots: int = 8) -> AsyncSchedule:
+                         masked: Sequence[int] = (), route_optimizer: bool = True, max_slots: int = 8,
+                         min_latency: float = 0.0) -> AsyncSchedule:
     dur = np.asarray(durations, dtype=np.float64)
     eng = AsyncGossipEngine(topo, nbytes, lambda k: float(dur[k]), lambda *a: None, None, decay, fanout, masked,
-                            route_optimizer, mix_rate)
+                            route_optimizer, mix_rate, min_latency)
     res = eng.run(epochs_per_peer)
     events = []
     for i, r in enumerate(eng.log):

@@ -366,7 +366,8 @@ class FedRuntime:
         masked = list(self.static_masked)
         dur = model_durations(N, cfg.async_epoch_s, cfg.async_spread, cfg.seed)
         sched = build_async_schedule(self.topo, self.nbytes, cfg.num_rounds, dur, cfg.staleness_decay, masked=masked,
-                                     route_optimizer=cfg.route_optimizer, fanout=cfg.async_fanout)
+                                     route_optimizer=cfg.route_optimizer, fanout=cfg.async_fanout,
+                                     min_latency=cfg.async_min_latency_s)
         R, P = sched.slots_per_peer, self.P
         outbox = comm.alloc("async_outbox", P * R * D).view(P, R, D)
         state = comm.alloc("async_state", P * D).view(P, D)
@@ -470,6 +471,7 @@ class FedRuntime:
                "info_passing": info_passing_time(self.topo, self.nbytes, 0, removed=masked)}
         self.async_schedule = sched
         self.async_state = state
+        res["phases_ms"] = self.timer.device_ms()        # this rank's device time per phase (aggregate includes flag waits)
         self.log.log("async_done", **res)
         return res
 
@@ -533,7 +535,7 @@ class FedRuntime:
 
         masked = list(self.static_masked)
         eng = AsyncGossipEngine(self.topo, self.nbytes, train_fn, mix_fn, publish_fn, cfg.staleness_decay,
-                                masked=masked, route_optimizer=cfg.route_optimizer)
+                                masked=masked, route_optimizer=cfg.route_optimizer, min_latency=cfg.async_min_latency_s)
         res = eng.run(cfg.num_rounds)
         keep = [k for k in range(self.N) if k not in masked]
         self.global_flat.zero_()

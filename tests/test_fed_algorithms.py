@@ -253,3 +253,28 @@ def test_async_schedule_protocol_check():
             ev.overwrite_waits = []
         with pytest.raises(AssertionError):
             verify_schedule(sched, 8, 8, trials=64, seed=0)
+
+
+def test_async_visibility_lag_breaks_the_dependency_chain():
+    """With ~1 ms modelled links and ~50 ms epochs every mix depends on the publish just before it (the execution
+    serialises across GPUs); a visibility lag of one epoch moves every dependency at least a GPU-round back while the
+    schedule stays valid under the protocol checker."""
+    from fedb200.p2p import Topology
+    from fedb200.p2p.schedule import build_async_schedule, model_durations, verify_schedule
+    n, world = 32, 8
+    dur = model_durations(n, base_s=0.05, seed=0)
+    topo = Topology.full(n)
+
+    def min_gap(s):
+        idx = {(e.peer, e.epoch): e.index for e in s.events}
+        gaps = [e.index - idx[(p, ep)] for e in s.events for p, ep in zip(e.sources, e.source_epochs)]
+        return min(gaps), len(gaps)
+
+    tight = build_async_schedule(topo, 1.34e9, 3, dur)
+    lagged = build_async_schedule(topo, 1.34e9, 3, dur, min_latency=float(dur.min()))
+    g0, n0 = min_gap(tight)
+    g1, n1 = min_gap(lagged)
+    assert g0 == 1 and n0 > 0                       # chain: some mix reads the version published by the previous event
+    assert g1 >= world and n1 > 0                   # lag: nothing more recent than a full sweep of the ranks
+    verify_schedule(lagged, n, world, trials=4)
+    assert lagged.slots_per_peer <= 4
