@@ -1,0 +1,154 @@
+"""Same-box restatements of the reference algorithm with stock PyTorch / HF modules (``bench.py --impl torch_baseline``).
+
+One FL round per peer, as in src/Serverlesscase/serverless_IID_IMDB.py:255-285: a local epoch over 100 samples
+(batch 32, AdamW lr 5e-5, eps 1e-6, wd 0, fresh optimizer), local evaluation on 100 samples, weight averaging, global
+evaluation on 100 fresh samples.  None of this repository's kernels run on this path; one process per GPU, one peer
+per process.  Arms (``--arm``):
+
+=====================  ==========  ==========================  ==================================================
+arm                    precision   attention                   aggregation
+=====================  ==========  ==========================  ==================================================
+``fp32_numpy``         fp32        HF eager                    D2H -> host numpy mean -> load_state_dict (:263-270)
+``fp32_nccl``          fp32        HF eager                    ``dist.all_reduce`` per parameter (NCCL), in place
+``bf16_sdpa_nccl``     bf16 amp    torch SDPA (library flash)  one flattened ``dist.all_reduce`` + scale
+``bf16_sdpa_bucketed`` bf16 amp    torch SDPA                  as above; batches sorted by length (less padding)
+=====================  ==========  ==========================  ==================================================
+
+The last two are the equal-precision comparison for the fused bf16 trainer: same dtype on the tensor cores, library
+attention, library all-reduce, fp32 master weights and optimizer state (autocast).  Timing: wall clock around K rounds
+after W warm-up rounds, bracketed by a barrier + ``torch.cuda.synchronize()``, max over ranks.
+"""
+from __future__ import annotations
+
+import json
+import os
+import time
+from collections import OrderedDict
+
+ARMS = ("fp32_numpy", "fp32_nccl", "bf16_sdpa_nccl", "bf16_sdpa_bucketed")
+
+
+def run(args, make_cfg, ClockSampler, published: float) -> None:
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from torch._utils import _flatten_dense_tensors, _unflatten_dense_tensors
+    from transformers import BertConfig, BertForSequenceClassification
+    from fedb200.data.build import build_corpus, client_loaders, global_test_loader
+    from fedb200.data.dataset import BatchLoader
+    from fedb200.parallel import init_distributed
+
+    arm = args.arm
+    if arm is None:                              # round-1 flags kept working
+        arm = "fp32_nccl" if args.agg == "nccl" else "fp32_numpy"
+        if args.amp:
+            arm = "bf16_sdpa_nccl"
+    amp = arm.startswith("bf16")
+    n = int(os.environ.get("WORLD_SIZE", "1"))
+    rank, world, local = init_distributed(torch.device("cuda"))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    cfg = make_cfg(args, n)
+    corpus = build_corpus(cfg.data, cfg.model, cfg.num_clients, cfg.seed)
+    torch.manual_seed(0)
+    hc = BertConfig(vocab_size=cfg.model.vocab_size, num_labels=2, hidden_size=cfg.model.hidden_size,
+                    num_hidden_layers=cfg.model.num_layers, num_attention_heads=cfg.model.num_heads,
+                    intermediate_size=cfg.model.intermediate_size, max_position_embeddings=cfg.model.max_position,
+                    attn_implementation="sdpa" if amp else "eager")
+    model = BertForSequenceClassification(hc).to(dev)
+    K, W = args.steps, args.warmup
+    accs = []
+
+    def bucketed(loader):
+        """Same samples, batches formed after sorting by length (the usual padding-reduction trick); batch order shuffled."""
+        if arm != "bf16_sdpa_bucketed":
+            return loader
+        ds = loader.dataset
+        order = np.argsort(ds.lengths(), kind="stable")
+        return BatchLoader(ds.select(order), loader.batch_size, shuffle=False, pin=False)
+
+    def evaluate(loader):
+        model.eval()
+        correct = total = 0
+        with torch.no_grad():
+            for batch in bucketed(loader):
+                batch = {k: v.to(dev, non_blocking=True) for k, v in batch.items()}
+                with torch.autocast("cuda", dtype=torch.bfloat16, enabled=amp):
+                    out = model(**batch)
+                correct += int((out.logits.argmax(-1) == batch["labels"]).sum().item())
+                total += int(batch["labels"].numel())
+        return correct / max(total, 1)
+
+    def one_round(rnd):
+        tr, te = client_loaders(corpus, cfg.data, rank, rnd)
+        opt = torch.optim.AdamW(model.parameters(), lr=5e-5, eps=1e-6, weight_decay=0.0)
+        model.train()
+        for batch in bucketed(tr):
+            batch = {k: v.to(dev, non_blocking=True) for k, v in batch.items()}
+            with torch.autocast("cuda", dtype=torch.bfloat16, enabled=amp):
+                loss = model(**batch).loss
+            loss.backward()
+            opt.step()
+            opt.zero_grad()
+        evaluate(te)
+        if arm == "fp32_numpy":
+            params = [v.cpu().numpy() for v in model.state_dict().values()]
+            allp = [params]
+            if n > 1:
+                allp = [None] * n
+                dist.all_gather_object(allp, params)
+            avg = [sum(p) / len(p) for p in zip(*allp)]
+            model.load_state_dict(OrderedDict((k, torch.tensor(v)) for k, v in zip(model.state_dict().keys(), avg)))
+        elif arm == "fp32_nccl":
+            for p in model.parameters():
+                if n > 1:
+                    dist.all_reduce(p.data)
+                p.data.div_(n)
+        else:
+            ps = [p.data for p in model.parameters()]
+            flat = _flatten_dense_tensors(ps)
+            if n > 1:
+                dist.all_reduce(flat)
+            flat.div_(n)
+            for p, q in zip(ps, _unflatten_dense_tensors(flat, ps)):
+                p.copy_(q)
+        accs.append(evaluate(global_test_loader(corpus, cfg.data, rnd)))
+        return tr.num_samples
+
+    def barrier():
+        if n > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    for r in range(W):
+        one_round(r)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    t0 = time.perf_counter()
+    samples = 0
+    for r in range(W, W + K):
+        samples += one_round(r)
+    barrier()
+    sec = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([sec], dtype=torch.float64, device=dev)
+    c = torch.tensor([samples], dtype=torch.float64, device=dev)
+    if n > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(c, op=dist.ReduceOp.SUM)
+    if rank == 0:
+        v = c.item() / t.item()
+        print(json.dumps({"metric": "train_samples_per_s (FL round = local epoch + local eval + aggregate + global eval)",
+                          "value": round(v, 2), "unit": "samples/s", "n_gpus": n, "steps": K, "warmup": W,
+                          "ms_per_step": round(t.item() / K * 1e3, 3), "higher_is_better": True, "scaling": "weak",
+                          "vs_baseline": round(v / published, 2), "dtype": "bf16-autocast" if amp else "fp32",
+                          "data": "synthetic", "impl": "torch_baseline", "arm": arm, "clocks": clocks,
+                          "config": {"model": f"transformers BertForSequenceClassification ({args.model} shape)",
+                                     "attention": hc._attn_implementation, "peers": n, "seq_len": args.seq_len,
+                                     "batch_per_peer": args.batch_size,
+                                     "global_accuracy_per_round": [round(a, 4) for a in accs],
+                                     "note": "restatement of the reference algorithm with stock PyTorch/HF; wall clock"},
+                          "gpu_launches": 0}))
+    if n > 1 and dist.is_initialized():
+        dist.destroy_process_group()

@@ -164,6 +164,27 @@ def run_fedb200(args):
     for r in range(W):
         kernel_round(rt, *rounds[r])
     barrier()
+    # ---------------- self-check (outside the timed region): the fused aggregate against a library all-reduce ----
+    # every rank's slot holds its own trained weights after the warm-up rounds; the fused peer-memory mean of those
+    # slots must equal dist.all_reduce(slot) / N computed by NCCL on a copy
+    if rt.P == 1 and rt.N == rt.world:
+        src = rt.slots[0]
+    else:
+        rt._local_weighted_sum([1.0] * len(rt.local_ids))
+        src = rt.acc
+    want = src.clone()
+    if n > 1:
+        dist.all_reduce(want)
+    want.div_(rt.N)
+    rt.comm.weighted_mean(src, float(len(rt.local_ids)), rt.global_flat)
+    sc = (rt.global_flat - want).abs().max().reshape(1).to(torch.float64)
+    if n > 1:
+        dist.all_reduce(sc, op=dist.ReduceOp.MAX)
+    rt.comm.check_errors()
+    selfcheck = {"max_abs": float(sc.item()), "against": "torch.distributed all_reduce (NCCL) / N on a copy of the same slots"
+                 if n > 1 else "the single local slot (N = 1: the mean of one model is that model)", "elements": int(rt.D)}
+    del want
+    barrier()
     sampler = ClockSampler(rt.local_rank)
     if rank == 0:
         sampler.start()
@@ -221,11 +242,15 @@ def run_fedb200(args):
                        "ledger": cfg.ledger, "dropout": cfg.model.hidden_dropout, "comm": rt.comm.name,
                        "train_tokens_per_s": round(tokens / (dev_ms / 1e3), 1),
                        "l2": "working set (433 MB weights + GBs of activations per step) far exceeds the 126 MB L2",
+                       "checkpoint": "per-round save_pretrained (reference :280) is NOT in the timed region of either arm; "
+                                     "FedRuntime writes it asynchronously when --checkpoint-dir is set",
                        "baseline_note": "vs_baseline divides by the reference's only recorded GPU run (Colab A100, 2000 train samples in 184.4 s whole-script)"},
             "clocks": clocks,
             "e2e": {"value": round(e2e_value, 2), "unit": "samples/s", "ms_per_step": round(e2e_s / K * 1e3, 3),
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "api": "fedb200.runtime.FedRuntime.round_serverless", "global_accuracy_last": rt.global_accuracies[-1] if rt.global_accuracies else None},
+            "accuracy_curve": [round(float(a), 4) for a in rt.global_accuracies],
+            "selfcheck": selfcheck,
             "gpu_launches": int(launches),
         }
         print(json.dumps(line))
@@ -235,107 +260,17 @@ def run_fedb200(args):
 
 
 def run_reference(args):
-    print(json.dumps({"impl": "reference", "unavailable":
-                      "reference is 11 flat scripts with no setup.py/pyproject (pip: 'not installable'); needs flwr, ray, "
-                      "evaluate (absent), transformers.AdamW (removed in 5.5) and HF-hub downloads (no network)"}))
+    """Unmodified reference script under baseline/_ref, executed with offline stand-ins (baseline/reference_arm.py)."""
+    sys.path.insert(0, os.path.join(ROOT, "baseline"))
+    import reference_arm
+    reference_arm.main(args)
 
 
 def run_torch_baseline(args):
-    """Same-box restatement of the reference algorithm with stock modules: HF
-    BertForSequenceClassification fp32, padded batches, torch AdamW(5e-5, eps 1e-6, wd 0), weights copied to
-    host numpy and averaged there (src/Serverlesscase/serverless_IID_IMDB.py:263-270) or, with --agg nccl, a
-    torch.distributed all_reduce.  None of this repo's kernels run on this path."""
-    import torch
-    import torch.distributed as dist
-    from collections import OrderedDict
-    from transformers import BertConfig, BertForSequenceClassification
-    from fedb200.data.build import build_corpus, client_loaders, global_test_loader
-    from fedb200.parallel import init_distributed
-    n = int(os.environ.get("WORLD_SIZE", "1"))
-    rank, world, local = init_distributed(torch.device("cuda"))
-    dev = torch.device("cuda", local)
-    torch.cuda.set_device(dev)
-    cfg = make_cfg(args, n)
-    corpus = build_corpus(cfg.data, cfg.model, cfg.num_clients, cfg.seed)
-    torch.manual_seed(0)
-    hc = BertConfig(vocab_size=cfg.model.vocab_size, num_labels=2)
-    model = BertForSequenceClassification(hc).to(dev)
-    K, W = args.steps, args.warmup
-
-    def evaluate(loader):
-        model.eval()
-        correct = 0
-        with torch.no_grad():
-            for batch in loader:
-                batch = {k: v.to(dev) for k, v in batch.items()}
-                with torch.autocast("cuda", dtype=torch.bfloat16, enabled=args.amp):
-                    out = model(**batch)
-                correct += int((out.logits.argmax(-1) == batch["labels"]).sum().item())
-        return correct
-
-    def one_round(rnd):
-        tr, te = client_loaders(corpus, cfg.data, rank, rnd)
-        opt = torch.optim.AdamW(model.parameters(), lr=5e-5, eps=1e-6, weight_decay=0.0)
-        model.train()
-        for batch in tr:
-            batch = {k: v.to(dev) for k, v in batch.items()}
-            with torch.autocast("cuda", dtype=torch.bfloat16, enabled=args.amp):
-                loss = model(**batch).loss
-            loss.backward()
-            opt.step()
-            opt.zero_grad()
-        evaluate(te)
-        if args.agg == "numpy":
-            params = [v.cpu().numpy() for v in model.state_dict().values()]
-            allp = [params]
-            if n > 1:
-                allp = [None] * n
-                dist.all_gather_object(allp, params)
-            avg = [sum(p) / len(p) for p in zip(*allp)]
-            model.load_state_dict(OrderedDict((k, torch.tensor(v)) for k, v in zip(model.state_dict().keys(), avg)))
-        else:
-            for p in model.parameters():
-                if n > 1:
-                    dist.all_reduce(p.data)
-                p.data.div_(n)
-        evaluate(global_test_loader(corpus, cfg.data, rnd))
-        return tr.num_samples
-
-    def barrier():
-        if n > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-    for r in range(W):
-        one_round(r)
-    barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    t0 = time.perf_counter()
-    samples = 0
-    for r in range(W, W + K):
-        samples += one_round(r)
-    barrier()
-    sec = time.perf_counter() - t0
-    clocks = sampler.stop() if rank == 0 else None
-    t = torch.tensor([sec], dtype=torch.float64, device=dev)
-    c = torch.tensor([samples], dtype=torch.float64, device=dev)
-    if n > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(c, op=dist.ReduceOp.SUM)
-    if rank == 0:
-        v = c.item() / t.item()
-        print(json.dumps({"metric": "train_samples_per_s (FL round = local epoch + local eval + aggregate + global eval)",
-                          "value": round(v, 2), "unit": "samples/s", "n_gpus": n, "steps": K, "warmup": W,
-                          "ms_per_step": round(t.item() / K * 1e3, 3), "higher_is_better": True, "scaling": "weak",
-                          "vs_baseline": round(v / PUBLISHED_TRAIN_SAMPLES_PER_S, 2), "dtype": "bf16-autocast" if args.amp else "fp32", "data": "synthetic",
-                          "impl": "torch_baseline", "clocks": clocks,
-                          "config": {"model": "transformers BertForSequenceClassification (BioBERT shape)", "agg": args.agg,
-                                     "peers": n, "seq_len": args.seq_len, "batch_per_peer": args.batch_size,
-                                     "note": "restatement of the reference algorithm with stock PyTorch/HF; wall clock"},
-                          "gpu_launches": 0}))
-    if n > 1 and dist.is_initialized():
-        dist.destroy_process_group()
+    """Stock PyTorch / HF restatements of the reference algorithm, four arms (baseline/torch_ref.py)."""
+    sys.path.insert(0, os.path.join(ROOT, "baseline"))
+    import torch_ref
+    torch_ref.run(args, make_cfg, ClockSampler, PUBLISHED_TRAIN_SAMPLES_PER_S)
 
 
 def main():
@@ -354,13 +289,14 @@ def main():
     ap.add_argument("--agg", default="numpy", choices=["numpy", "nccl"])
     ap.add_argument("--no-ledger", action="store_true")
     ap.add_argument("--amp", action="store_true", help="torch_baseline only: bf16 autocast instead of the reference's fp32")
+    ap.add_argument("--arm", default=None, choices=["fp32_numpy", "fp32_nccl", "bf16_sdpa_nccl", "bf16_sdpa_bucketed"],
+                    help="torch_baseline only: which restatement (baseline/torch_ref.py)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.impl == "reference":
-        if int(os.environ.get("RANK", "0")) == 0:
-            run_reference(args)
+        run_reference(args)            # rank 0 runs the single-process reference; other ranks return at once
         return
     if args.gpus > 1 and world == 1:
         # convenience: re-launch ourselves under torchrun (the driver launches torchrun itself)
