@@ -109,6 +109,7 @@ class FedConfig:
     async_epoch_s: float = 0.05        # modelled local-epoch duration of the schedule's virtual clock
     async_spread: float = 0.5          # peer heterogeneity of the modelled durations
     async_fanout: Optional[int] = None # destinations per publish (None = every reachable peer)
+    async_time: str = "measured"       # single-process engine clock: measured epoch durations | modelled (async_epoch_s, async_spread)
     async_min_latency_s: float = 0.0   # visibility lag of a publish in the schedule's virtual time (see AsyncGossipEngine)
     topology: str = "full"             # full | ring | reference10 | random
     route_optimizer: bool = True
@@ -117,7 +118,15 @@ class FedConfig:
     inject_kind: str = "scale"         # scale | signflip | noise
     ledger: bool = False
     ledger_chunk_bytes: int = 1 << 20
+    # fine-tune from a local HF checkpoint directory (config.json + model.safetensors / pytorch_model.bin [+ vocab.txt]):
+    # AutoModelForSequenceClassification.from_pretrained(CHECKPOINT, num_labels=...), server_IID_IMDB.py:142-144
+    init_checkpoint: Optional[str] = None
+    ignore_mismatched_sizes: bool = False   # server_noniid_medical_transcriptions.py:146-148
+    vocab_path: Optional[str] = None   # vocab.txt (or its directory) for the WordPiece tokenizer; default: init_checkpoint
+    deterministic: bool = False        # bit-reproducible training (ordered split-K wgrad reduction): ledger roots re-derivable
+    placement: str = "balanced"        # balanced (token-count LPT) | block (contiguous id blocks)
     checkpoint_dir: Optional[str] = None
+    checkpoint_async: bool = True      # background writer: the round loop only pays a device->pinned-host copy
     checkpoint_every: int = 1          # serverless_IID_IMDB.py:280 saves every round
     resume: bool = False
     metrics_path: Optional[str] = None
@@ -155,12 +164,20 @@ def build_parser(defaults: Optional[FedConfig] = None, description: str = "") ->
     p.add_argument("--async-fanout", type=int, default=d.async_fanout)
     p.add_argument("--async-epoch-s", type=float, default=d.async_epoch_s)
     p.add_argument("--async-min-latency-s", type=float, default=d.async_min_latency_s)
+    p.add_argument("--async-time", default=d.async_time, choices=["measured", "modelled"])
     p.add_argument("--topology", default=d.topology)
     p.add_argument("--no-route-optimizer", dest="route_optimizer", action="store_false", default=d.route_optimizer)
     p.add_argument("--anomaly-detector", default=d.anomaly_detector)
     p.add_argument("--inject-anomalies", type=int, default=d.inject_anomalies)
     p.add_argument("--inject-kind", default=d.inject_kind)
     p.add_argument("--ledger", action="store_true", default=d.ledger)
+    p.add_argument("--init-checkpoint", default=d.init_checkpoint,
+                   help="local HF checkpoint directory to fine-tune from (from_pretrained equivalent)")
+    p.add_argument("--ignore-mismatched-sizes", action="store_true", default=d.ignore_mismatched_sizes)
+    p.add_argument("--vocab", dest="vocab_path", default=d.vocab_path, help="vocab.txt for the WordPiece tokenizer")
+    p.add_argument("--deterministic", action="store_true", default=d.deterministic)
+    p.add_argument("--placement", default=d.placement, choices=["balanced", "block"])
+    p.add_argument("--checkpoint-sync", dest="checkpoint_async", action="store_false", default=d.checkpoint_async)
     p.add_argument("--checkpoint-dir", default=d.checkpoint_dir)
     p.add_argument("--checkpoint-every", type=int, default=d.checkpoint_every)
     p.add_argument("--resume", action="store_true", default=d.resume)
@@ -180,6 +197,16 @@ def config_from_args(args: argparse.Namespace, defaults: Optional[FedConfig] = N
     if args.no_dropout:
         mo.update(hidden_dropout=0.0, attention_dropout=0.0)
     cfg.model = ModelConfig.preset(args.model, **mo)
+    cfg.init_checkpoint, cfg.ignore_mismatched_sizes = args.init_checkpoint, args.ignore_mismatched_sizes
+    cfg.vocab_path = args.vocab_path or args.init_checkpoint
+    cfg.deterministic, cfg.placement, cfg.checkpoint_async = args.deterministic, args.placement, args.checkpoint_async
+    if args.init_checkpoint:
+        # the architecture comes from the checkpoint's config.json, the label count from the task (num_labels=...)
+        import dataclasses as _dc
+        from .models.hf_io import load_config
+        loaded = load_config(args.init_checkpoint)
+        drop = dict(hidden_dropout=0.0, attention_dropout=0.0) if args.no_dropout else {}
+        cfg.model = _dc.replace(loaded, num_labels=nl, name=args.model, **drop)
     dd = dataclasses.asdict(cfg.data)
     dd.update(dataset=args.dataset, source=args.source, data_dir=args.data_dir, split=args.split,
               dirichlet_alpha=args.dirichlet_alpha, train_per_client=args.train_per_client,
@@ -190,7 +217,7 @@ def config_from_args(args: argparse.Namespace, defaults: Optional[FedConfig] = N
     cfg.device, cfg.backend, cfg.comm = args.device, args.backend, args.comm
     cfg.serverless_semantics, cfg.asynchronous = args.semantics, args.asynchronous
     cfg.async_scheduled, cfg.async_fanout, cfg.async_epoch_s = args.async_scheduled, args.async_fanout, args.async_epoch_s
-    cfg.async_min_latency_s = args.async_min_latency_s
+    cfg.async_min_latency_s, cfg.async_time = args.async_min_latency_s, args.async_time
     cfg.topology, cfg.route_optimizer = args.topology, args.route_optimizer
     cfg.anomaly_detector, cfg.inject_anomalies, cfg.inject_kind = (
         args.anomaly_detector, args.inject_anomalies, args.inject_kind)

@@ -27,12 +27,15 @@ class Corpus:
     partitioner: Partitioner
 
 
-def build_corpus(data: DataConfig, model: ModelConfig, num_clients: int, seed: int = 0) -> Corpus:
+def build_corpus(data: DataConfig, model: ModelConfig, num_clients: int, seed: int = 0,
+                 vocab_path: str | None = None) -> Corpus:
     if data.source == "csv":
         if not data.data_dir or data.dataset not in CSV_SPECS:
             raise ValueError("csv source needs --data-dir and one of " + ", ".join(CSV_SPECS))
-        raw_train = load_csv_dataset(data.dataset, data.data_dir, "train", model.vocab_size, data.max_seq_len)
-        raw_test = load_csv_dataset(data.dataset, data.data_dir, "test", model.vocab_size, data.max_seq_len)
+        raw_train = load_csv_dataset(data.dataset, data.data_dir, "train", model.vocab_size, data.max_seq_len,
+                                     vocab_path=vocab_path)
+        raw_test = load_csv_dataset(data.dataset, data.data_dir, "test", model.vocab_size, data.max_seq_len,
+                                    vocab_path=vocab_path)
         perm = np.random.default_rng(data.seed).permutation(len(raw_train))
         train, unshuf = raw_train.select(perm), raw_train
         test = raw_test

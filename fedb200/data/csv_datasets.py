@@ -13,7 +13,7 @@ import os
 from typing import Optional
 
 from .dataset import TokenDataset
-from .tokenizer import HashTokenizer
+from .tokenizer import load_tokenizer
 
 CSV_SPECS = {
     "medical_transcriptions": dict(train="train_file_mt.csv", test="test_file_mt.csv",
@@ -31,10 +31,14 @@ CSV_SPECS = {
 
 
 def load_csv_dataset(name: str, data_dir: str, split: str = "train", vocab_size: int = 28996,
-                     max_seq_len: int = 512, rows: Optional[int] = None) -> TokenDataset:
+                     max_seq_len: int = 512, rows: Optional[int] = None, vocab_path: Optional[str] = None) -> TokenDataset:
+    """``vocab_path``: checkpoint directory / ``vocab.txt`` -> real WordPiece ids (``AutoTokenizer.from_pretrained``,
+    src/Servercase/server_IID_IMDB.py:72-76); without one the hash tokenizer stands in."""
     spec = CSV_SPECS[name]
     path = os.path.join(data_dir, spec[split if split in ("train", "test") else "train"])
-    tok = HashTokenizer(vocab_size=vocab_size, max_length=max_seq_len)
+    tok = load_tokenizer(vocab_path, vocab_size, max_seq_len)
+    if getattr(tok, "vocab_size", vocab_size) > vocab_size:
+        raise ValueError(f"tokenizer vocabulary ({tok.vocab_size}) exceeds the model's embedding table ({vocab_size})")
     seqs, labels, label_map = [], [], {}
     with open(path, newline="", encoding="utf-8", errors="replace") as fh:
         for i, row in enumerate(csv.DictReader(fh)):

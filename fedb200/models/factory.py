@@ -27,5 +27,5 @@ def build_model(config: ModelConfig, device="cpu", seed: Optional[int] = None,
     model = cls(config)
     if checkpoint:
         from .hf_io import load_pretrained
-        load_pretrained(model, checkpoint, ignore_mismatched_sizes=ignore_mismatched_sizes)
+        model.load_report = load_pretrained(model, checkpoint, ignore_mismatched_sizes=ignore_mismatched_sizes)["load_report"]
     return model.to(device)

@@ -106,7 +106,8 @@ class FusedRunner:
         self.max_tokens = max_tokens or fed.data.batch_size * min(fed.data.max_seq_len, c.max_position)
 
         # ---- arenas: HF keys, compute-friendly memory order (q|k|v weights contiguous) -----------------
-        ref = build_model(c, "cpu", seed)
+        ref = build_model(c, "cpu", seed, checkpoint=fed.init_checkpoint, ignore_mismatched_sizes=fed.ignore_mismatched_sizes)
+        self.load_report = getattr(ref, "load_report", None)
         sd = ref.state_dict()
         hf_order = list(sd.keys())
         self.roles = R = _roles(c)
@@ -261,6 +262,11 @@ class FusedRunner:
         if missing:
             raise KeyError(f"state_dict key mismatch (strict): {sorted(missing)[:4]} …")
         self.arena.load(state)
+        self._shadow_fresh = False                  # the master changed behind the latch: the next sync_shadow() must cast
+
+    def mark_dirty(self) -> None:
+        """Call after editing ``flat`` in place (e.g. fault injection): the bf16 shadow no longer matches the master."""
+        self._shadow_fresh = False
 
     def sync_shadow(self) -> None:
         """Refresh the bf16 tensor-core copy after the fp32 master was overwritten (load / aggregation)."""

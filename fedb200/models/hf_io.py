@@ -50,13 +50,14 @@ def config_from_hf(d: dict, name: str = "loaded") -> ModelConfig:
 
 def _save_tensors(state: Dict[str, torch.Tensor], path: str) -> str:
     cpu = OrderedDict((k, v.detach().to("cpu", torch.float32).contiguous().clone()) for k, v in state.items())
-    try:
+    try:                                     # written under a temporary name and renamed: a reader never sees half a file
         from safetensors.torch import save_file
         fn = os.path.join(path, "model.safetensors")
-        save_file(cpu, fn, metadata={"format": "pt"})
+        save_file(cpu, fn + ".tmp", metadata={"format": "pt"})
     except ImportError:                      # pragma: no cover - safetensors ships with transformers
         fn = os.path.join(path, "pytorch_model.bin")
-        torch.save(cpu, fn)
+        torch.save(cpu, fn + ".tmp")
+    os.replace(fn + ".tmp", fn)
     return fn
 
 
@@ -81,20 +82,53 @@ def load_state(path: str) -> "OrderedDict[str, torch.Tensor]":
     return OrderedDict(torch.load(os.path.join(path, "pytorch_model.bin"), map_location="cpu"))
 
 
-def load_pretrained(model: torch.nn.Module, path: str, ignore_mismatched_sizes: bool = False) -> dict:
-    """Load an HF-layout checkpoint into ``model``; returns ``fed_state`` (``{}`` if absent)."""
-    state = load_state(path)
+def _canonical_keys(state: "OrderedDict[str, torch.Tensor]", own_keys, arch: str) -> "OrderedDict[str, torch.Tensor]":
+    """Key fix-ups ``transformers`` applies on load: old TF-style LayerNorm names (``gamma`` / ``beta``, e.g. the original
+    BioBERT conversion) and checkpoints of the bare encoder (``embeddings.…`` without the ``bert.`` / ``albert.`` prefix)."""
+    out = OrderedDict()
+    prefix = arch + "."
+    for k, v in state.items():
+        if k.endswith("LayerNorm.gamma"):
+            k = k[: -len("gamma")] + "weight"
+        elif k.endswith("LayerNorm.beta"):
+            k = k[: -len("beta")] + "bias"
+        if k not in own_keys and (prefix + k) in own_keys:
+            k = prefix + k
+        out[k] = v
+    return out
+
+
+def load_pretrained(model: torch.nn.Module, path: str, ignore_mismatched_sizes: bool = False,
+                    strict: bool = False) -> dict:
+    """Load an HF-layout checkpoint directory into ``model`` with ``from_pretrained`` semantics
+    (src/Servercase/server_IID_IMDB.py:142-144): checkpoint keys the model does not have (e.g. the ``cls.predictions.*``
+    pre-training head of BioBERT) are ignored, model keys the checkpoint lacks (the fresh ``classifier``) keep their
+    initialisation, a shape mismatch is an error unless ``ignore_mismatched_sizes`` (then that tensor also keeps its
+    initialisation — src/Servercase/server_noniid_medical_transcriptions.py:146-148).  ``strict=True`` demands an exact key
+    match (our own checkpoints, ``--resume``).  Returns ``fed_state`` (``{}`` if absent) with a ``"load_report"`` entry."""
     own = model.state_dict()
-    if ignore_mismatched_sizes:
-        state = OrderedDict((k, v) for k, v in state.items() if k in own and own[k].shape == v.shape)
-        own.update(state)
-        state = own
-    model.load_state_dict(state, strict=True)
+    arch = "albert" if any(k.startswith("albert.") for k in own) else "bert"
+    state = _canonical_keys(load_state(path), own, arch)
+    unexpected = [k for k in state if k not in own]
+    missing = [k for k in own if k not in state]
+    mismatched = [k for k in state if k in own and tuple(own[k].shape) != tuple(state[k].shape)]
+    if strict and (unexpected or missing):
+        raise KeyError(f"checkpoint key mismatch (strict): missing {missing[:3]}, unexpected {unexpected[:3]}")
+    if mismatched and not ignore_mismatched_sizes:
+        k = mismatched[0]
+        raise RuntimeError(f"size mismatch for {k}: checkpoint {tuple(state[k].shape)} vs model {tuple(own[k].shape)} "
+                           "(pass ignore_mismatched_sizes=True / --ignore-mismatched-sizes to re-initialise it)")
+    for k, v in state.items():
+        if k in own and k not in mismatched:
+            own[k] = v
+    model.load_state_dict(own, strict=True)
+    out = {}
     fs = os.path.join(path, "fed_state.json")
     if os.path.exists(fs):
         with open(fs) as fh:
-            return json.load(fh)
-    return {}
+            out = json.load(fh)
+    out["load_report"] = {"missing": missing, "unexpected": unexpected, "mismatched": mismatched}
+    return out
 
 
 def load_config(path: str) -> ModelConfig:

@@ -42,10 +42,24 @@ def adamw_flat(p, g, m, v, shadow, step, lr, b1, b2, eps, wd, grad_scale=1.0, ze
     count()
 
 
+MAX_MIX_SOURCES = 64          # FEDB200_MAX_MIX_SOURCES in include/fedb200.h
+
+
 def mix_n(srcs: Sequence, weights: Sequence[float], out: torch.Tensor, shadow: Optional[torch.Tensor] = None,
           numel: Optional[int] = None) -> None:
-    """``out = sum_j weights[j] * srcs[j]``; a source may be a tensor or a raw (peer-mapped) device pointer."""
+    """``out = sum_j weights[j] * srcs[j]``; a source may be a tensor or a raw (peer-mapped) device pointer.  More than
+    ``FEDB200_MAX_MIX_SOURCES`` (64) sources are combined in passes: ``out`` re-enters the next pass as a source with weight 1
+    (each thread reads and then writes its own elements, so the in-place accumulation is safe)."""
     n = len(srcs)
+    if n > MAX_MIX_SOURCES:
+        srcs, weights = list(srcs), list(weights)
+        mix_n(srcs[:MAX_MIX_SOURCES], weights[:MAX_MIX_SOURCES], out, None, numel)
+        o = MAX_MIX_SOURCES
+        while o < n:
+            e = min(n, o + MAX_MIX_SOURCES - 1)
+            mix_n([out] + srcs[o:e], [1.0] + weights[o:e], out, shadow if e == n else None, numel)
+            o = e
+        return
     ptrs = (C.c_void_p * n)(*[(s.data_ptr() if isinstance(s, torch.Tensor) else int(s)) for s in srcs])
     ws = (C.c_float * n)(*[float(w) for w in weights])
     _chk(out, torch.float32, "out")

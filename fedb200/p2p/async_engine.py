@@ -66,13 +66,19 @@ class AsyncGossipEngine:
                  mix_fn: Callable[[int, List[int], List[float], float], None],
                  publish_fn: Optional[Callable[[int, int], None]] = None, decay: float = 0.5,
                  fanout: Optional[int] = None, masked: Sequence[int] = (), route_optimizer: bool = True,
-                 mix_rate: float = 0.5, min_latency: float = 0.0):
+                 mix_rate: float = 0.5, min_latency: float = 0.0,
+                 land_fn: Optional[Callable[[int, int, int, bool], None]] = None):
         self.topo, self.nbytes, self.decay, self.mix_rate = topo, nbytes, decay, mix_rate
         # visibility lag: a published version is never mixable earlier than this after its publish, whatever the link
         # model says.  On one NVSwitch box the modelled link latencies are ~1 ms against ~100 ms epochs, so without a lag
         # every mix depends on the publish just before it and the real execution serialises across GPUs.
         self.min_latency = float(min_latency)
         self.train_fn, self.mix_fn, self.publish_fn = train_fn, mix_fn, publish_fn
+        # land_fn(dst, src, epoch, accepted): the version (src, epoch) has arrived at dst; ``accepted`` is False when a newer
+        # one of the same source is already in dst's inbox (or dst is masked).  The data plane keeps one snapshot per
+        # published VERSION and binds the inbox entry here, so a source that republishes before its earlier version has
+        # landed can never change the bytes a logged mix refers to.
+        self.land_fn = land_fn
         self.masked = set(int(m) for m in masked)
         n = topo.n
         self.epoch = np.zeros(n, dtype=np.int64)
@@ -123,11 +129,16 @@ class AsyncGossipEngine:
         while heap:
             ev = heapq.heappop(heap)
             if ev.peer in self.masked:
+                if ev.kind == "landed" and self.land_fn is not None:
+                    self.land_fn(ev.peer, ev.src, int(ev.epoch), False)
                 continue
             if ev.kind == "landed":
                 prev = self.inbox[ev.peer].get(ev.src, -1)
-                if ev.epoch > prev:                        # monotone: never replace newer by older
+                ok = ev.epoch > prev                       # monotone: never replace newer by older
+                if ok:
                     self.inbox[ev.peer][ev.src] = ev.epoch
+                if self.land_fn is not None:
+                    self.land_fn(ev.peer, ev.src, int(ev.epoch), bool(ok))
                 continue
             i = ev.peer
             self.epoch[i] = ev.epoch

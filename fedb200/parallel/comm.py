@@ -97,6 +97,11 @@ class Comm:
     def check_errors(self) -> None:
         pass
 
+    def error_word(self) -> Optional[torch.Tensor]:
+        """Device word that a timed-out spin of the peer protocol sets (None: the backend has no device-side waits).  The
+        round loops read it with the round's other results — no extra synchronisation."""
+        return None
+
     def close(self) -> None:
         pass
 
@@ -107,6 +112,8 @@ class LoopbackComm(Comm):
     name = "loopback"
 
     def weighted_mean(self, acc, weight, out, shadow=None):
+        if float(weight) <= 0.0:              # every contributor masked out: keep the previous global model
+            return
         if acc.is_cuda:
             from ..ops import cuda_ops
             cuda_ops.mix_n([acc], [1.0 / float(weight)], out, shadow)
@@ -168,6 +175,8 @@ class TorchDistComm(Comm):
     def weighted_mean(self, acc, weight, out, shadow=None):
         w = torch.tensor([float(weight)], dtype=torch.float64, device=self.device)
         dist.all_reduce(w)
+        if float(w.item()) <= 0.0:            # every contributor masked out: keep the previous global model
+            return
         if out.data_ptr() != acc.data_ptr():
             out.copy_(acc)
         dist.all_reduce(out)

@@ -135,6 +135,9 @@ class PeerComm(Comm):
         count()
         self.launches += 1
 
+    def error_word(self) -> torch.Tensor:
+        return self.flags.tensor.view(torch.int32)[18:19]
+
     def check_errors(self) -> None:
         if int(self.flags.tensor.view(torch.int32)[18].item()) != 0:
             raise RuntimeError("a peer-memory barrier timed out (flag protocol error or a rank is missing)")

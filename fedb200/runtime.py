@@ -37,6 +37,7 @@ from .server.fedavg import FedAvg, weighted_average
 from .trainer.local import make_runner, resolve_device
 from .utils import MetricsLogger, OverheadMeter, PhaseTimer
 from .utils.readback import HostReadback
+from contextlib import nullcontext as _nullctx
 
 
 class FedRuntime:
@@ -54,7 +55,7 @@ class FedRuntime:
         self.local_ids = local_peer_ids(self.N, self.rank, self.world)
         self.P = peers_per_rank(self.N, self.world)
         cfg.data.max_seq_len = min(cfg.data.max_seq_len, cfg.model.max_position)
-        self.corpus = build_corpus(cfg.data, cfg.model, self.N, cfg.seed)
+        self.corpus = build_corpus(cfg.data, cfg.model, self.N, cfg.seed, vocab_path=cfg.vocab_path or cfg.init_checkpoint)
         self.runner = make_runner(cfg, self.device, cfg.seed)
         self.D = self.runner.flat.numel()
         self.nbytes = self.D * 4
@@ -80,12 +81,14 @@ class FedRuntime:
         self.masked: List[int] = []
         self.start_round = 0
         self.peer_state = None
+        self.ckpt_writer = None
         if cfg.mode == "serverless" and cfg.serverless_semantics == "parallel" and not self._full_uniform():
             self.peer_state = self.comm.alloc("state", self.P * self.D).view(self.P, self.D)
-            for li in range(len(self.local_ids)):
-                self.peer_state[li].copy_(self.global_flat)
         if cfg.resume and cfg.checkpoint_dir and os.path.exists(os.path.join(cfg.checkpoint_dir, "config.json")):
             self._resume()
+        if self.peer_state is not None and not getattr(self, "_peer_state_restored", False):
+            for li in range(len(self.local_ids)):            # after _resume(): start from the checkpointed consensus
+                self.peer_state[li].copy_(self.global_flat)
         static = detect(self.topo, cfg.anomaly_detector) if cfg.anomaly_detector not in ("none", "cosine_pagerank") else []
         self.static_masked = static
         self.log.log("init", mode=cfg.mode, clients=self.N, world=self.world, device=str(self.device),
@@ -113,22 +116,77 @@ class FedRuntime:
             if self.ledger is not None and os.path.exists(lp):
                 self.ledger = Ledger.load(lp)
                 self.ledger.assert_valid()
-        self.log.log("resume", round=self.start_round, path=path)
+        # gossip topologies keep one state per peer: each rank restores the states of its own peers
+        pp = os.path.join(path, f"peer_states_rank{self.rank}.safetensors")
+        if self.peer_state is not None and os.path.exists(pp):
+            from safetensors.torch import load_file
+            saved = load_file(pp)
+            for li, k in enumerate(self.local_ids):
+                if f"peer_{k}" in saved:
+                    self.peer_state[li].copy_(saved[f"peer_{k}"])
+            self._peer_state_restored = all(f"peer_{k}" in saved for k in self.local_ids)
+        self.log.log("resume", round=self.start_round, path=path, peer_states=bool(getattr(self, "_peer_state_restored", False)))
 
     def _checkpoint(self, rnd: int) -> Optional[float]:
+        """``global_model.save_pretrained(dir)`` every round (serverless_IID_IMDB.py:280-284).  The round loop only takes a
+        device-side snapshot; the HF-layout directory is written by a background thread (``--checkpoint-sync`` writes in
+        line and adds the cross-rank barrier of round 1).  Gossip topologies also save each rank's per-peer states."""
         cfg = self.cfg
         if not cfg.checkpoint_dir or (rnd + 1) % max(cfg.checkpoint_every, 1) != 0:
             return None
-        size = None
-        if self.rank == 0:
-            self.runner.load_flat(self.global_flat)
-            meta = {"round": rnd, "global_accuracies": self.global_accuracies, "mode": cfg.mode,
-                    "ledger_height": self.ledger.height if self.ledger else 0, "masked": self.masked}
-            size = save_pretrained(self.runner.state_dict(), cfg.model, cfg.checkpoint_dir, meta)
-            if self.ledger is not None:
-                self.ledger.save(os.path.join(cfg.checkpoint_dir, "ledger.json"))
+        cuda = self.device.type == "cuda"
+        snap = self.global_flat.clone() if self.rank == 0 else None
+        peers = self.peer_state[: len(self.local_ids)].clone() if self.peer_state is not None else None
+        ev = None
+        if cuda:
+            ev = torch.cuda.Event()
+            ev.record()
+        meta = {"round": rnd, "global_accuracies": list(self.global_accuracies), "mode": cfg.mode,
+                "ledger_height": self.ledger.height if self.ledger else 0, "masked": list(self.masked)}
+        ledger_blob = self.ledger.to_json() if (self.ledger is not None and self.rank == 0) else None
+        arena, ids, rank, path, dev = self.runner.arena, list(self.local_ids), self.rank, cfg.checkpoint_dir, self.device
+
+        def job() -> Optional[float]:
+            from .models.arena import FlatArena
+            if cuda:
+                torch.cuda.set_device(dev)
+                ev.synchronize()
+                if not hasattr(self, "_ck_stream"):
+                    self._ck_stream = torch.cuda.Stream(dev)
+            os.makedirs(path, exist_ok=True)
+            size = None
+            with (torch.cuda.stream(self._ck_stream) if cuda else _nullctx()):
+                if peers is not None:
+                    from safetensors.torch import save_file
+                    host = peers.to("cpu")
+                    fn = os.path.join(path, f"peer_states_rank{rank}.safetensors")
+                    save_file({f"peer_{k}": host[li].contiguous() for li, k in enumerate(ids)}, fn + ".tmp")
+                    os.replace(fn + ".tmp", fn)
+                if snap is not None:
+                    host = snap.to("cpu")
+                    state = FlatArena(arena.shapes, torch.float32, "cpu", buffer=host, key_order=arena.key_order).state_dict()
+                    size = save_pretrained(state, cfg.model, path, meta)
+                    if ledger_blob is not None:
+                        with open(os.path.join(path, "ledger.json.tmp"), "w") as fh:
+                            fh.write(ledger_blob)
+                        os.replace(os.path.join(path, "ledger.json.tmp"), os.path.join(path, "ledger.json"))
+            return size
+
+        if cfg.checkpoint_async:
+            if self.ckpt_writer is None:
+                from .utils.ckpt_writer import AsyncCheckpointWriter
+                self.ckpt_writer = AsyncCheckpointWriter()
+            self.ckpt_writer.submit(job)
+            return self.ckpt_writer.last_size_gib       # size of the newest checkpoint already on disk (may lag a round)
+        size = job()
         self.comm.barrier()
         return size
+
+    @staticmethod
+    def _raise_on_peer_error(rb: HostReadback, h_err) -> None:
+        if h_err is not None and int(rb.get(h_err).view(-1)[0]) != 0:
+            raise RuntimeError("a peer-memory barrier timed out during this round (a rank is late or missing): the "
+                               "aggregate may be incomplete, so the round is not recorded")
 
     # ---- one client visit ----------------------------------------------------------------------
     def _train_peer(self, li: int, k: int, rnd: int, start: torch.Tensor, lazy: bool = False) -> Dict:
@@ -141,6 +199,8 @@ class FedRuntime:
             stats = self.runner.train_epochs(tr, self.cfg.local_epochs, lazy=lazy) if lazy else \
                 self.runner.train_epochs(tr, self.cfg.local_epochs)
         corrupted = self.injector.maybe_corrupt(k, self.runner.flat, start, rnd)
+        if corrupted and hasattr(self.runner, "mark_dirty"):
+            self.runner.mark_dirty()                       # flat was edited in place: the bf16 shadow is stale
         with self.timer.phase("publish"):
             root = self._publish(li, lazy=lazy)
         return {"peer": k, "batches": len(tr), "samples": tr.num_samples, "tokens": tr.num_tokens(),
@@ -235,7 +295,10 @@ class FedRuntime:
                 te = i["testloader"]
                 ls, co, n_ds, tot = self.runner.evaluate_lazy(te)
                 pend.append((rb.push(ls.to(torch.float32)), rb.push(co.to(torch.int64)), n_ds, tot, len(te)))
+        ew = self.comm.error_word()
+        h_err = rb.push(ew) if ew is not None else None
         rb.sync()
+        self._raise_on_peer_error(rb, h_err)             # a timed-out peer barrier fails the round before it is recorded
         self.runner.d2h_bytes = getattr(self.runner, "d2h_bytes", 0) + (rb.bytes_read - rb_bytes0)
         for i in infos:
             if isinstance(i["loss"], tuple):
@@ -333,7 +396,10 @@ class FedRuntime:
         if rnd + 1 < cfg.num_rounds:
             for k in self.local_ids:
                 self._loader_cache[(k, rnd + 1)] = client_loaders(self.corpus, cfg.data, k, rnd + 1, pin=self.device.type == "cuda")
+        ew = self.comm.error_word()
+        h_err = rb.push(ew) if ew is not None else None
         rb.sync()                                            # the round's only device -> host synchronisation
+        self._raise_on_peer_error(rb, h_err)                 # a timed-out peer barrier fails the round before it is recorded
         self.runner.d2h_bytes = getattr(self.runner, "d2h_bytes", 0) + (rb.bytes_read - rb_bytes0)
         for i in infos:
             if isinstance(i["loss"], tuple):
@@ -484,6 +550,10 @@ class FedRuntime:
         for k in range(self.N):
             state[k].copy_(self.global_flat)
         epochs = np.zeros(self.N, dtype=np.int64)
+        modelled = None
+        if cfg.async_time == "modelled":                   # deterministic virtual clock (same model as the scheduler)
+            from .p2p import model_durations
+            modelled = model_durations(self.N, cfg.async_epoch_s, cfg.async_spread, cfg.seed)
 
         def train_fn(k: int) -> float:
             rnd = int(epochs[k])
@@ -496,46 +566,83 @@ class FedRuntime:
                 self.injector.maybe_corrupt(k, self.runner.flat, state[k], rnd)
                 state[k].copy_(self.runner.flat)
             epochs[k] += 1
+            if modelled is not None:
+                return float(modelled[k])
             if self.device.type == "cuda":
                 torch.cuda.synchronize()
             return time.perf_counter() - t0
 
+        # Data plane: one snapshot per published VERSION (src, epoch), shared by all its destinations and reference
+        # counted; an inbox entry (dst, src) names the version that has LANDED there (bound by land_fn), so a source that
+        # republishes before its previous version arrived cannot change what a logged mix reads.
+        versions: Dict = {}                               # (src, epoch) -> [tensor, root, references]
+        self.async_audit: List = []                       # filled when self._audit_async is set (tests)
+
+        def release(key) -> None:
+            v = versions.get(key)
+            if v is not None:
+                v[2] -= 1
+                if v[2] <= 0:
+                    del versions[key]
+
         def publish_fn(src: int, dst: int) -> None:
+            key = (src, int(epochs[src]))
             with self.timer.phase("publish"):
-                buf = inbox.setdefault((dst, src), torch.empty_like(state[src]))
-                if self.ledger is not None and buf.is_cuda:
-                    from .ops import cuda_ops
-                    root = cuda_ops.sha256_copy_root(state[src], buf, self.ledger.chunk_bytes)
-                    self.comm.launches += 2
-                else:
-                    buf.copy_(state[src])
-                    root = None
-                    if self.ledger is not None:
-                        from .ledger.merkle import merkle_root
-                        root = merkle_root(buf.numpy().tobytes(), self.ledger.chunk_bytes)
+                v = versions.get(key)
+                if v is None:
+                    buf = torch.empty_like(state[src])
+                    if self.ledger is not None and buf.is_cuda:
+                        from .ops import cuda_ops
+                        root = cuda_ops.sha256_copy_root(state[src], buf, self.ledger.chunk_bytes)
+                        self.comm.launches += 2
+                    else:
+                        buf.copy_(state[src])
+                        root = None
+                        if self.ledger is not None:
+                            from .ledger.merkle import merkle_root
+                            root = merkle_root(buf.numpy().tobytes(), self.ledger.chunk_bytes)
+                    v = versions[key] = [buf, root, 0]
+                    if getattr(self, "_audit_async", False):
+                        self.async_audit.append(("pub", src, key[1], float(buf.double().sum())))
+                v[2] += 1
                 if self.ledger is not None:
-                    self.ledger.append(int(epochs[src]), src, dst, root, self.nbytes, 0, [src, dst])
+                    self.ledger.append(key[1], src, dst, v[1], self.nbytes, 0, [src, dst])
+
+        def land_fn(dst: int, src: int, epoch: int, accepted: bool) -> None:
+            if not accepted:
+                release((src, epoch))
+                return
+            old = inbox.get((dst, src))
+            if old is not None:
+                release((src, old))
+            inbox[(dst, src)] = epoch
 
         def mix_fn(k: int, srcs: List[int], ws: List[float], self_w: float) -> None:
-            if not srcs:
-                return
             with self.timer.phase("aggregate"):
-                bufs = [state[k]] + [inbox[(k, s)] for s in srcs]
-                wts = [self_w] + list(ws)
-                if state.is_cuda:
-                    from .ops import cuda_ops
-                    cuda_ops.mix_n(bufs, wts, self.acc)
-                    self.comm.launches += 1
-                    state[k].copy_(self.acc)
-                else:
-                    self.acc.zero_()
-                    for b, w in zip(bufs, wts):
-                        self.acc.add_(b, alpha=float(w))
-                    state[k].copy_(self.acc)
+                if srcs:
+                    used = [(s, inbox[(k, s)]) for s in srcs]
+                    bufs = [state[k]] + [versions[u][0] for u in used]
+                    wts = [self_w] + list(ws)
+                    if getattr(self, "_audit_async", False):
+                        self.async_audit.append(("mix", k, int(epochs[k]), [(s, e, float(versions[(s, e)][0].double().sum()))
+                                                                             for s, e in used]))
+                    if state.is_cuda:
+                        from .ops import cuda_ops
+                        cuda_ops.mix_n(bufs, wts, self.acc)
+                        self.comm.launches += 1
+                        state[k].copy_(self.acc)
+                    else:
+                        self.acc.zero_()
+                        for b, w in zip(bufs, wts):
+                            self.acc.add_(b, alpha=float(w))
+                        state[k].copy_(self.acc)
+                for (d, s) in [key for key in inbox if key[0] == k]:        # the engine clears k's inbox after every mix
+                    release((s, inbox.pop((d, s))))
 
         masked = list(self.static_masked)
         eng = AsyncGossipEngine(self.topo, self.nbytes, train_fn, mix_fn, publish_fn, cfg.staleness_decay,
-                                masked=masked, route_optimizer=cfg.route_optimizer, min_latency=cfg.async_min_latency_s)
+                                masked=masked, route_optimizer=cfg.route_optimizer, min_latency=cfg.async_min_latency_s,
+                                fanout=cfg.async_fanout, land_fn=land_fn)
         res = eng.run(cfg.num_rounds)
         keep = [k for k in range(self.N) if k not in masked]
         self.global_flat.zero_()
@@ -582,6 +689,9 @@ class FedRuntime:
         return self._finish(last)
 
     def _finish(self, last: Dict) -> Dict:
+        if self.ckpt_writer is not None:
+            last = dict(last, model_size_gib=self.ckpt_writer.flush())       # newest checkpoint is on disk from here on
+            self.comm.barrier()
         rep = self.overhead.report()
         comm_model = info_passing_time(self.topo, self.nbytes, 0, removed=self.masked)
         out = {"global_accuracies": self.global_accuracies, **rep, "info_passing_time": comm_model,
@@ -590,6 +700,9 @@ class FedRuntime:
         return out
 
     def close(self) -> None:
+        if self.ckpt_writer is not None:
+            self.ckpt_writer.close()
+            self.ckpt_writer = None
         self.log.close()
         self.comm.close()
 

@@ -148,3 +148,106 @@ def test_checkpoint_save_load_equality_and_hf_layout(tmp_path):
     load_pretrained(m3, str(tmp_path / "ck"), ignore_mismatched_sizes=True)      # head re-initialised, body loaded
     torch.testing.assert_close(m3.state_dict()["bert.pooler.dense.weight"], m.state_dict()["bert.pooler.dense.weight"])
     assert m3.state_dict()["classifier.weight"].shape[0] == 7
+
+
+# ---- fine-tuning from a pretrained directory: from_pretrained semantics + WordPiece -------------------------------
+_VOCAB = ["[PAD]", "[UNK]", "[CLS]", "[SEP]", "[MASK]", "the", "patient", "##s", "pre", "##sent", "##ed", "with", "a",
+          "chest", "pain", ",", ".", "Pat", "##ient", "cafe", "un", "##believ", "##able", "!", "(", ")", "12", "##3", "mg", "/", "d"]
+
+
+def test_wordpiece_matches_transformers_bert_tokenizer(tmp_path):
+    from fedb200.data.tokenizer import HashTokenizer, WordPieceTokenizer, load_tokenizer
+    (tmp_path / "vocab.txt").write_text("\n".join(_VOCAB) + "\n", encoding="utf-8")
+    texts = ["The patients presented with a chest pain, unbelievable!", "Patient (123 mg/d) café. xyzzy the",
+             "  the\tpatient\n\npresented  ", "Patients unbelievable123", ""]
+    tr = pytest.importorskip("transformers")
+    for lower in (False, True):
+        (tmp_path / "tokenizer_config.json").write_text('{"do_lower_case": %s}' % ("true" if lower else "false"))
+        mine = WordPieceTokenizer.from_pretrained(str(tmp_path))
+        assert mine.lowercase is lower and mine.cls_id == 2 and mine.sep_id == 3 and mine.unk_id == 1
+        hf = tr.BertTokenizer(vocab={w: i for i, w in enumerate(_VOCAB)}, do_lower_case=lower)
+        for t in texts:
+            assert mine.encode(t) == hf(t)["input_ids"], (lower, t)
+    # greedy longest match, '##' continuation, whole-word [UNK]
+    cased = WordPieceTokenizer({w: i for i, w in enumerate(_VOCAB)}, lowercase=False)
+    assert cased.encode("unbelievable patients") == [2, 20, 21, 22, 6, 7, 3]
+    assert cased.encode("unbelievablez") == [2, 1, 3]
+    assert len(cased.encode("the " * 600)) == 512                                    # truncation=True
+    # cased / uncased inferred from the vocabulary when there is no tokenizer_config.json
+    (tmp_path / "tokenizer_config.json").unlink()
+    assert WordPieceTokenizer.from_pretrained(str(tmp_path)).lowercase is False       # "Pat" is in the vocabulary
+    assert isinstance(load_tokenizer(None, 28996), HashTokenizer)
+    assert isinstance(load_tokenizer(str(tmp_path), 28996), WordPieceTokenizer)
+
+
+def test_from_pretrained_semantics_missing_unexpected_renamed_keys(tmp_path):
+    """A pre-training checkpoint (BioBERT-style: ``cls.predictions.*`` head, TF LayerNorm names, no classifier) loads the
+    way ``AutoModelForSequenceClassification.from_pretrained`` loads it: body taken, extra head ignored, classifier fresh."""
+    c = ModelConfig.preset("bert-tiny", num_labels=2)
+    src = build_model(c, seed=11)
+    sd = OrderedDict((k, v.clone()) for k, v in src.state_dict().items() if not k.startswith("classifier."))
+    sd["cls.predictions.bias"] = torch.zeros(c.vocab_size)
+    for k in [k for k in sd if k.endswith("LayerNorm.weight")]:
+        sd[k[: -len("weight")] + "gamma"] = sd.pop(k)
+    for k in [k for k in sd if k.endswith("LayerNorm.bias")]:
+        sd[k[: -len("bias")] + "beta"] = sd.pop(k)
+    save_pretrained(sd, c, str(tmp_path / "pre"))
+    dst = build_model(ModelConfig.preset("bert-tiny", num_labels=40), seed=12)
+    fresh_head = dst.state_dict()["classifier.weight"].clone()
+    rep = load_pretrained(dst, str(tmp_path / "pre"))["load_report"]
+    assert rep["unexpected"] == ["cls.predictions.bias"] and sorted(rep["missing"]) == ["classifier.bias", "classifier.weight"]
+    for k, v in src.state_dict().items():
+        if not k.startswith("classifier."):
+            torch.testing.assert_close(dst.state_dict()[k], v)
+    torch.testing.assert_close(dst.state_dict()["classifier.weight"], fresh_head)
+    with pytest.raises(KeyError):
+        load_pretrained(dst, str(tmp_path / "pre"), strict=True)
+    # a classifier of another width is an error unless ignore_mismatched_sizes
+    save_pretrained(src.state_dict(), c, str(tmp_path / "two"))
+    with pytest.raises(RuntimeError, match="size mismatch"):
+        load_pretrained(dst, str(tmp_path / "two"))
+    assert sorted(load_pretrained(dst, str(tmp_path / "two"), ignore_mismatched_sizes=True)["load_report"]["mismatched"]) == \
+        ["classifier.bias", "classifier.weight"]
+
+
+def test_init_checkpoint_flag_fine_tunes_loaded_weights_on_csv_text(tmp_path):
+    """``serverless_IID.py --source csv --init-checkpoint DIR``: architecture from DIR/config.json, weights from DIR,
+    word pieces from DIR/vocab.txt; the run starts from the loaded weights (save_pretrained -> --init-checkpoint cycle)."""
+    import csv
+    from fedb200.config import build_parser, config_from_args
+    from fedb200.runtime import FedRuntime
+    words = ["w%d" % i for i in range(200)]
+    vocab = ["[PAD]", "[UNK]", "[CLS]", "[SEP]", "[MASK]"] + words + ["##x"]
+    c = ModelConfig.preset("bert-tiny", num_labels=2, vocab_size=len(vocab) + 10)
+    pre = build_model(c, seed=21)
+    ck = tmp_path / "pretrained"
+    save_pretrained(pre.state_dict(), c, str(ck))
+    (ck / "vocab.txt").write_text("\n".join(vocab) + "\n")
+    data = tmp_path / "Dataset"
+    data.mkdir()
+    rng = np.random.default_rng(0)
+    for fn, n in (("train_file_mt.csv", 120), ("test_file_mt.csv", 60)):
+        with open(data / fn, "w", newline="") as fh:
+            w = csv.writer(fh)
+            w.writerow(["", "description", "medical_specialty"])
+            for i in range(n):
+                y = int(rng.integers(0, 40))
+                w.writerow([i, " ".join(words[(y * 5 + int(j)) % 200] for j in rng.integers(0, 5, size=12)), y])
+    args = build_parser().parse_args(["--source", "csv", "--dataset", "medical_transcriptions", "--data-dir", str(data),
+                                      "--init-checkpoint", str(ck), "--ignore-mismatched-sizes", "--clients", "2",
+                                      "--rounds", "1", "--train-per-client", "32", "--test-per-client", "16",
+                                      "--device", "cpu", "--backend", "torch", "--lr", "1e-3"])
+    cfg = config_from_args(args)
+    assert cfg.model.hidden_size == 64 and cfg.model.num_labels == 40 and cfg.model.vocab_size == len(vocab) + 10
+    rt = FedRuntime(cfg, echo=False)
+    sd0 = rt.runner.state_dict()
+    torch.testing.assert_close(sd0["bert.encoder.layer.0.attention.self.query.weight"].cpu(),
+                               pre.state_dict()["bert.encoder.layer.0.attention.self.query.weight"])
+    assert sd0["classifier.weight"].shape[0] == 40                       # mismatched head re-initialised
+    assert int(rt.corpus.train.tokens.max()) < len(vocab) and int(rt.corpus.train.sequence(0)[0]) == 2    # real vocab ids
+    out = rt.run()
+    rt.close()
+    assert len(out["global_accuracies"]) == 1
+    moved = (rt.runner.state_dict()["bert.encoder.layer.0.attention.self.query.weight"].cpu()
+             - pre.state_dict()["bert.encoder.layer.0.attention.self.query.weight"]).abs().max()
+    assert 0 < float(moved) < 0.1                                        # fine-tuned FROM the loaded weights

@@ -185,3 +185,76 @@ def test_host_readback_roundtrip():
     with pytest.raises(RuntimeError):
         for _ in range(20):
             rb.push(b)
+
+
+def test_resume_on_ring_topology_restores_per_peer_states(tmp_path):
+    """Gossip topologies keep one state per peer; a resumed run must continue from those states (and, without them, from the
+    checkpointed consensus) — never from the initial weights under a continued ledger."""
+    cfg = _cfg(topology="ring", ledger=True, checkpoint_dir=str(tmp_path / "ck"), num_rounds=2, num_clients=5)
+    rt = FedRuntime(cfg, echo=False)
+    init = rt.global_flat.clone()
+    rt.run()
+    states = rt.peer_state.clone()
+    consensus = rt.global_flat.clone()
+    rt.close()
+    assert (tmp_path / "ck" / "peer_states_rank0.safetensors").exists()
+    assert float((states[0] - init).abs().max()) > 0 and float((states[0] - states[1]).abs().max()) > 0
+    rt2 = FedRuntime(_cfg(topology="ring", ledger=True, checkpoint_dir=str(tmp_path / "ck"), resume=True, num_rounds=3,
+                          num_clients=5), echo=False)
+    assert rt2.start_round == 2
+    torch.testing.assert_close(rt2.peer_state, states)
+    torch.testing.assert_close(rt2.global_flat, consensus)
+    out = rt2.run()
+    rt2.close()
+    assert len(out["global_accuracies"]) == 3 and out["ledger_height"] == 15
+    # per-peer file missing (older checkpoint): peers restart from the checkpointed consensus, not from the init weights
+    os.remove(tmp_path / "ck" / "peer_states_rank0.safetensors")
+    rt3 = FedRuntime(_cfg(topology="ring", checkpoint_dir=str(tmp_path / "ck"), resume=True, num_rounds=4, num_clients=5),
+                     echo=False)
+    torch.testing.assert_close(rt3.peer_state[1], rt3.global_flat)
+    assert float((rt3.global_flat - init).abs().max()) > 0
+    rt3.close()
+
+
+def test_async_single_process_mixes_the_version_the_log_names_when_latency_exceeds_an_epoch():
+    """Visibility lag > one epoch: a source republishes before its previous version has landed.  Every mix must read exactly
+    the (source, epoch) versions its log record names (replayable event log)."""
+    cfg = _cfg(asynchronous=True, num_clients=3, num_rounds=6, async_time="modelled", async_epoch_s=0.05,
+               async_min_latency_s=0.12)
+    rt = FedRuntime(cfg, echo=False)
+    rt._audit_async = True
+    rt.run()
+    eng, audit = rt.async_engine, rt.async_audit
+    rt.close()
+    pubs = {(src, ep): chk for kind, src, ep, chk in [a for a in audit if a[0] == "pub"]}
+    mixes = [a for a in audit if a[0] == "mix"]
+    logged = [r for r in eng.log if r.sources]
+    assert len(mixes) == len(logged) and len(mixes) > 0
+    stale = 0
+    for (_, peer, epoch, used), rec in zip(mixes, logged):
+        assert peer == rec.peer and epoch == rec.epoch
+        assert [(s, e) for s, e, _ in used] == list(zip(rec.sources, rec.source_epochs))
+        for s, e, chk in used:
+            assert chk == pubs[(s, e)], "mixed bytes are not the logged version"
+            stale += int(e < epoch - 1)
+    assert stale > 0, "the lag never exceeded an epoch; the test does not exercise the overwrite hazard"
+
+
+def test_async_checkpoint_writer_latest_wins_and_all_masked_keeps_model(tmp_path):
+    from fedb200.parallel.comm import LoopbackComm
+    cfg = _cfg(checkpoint_dir=str(tmp_path / "ck"), num_rounds=3)
+    assert cfg.checkpoint_async
+    rt = FedRuntime(cfg, echo=False)
+    out = rt.run()
+    w = rt.ckpt_writer
+    assert w.written >= 1 and w.written + w.dropped == 3 and out["last"]["model_size_gib"] > 0
+    from fedb200.models.hf_io import load_state
+    sd = load_state(str(tmp_path / "ck"))                  # flushed by run(): the newest round is on disk
+    from fedb200.models.arena import FlatArena
+    want = FlatArena(rt.runner.arena.shapes, buffer=rt.global_flat.clone(), key_order=rt.runner.arena.key_order).state_dict()
+    for k, v in want.items():
+        torch.testing.assert_close(sd[k], v)
+    g = rt.global_flat.clone()
+    rt.comm.weighted_mean(rt.acc, 0.0, rt.global_flat)     # every contributor masked: the global model is kept
+    torch.testing.assert_close(rt.global_flat, g)
+    rt.close()
