@@ -58,6 +58,27 @@ def run(args, make_cfg, ClockSampler, published: float) -> None:
     model = BertForSequenceClassification(hc).to(dev)
     K, W = args.steps, args.warmup
     accs = []
+    # FEDB200_TB_SDPA = default | no_cudnn | flash_efficient : which library SDPA kernels torch may pick (diagnostic knob;
+    # the cuDNN backend builds an execution plan per new (batch, seq) shape, which is slow with pad-to-longest batches)
+    sdpa_mode = os.environ.get("FEDB200_TB_SDPA", "default")
+    if sdpa_mode != "default":
+        torch.backends.cuda.enable_cudnn_sdp(False)
+    phases = {"train": 0.0, "eval": 0.0, "aggregate": 0.0}
+    want_phases = os.environ.get("FEDB200_TB_PHASES", "0") == "1"
+
+    class _phase:                                   # optional per-phase wall time (adds a device sync per phase)
+        def __init__(self, name):
+            self.name = name
+
+        def __enter__(self):
+            if want_phases:
+                torch.cuda.synchronize()
+                self.t = time.perf_counter()
+
+        def __exit__(self, *a):
+            if want_phases:
+                torch.cuda.synchronize()
+                phases[self.name] += time.perf_counter() - self.t
 
     def bucketed(loader):
         """Same samples, batches formed after sorting by length (the usual padding-reduction trick); batch order shuffled."""
@@ -83,14 +104,19 @@ def run(args, make_cfg, ClockSampler, published: float) -> None:
         tr, te = client_loaders(corpus, cfg.data, rank, rnd)
         opt = torch.optim.AdamW(model.parameters(), lr=5e-5, eps=1e-6, weight_decay=0.0)
         model.train()
-        for batch in bucketed(tr):
-            batch = {k: v.to(dev, non_blocking=True) for k, v in batch.items()}
-            with torch.autocast("cuda", dtype=torch.bfloat16, enabled=amp):
-                loss = model(**batch).loss
-            loss.backward()
-            opt.step()
-            opt.zero_grad()
-        evaluate(te)
+        with _phase("train"):
+            for batch in bucketed(tr):
+                batch = {k: v.to(dev, non_blocking=True) for k, v in batch.items()}
+                with torch.autocast("cuda", dtype=torch.bfloat16, enabled=amp):
+                    loss = model(**batch).loss
+                loss.backward()
+                opt.step()
+                opt.zero_grad()
+        with _phase("eval"):
+            evaluate(te)
+        if want_phases:
+            torch.cuda.synchronize()
+        t_agg = time.perf_counter()
         if arm == "fp32_numpy":
             params = [v.cpu().numpy() for v in model.state_dict().values()]
             allp = [params]
@@ -112,7 +138,11 @@ def run(args, make_cfg, ClockSampler, published: float) -> None:
             flat.div_(n)
             for p, q in zip(ps, _unflatten_dense_tensors(flat, ps)):
                 p.copy_(q)
-        accs.append(evaluate(global_test_loader(corpus, cfg.data, rnd)))
+        if want_phases:
+            torch.cuda.synchronize()
+            phases["aggregate"] += time.perf_counter() - t_agg
+        with _phase("eval"):
+            accs.append(evaluate(global_test_loader(corpus, cfg.data, rnd)))
         return tr.num_samples
 
     def barrier():
@@ -145,7 +175,9 @@ def run(args, make_cfg, ClockSampler, published: float) -> None:
                           "vs_baseline": round(v / published, 2), "dtype": "bf16-autocast" if amp else "fp32",
                           "data": "synthetic", "impl": "torch_baseline", "arm": arm, "clocks": clocks,
                           "config": {"model": f"transformers BertForSequenceClassification ({args.model} shape)",
-                                     "attention": hc._attn_implementation, "peers": n, "seq_len": args.seq_len,
+                                     "attention": hc._attn_implementation, "sdpa_mode": sdpa_mode,
+                                     "phases_s_incl_warmup": {k: round(v, 3) for k, v in phases.items()} if want_phases else None,
+                                     "peers": n, "seq_len": args.seq_len,
                                      "batch_per_peer": args.batch_size,
                                      "global_accuracy_per_round": [round(a, 4) for a in accs],
                                      "note": "restatement of the reference algorithm with stock PyTorch/HF; wall clock"},

@@ -55,38 +55,46 @@ def _dump(name: str, payload) -> None:
     json.dump(data, open(path, "w"), indent=1)
 
 
-def _first_below(curve, frac: float) -> int:
-    base = curve[0]["eval_loss"]
+def _first_learnt(curve, acc: float = 0.95) -> int:
     for c in curve:
-        if c["eval_loss"] < frac * base:
+        if c["accuracy"] >= acc:
             return c["round"]
     return len(curve)
 
 
-def test_bert_mini_12_rounds_curves_match_without_dropout(cuda_lib):
+def _tail_accuracy(curve, k: int = 3) -> float:
+    return float(np.mean([c["accuracy"] for c in curve[-k:]]))
+
+
+# lr 1e-3 / 16 rounds: calibrated on the fp32 CPU path — the synthetic task is at chance for ~8 rounds, collapses to
+# ~100 % within one round, wobbles once around round 10 (fresh AdamW state every round) and is stable from round 12 on.
+ROUNDS, LR = 16, 1e-3
+
+
+def test_bert_mini_16_rounds_curves_match_without_dropout(cuda_lib):
     """No dropout: the two runs differ only by bf16 rounding and summation order, so the curves must track each other —
-    same plateau (within 3 %), the loss collapses within one round of each other, same final accuracy."""
-    fused = _run("bert-mini", "fused", 12, 2e-3, dropout=False)
-    ref = _run("bert-mini", "torch", 12, 2e-3, dropout=False)
+    same plateau (within 3 %), the task is learnt within one round of each other, same accuracy at the end."""
+    fused = _run("bert-mini", "fused", ROUNDS, LR, dropout=False)
+    ref = _run("bert-mini", "torch", ROUNDS, LR, dropout=False)
     _dump("bert_mini_nodrop", {"fused_bf16": fused, "torch_fp32": ref})
-    t_f, t_r = _first_below(fused, 0.5), _first_below(ref, 0.5)
-    assert t_r < 12, "the fp32 oracle itself did not learn the synthetic task; the test is mis-calibrated"
+    t_f, t_r = _first_learnt(fused), _first_learnt(ref)
+    assert t_r < ROUNDS, "the fp32 oracle itself did not learn the synthetic task; the test is mis-calibrated"
     assert abs(t_f - t_r) <= 1, (t_f, t_r)
     for f, r in zip(fused[: min(t_f, t_r)], ref[: min(t_f, t_r)]):        # plateau before the collapse
         assert abs(f["eval_loss"] - r["eval_loss"]) <= 0.03 * r["eval_loss"], (f, r)
-    assert abs(fused[-1]["accuracy"] - ref[-1]["accuracy"]) <= 0.02, (fused[-1], ref[-1])
-    assert fused[-1]["accuracy"] >= 0.95
+    assert abs(_tail_accuracy(fused) - _tail_accuracy(ref)) <= 0.02, (fused[-3:], ref[-3:])
+    assert _tail_accuracy(fused) >= 0.95
 
 
-def test_bert_mini_14_rounds_final_accuracy_with_dropout(cuda_lib):
+def test_bert_mini_16_rounds_final_accuracy_with_dropout(cuda_lib):
     """Dropout 0.1 on (the reference's setting): the masks come from different generators, so only the outcome is compared —
-    both runs must learn the task and end within 2 accuracy points of each other."""
-    fused = _run("bert-mini", "fused", 14, 2e-3, dropout=True)
-    ref = _run("bert-mini", "torch", 14, 2e-3, dropout=True)
+    both runs must learn the task, at about the same round, and end within 2 accuracy points of each other."""
+    fused = _run("bert-mini", "fused", ROUNDS, LR, dropout=True)
+    ref = _run("bert-mini", "torch", ROUNDS, LR, dropout=True)
     _dump("bert_mini_dropout", {"fused_bf16": fused, "torch_fp32": ref})
-    assert ref[-1]["accuracy"] >= 0.9, "the fp32 oracle did not learn; mis-calibrated test"
-    assert abs(fused[-1]["accuracy"] - ref[-1]["accuracy"]) <= 0.02, (fused[-1], ref[-1])
-    assert abs(_first_below(fused, 0.5) - _first_below(ref, 0.5)) <= 2
+    assert _tail_accuracy(ref) >= 0.9, "the fp32 oracle did not learn; mis-calibrated test"
+    assert abs(_tail_accuracy(fused) - _tail_accuracy(ref)) <= 0.02, (fused[-3:], ref[-3:])
+    assert abs(_first_learnt(fused) - _first_learnt(ref)) <= 2
 
 
 def test_biobert_shape_3_rounds_losses_track_fp32(cuda_lib):
