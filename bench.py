@@ -111,10 +111,11 @@ def stage_round(rt, rnd, device):
 
 
 def kernel_round(rt, staged, gtest):
-    """One FL round entirely on the device: no H2D of inputs, no D2H of results."""
+    """One FL round entirely on the device: no H2D of inputs, no D2H of results.  Same launch order as
+    FedRuntime.round_serverless: train + publish every local peer, start the fused aggregate on the side stream, evaluate the
+    local peers underneath it, join, evaluate the new global model."""
     from fedb200.ops import cuda_ops
     run = rt.runner
-    ws = []
     for li, (train_b, test_b, n) in enumerate(staged):
         run.load_flat(rt.global_flat)
         run.sync_shadow()
@@ -126,13 +127,13 @@ def kernel_round(rt, staged, gtest):
             cuda_ops.merkle_root(leaves, rt._bench_scratch, rt._bench_root)
         else:
             rt.slots[li].copy_(run.flat)
+    rt._aggregate([1.0] * len(staged), float(len(staged)), overlap=True)
+    for li, (train_b, test_b, n) in enumerate(staged):
+        if len(staged) > 1:
+            run.load_flat(rt.slots[li])
+            run.sync_shadow()
         run.evaluate_packed(*test_b)                    # local evaluation of the trained peer (results stay on device)
-        ws.append(1.0)
-    if rt.P == 1 and rt.N == rt.world:
-        rt.comm.weighted_mean(rt.slots[0], 1.0, rt.global_flat)
-    else:
-        rt._local_weighted_sum(ws)
-        rt.comm.weighted_mean(rt.acc, float(len(ws)), rt.global_flat)
+    rt._aggregate_join()
     run.load_flat(rt.global_flat)
     run.sync_shadow()
     run.evaluate_packed(*gtest)
@@ -176,7 +177,7 @@ def run_fedb200(args):
     if n > 1:
         dist.all_reduce(want)
     want.div_(rt.N)
-    rt.comm.weighted_mean(src, float(len(rt.local_ids)), rt.global_flat)
+    rt.comm.weighted_mean(src, float(len(rt.local_ids)), rt.global_flat, max_ctas=rt.cfg.aggregate_ctas)   # the overlapped form
     sc = (rt.global_flat - want).abs().max().reshape(1).to(torch.float64)
     if n > 1:
         dist.all_reduce(sc, op=dist.ReduceOp.MAX)

@@ -25,6 +25,13 @@ constexpr int FLG_DONE = FLG_GO + 1;               // local: finished-block coun
 constexpr int FLG_ERROR = FLG_GO + 2;              // local: set to 1 when a spin timed out
 constexpr int FLG_BAR = FLG_GO + 8;                // [FLG_BAR + p]: standalone barrier epochs
 constexpr int FLG_WEIGHT = FLG_BAR + FEDB200_MAX_RANKS;   // [FLG_WEIGHT + p]: rank p's aggregation weight (float bits)
+constexpr int FLG_XCHG = FLG_WEIGHT + FEDB200_MAX_RANKS;  // [FLG_XCHG + p]  : slot-exchange barrier epochs
+constexpr int FLG_OS_START = FLG_XCHG + FEDB200_MAX_RANKS;      // one-shot all-reduce: start / end epochs
+constexpr int FLG_OS_END = FLG_OS_START + FEDB200_MAX_RANKS;
+constexpr int FLG_CLAIM = FLG_OS_END + FEDB200_MAX_RANKS;       // local: epoch claimed by the first CTA to arrive (two-shot)
+constexpr int FLG_OS_CLAIM = FLG_CLAIM + 1;                     // local: same for the one-shot family
+constexpr int FLG_OS_DONE = FLG_CLAIM + 2;                      // local: finished-block counter of the one-shot family
+static_assert(FLG_OS_DONE < FEDB200_FLAG_WORDS, "flag buffer too small");
 
 struct PeerTable {
     const float* acc[FEDB200_MAX_RANKS];
@@ -73,74 +80,151 @@ __device__ __forceinline__ void cross_rank_barrier(const PeerTable& t, int base,
     }
 }
 
-__global__ void __launch_bounds__(512) fedavg_reduce_kernel(const PeerTable t, int rank, int world, size_t n,
-                                                            float my_weight, float inv_w_arg, unsigned int epoch,
-                                                            long long timeout_cycles) {
+// Flag bases of one collective family.  Two-shot FedAvg, the one-shot small all-reduce and the slot exchange each own a
+// set of words, so their epoch sequences are independent and calls of different families may be interleaved freely.
+struct FlagBases { int start, end, claim, done; };
+constexpr FlagBases FB_TWOSHOT = {FLG_START, FLG_END, FLG_CLAIM, FLG_DONE};
+constexpr FlagBases FB_ONESHOT = {FLG_OS_START, FLG_OS_END, FLG_OS_CLAIM, FLG_OS_DONE};
+
+// Start barrier without an intra-rank dependency: the first CTA of this rank to arrive (atomicMax claim) tells every
+// peer "my input is complete" (+ publishes this rank's weight); EVERY CTA then polls this rank's own flag words, which
+// the peers write.  No CTA waits for another CTA of the same launch, so the grid need not be co-resident and a small
+// grid can run beside compute kernels on a side stream.
+__device__ __forceinline__ void start_barrier(const PeerTable& t, const FlagBases fb, int rank, int world, unsigned int epoch,
+                                              long long deadline, int publish_weight, float weight) {
     unsigned int* my = t.flags[rank];
-    const long long deadline = clock64() + timeout_cycles;
-    // ---- start barrier: every rank's accumulator is complete ------------------------------------------
-    if (blockIdx.x == 0) {
-        cross_rank_barrier(t, FLG_START, rank, world, epoch, deadline, 1, my_weight);
-        __syncthreads();
-        if (threadIdx.x == 0) st_release_gpu(my + FLG_GO, epoch);
-    } else {
-        if (threadIdx.x == 0 && !spin_until(my + FLG_GO, epoch, deadline, false)) my[FLG_ERROR] = 1u;
-        __syncthreads();
-    }
-    // sample-count weighting: every rank published its sum of n_k; the scale is 1 / sum over ranks
-    float inv_w = inv_w_arg;
-    if (inv_w <= 0.f) {
-        float tot = 0.f;
-        for (int p = 0; p < world; ++p) tot += __uint_as_float(ld_acquire_gpu(my + FLG_WEIGHT + p));
-        inv_w = tot > 0.f ? 1.f / tot : 0.f;
-    }
-    // ---- two-shot: reduce my slice from all peers, push it to all peers ---------------------------------
-    const size_t n4 = n / 4;
-    const size_t per = (n4 + world - 1) / world;
-    const size_t lo = per * rank, hi = lo + per < n4 ? lo + per : n4;
-    const size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t i = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
-        float4 v[FEDB200_MAX_RANKS];
-#pragma unroll
-        for (int p = 0; p < FEDB200_MAX_RANKS; ++p)
-            if (p < world) v[p] = __ldcs(reinterpret_cast<const float4*>(t.acc[p]) + i);
-        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-        for (int p = 0; p < FEDB200_MAX_RANKS; ++p)
-            if (p < world) { s.x += v[p].x; s.y += v[p].y; s.z += v[p].z; s.w += v[p].w; }
-        s.x *= inv_w; s.y *= inv_w; s.z *= inv_w; s.w *= inv_w;
-        uint2 sh;
-        sh.x = pack_bf16x2(s.x, s.y);
-        sh.y = pack_bf16x2(s.z, s.w);
-#pragma unroll
-        for (int p = 0; p < FEDB200_MAX_RANKS; ++p) {
-            if (p < world) {
-                reinterpret_cast<float4*>(t.out[p])[i] = s;
-                if (t.shadow[p] != nullptr) reinterpret_cast<uint2*>(t.shadow[p])[i] = sh;
-            }
+    __shared__ unsigned int s_first;
+    if (threadIdx.x == 0) s_first = atomicMax(my + fb.claim, epoch) < epoch ? 1u : 0u;
+    __syncthreads();
+    const int p = threadIdx.x;
+    if (p < world) {
+        if (s_first) {
+            if (publish_weight) t.flags[p][FLG_WEIGHT + rank] = __float_as_uint(weight);   // ordered by the release below
+            __threadfence_system();
+            st_release_sys(t.flags[p] + fb.start + rank, epoch);
         }
+        if (!spin_until(my + fb.start + p, epoch, deadline, true)) my[FLG_ERROR] = 1u;
     }
-    if (rank == world - 1) {       // scalar tail (n not a multiple of 4) is owned by the last rank
-        for (size_t i = n4 * 4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-            float s = 0.f;
-            for (int p = 0; p < world; ++p) s += t.acc[p][i];
-            s *= inv_w;
-            for (int p = 0; p < world; ++p) {
-                t.out[p][i] = s;
-                if (t.shadow[p] != nullptr) t.shadow[p][i] = __float2bfloat16_rn(s);
-            }
-        }
-    }
-    // ---- end barrier: all pushes have landed everywhere before any rank's next kernel reads `out` --------
+    __syncthreads();
+}
+// End barrier: the last CTA of this rank to finish tells every peer "my stores have been issued and fenced" and waits
+// until every peer said the same, so the next kernel on this stream sees all peers' pushes.
+__device__ __forceinline__ void end_barrier(const PeerTable& t, const FlagBases fb, int rank, int world, unsigned int epoch,
+                                            long long deadline) {
+    unsigned int* my = t.flags[rank];
     __threadfence_system();
     __syncthreads();
     __shared__ unsigned int is_last;
-    if (threadIdx.x == 0) is_last = atomicAdd(my + FLG_DONE, 1u) == gridDim.x - 1 ? 1u : 0u;
+    if (threadIdx.x == 0) is_last = atomicAdd(my + fb.done, 1u) == gridDim.x - 1 ? 1u : 0u;
     __syncthreads();
     if (is_last) {
-        if (threadIdx.x == 0) my[FLG_DONE] = 0u;
-        cross_rank_barrier(t, FLG_END, rank, world, epoch, deadline);
+        if (threadIdx.x == 0) my[fb.done] = 0u;
+        cross_rank_barrier(t, fb.end, rank, world, epoch, deadline);
     }
+}
+
+__device__ __forceinline__ float4 ld_stream4(const float* base, size_t i) { return __ldcs(reinterpret_cast<const float4*>(base) + i); }
+
+// ONESHOT = false: two-shot (rank r reduces slice r and pushes it to every rank's `out`) — bandwidth-optimal for whole models.
+// ONESHOT = true : every rank reduces the WHOLE range and writes only its own `out` — one pass, for payloads of a few KB
+//                  (Gram partials, scalars) where the second hop of the two-shot form costs more than the extra reads.
+template <bool ONESHOT>
+__global__ void __launch_bounds__(512) fedavg_reduce_kernel(const PeerTable t, int rank, int world, size_t n,
+                                                            float my_weight, float inv_w_arg, unsigned int epoch,
+                                                            long long timeout_cycles) {
+    const FlagBases fb = ONESHOT ? FB_ONESHOT : FB_TWOSHOT;
+    unsigned int* my = t.flags[rank];
+    const long long deadline = clock64() + timeout_cycles;
+    start_barrier(t, fb, rank, world, epoch, deadline, 1, my_weight);
+    // sample-count weighting: every rank published its sum of n_k; the scale is 1 / sum over ranks
+    float inv_w = inv_w_arg;
+    bool skip = false;
+    if (inv_w <= 0.f) {
+        float tot = 0.f;
+        for (int p = 0; p < world; ++p) tot += __uint_as_float(ld_acquire_gpu(my + FLG_WEIGHT + p));
+        skip = !(tot > 0.f);             // every contributor masked out: keep the previous global model on every rank
+        inv_w = skip ? 0.f : 1.f / tot;
+    }
+    // a start barrier that timed out means some rank's input is missing: do not push a partial sum over the old model
+    if (ld_acquire_gpu(my + FLG_ERROR) != 0u) skip = true;
+    if (!skip) {
+        const size_t n4 = n / 4;
+        const size_t per = ONESHOT ? n4 : (n4 + world - 1) / world;
+        const size_t lo = ONESHOT ? 0 : per * rank, hi = lo + per < n4 ? lo + per : n4;
+        const size_t stride = (size_t)gridDim.x * blockDim.x;
+        auto reduce_store = [&](size_t i, const float4 (&v)[FEDB200_MAX_RANKS]) {
+            float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int p = 0; p < FEDB200_MAX_RANKS; ++p)
+                if (p < world) { s.x += v[p].x; s.y += v[p].y; s.z += v[p].z; s.w += v[p].w; }
+            s.x *= inv_w; s.y *= inv_w; s.z *= inv_w; s.w *= inv_w;
+            uint2 sh;
+            sh.x = pack_bf16x2(s.x, s.y);
+            sh.y = pack_bf16x2(s.z, s.w);
+            if (ONESHOT) {
+                reinterpret_cast<float4*>(t.out[rank])[i] = s;
+                if (t.shadow[rank] != nullptr) reinterpret_cast<uint2*>(t.shadow[rank])[i] = sh;
+            } else {
+#pragma unroll
+                for (int p = 0; p < FEDB200_MAX_RANKS; ++p) {
+                    if (p < world) {
+                        reinterpret_cast<float4*>(t.out[p])[i] = s;
+                        if (t.shadow[p] != nullptr) reinterpret_cast<uint2*>(t.shadow[p])[i] = sh;
+                    }
+                }
+            }
+        };
+        // two positions per thread and iteration: 2 x world 16-byte peer loads in flight per thread, which is what lets a
+        // 32-CTA grid cover the ~2 us NVLink round trip at full bandwidth
+        size_t i = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+        for (; i + stride < hi; i += 2 * stride) {
+            float4 v0[FEDB200_MAX_RANKS], v1[FEDB200_MAX_RANKS];
+#pragma unroll
+            for (int p = 0; p < FEDB200_MAX_RANKS; ++p)
+                if (p < world) { v0[p] = ld_stream4(t.acc[p], i); v1[p] = ld_stream4(t.acc[p], i + stride); }
+            reduce_store(i, v0);
+            reduce_store(i + stride, v1);
+        }
+        if (i < hi) {
+            float4 v0[FEDB200_MAX_RANKS];
+#pragma unroll
+            for (int p = 0; p < FEDB200_MAX_RANKS; ++p)
+                if (p < world) v0[p] = ld_stream4(t.acc[p], i);
+            reduce_store(i, v0);
+        }
+        if (ONESHOT || rank == world - 1) {       // scalar tail (n not a multiple of 4): last rank (two-shot) / everyone
+            for (size_t k = n4 * 4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) {
+                float s = 0.f;
+                for (int p = 0; p < world; ++p) s += t.acc[p][k];
+                s *= inv_w;
+                for (int p = 0; p < world; ++p) {
+                    if (ONESHOT && p != rank) continue;
+                    t.out[p][k] = s;
+                    if (t.shadow[p] != nullptr) t.shadow[p][k] = __float2bfloat16_rn(s);
+                }
+            }
+        }
+    }
+    // all pushes have landed everywhere (two-shot) / nobody's source is overwritten while a peer still reads it (one-shot)
+    end_barrier(t, fb, rank, world, epoch, deadline);
+}
+
+// Slot exchange: every rank owns slot `rank` of a [world, slot_words] table that exists on every rank (symmetric buffer).
+// One small kernel pushes the own slot into every peer's copy and runs a cross-rank barrier, after which every rank holds
+// the whole table locally — the device-side replacement of a host all_gather of per-round metadata (Merkle roots, sample
+// counts, evaluation sums), read back with the round's other results.
+__global__ void __launch_bounds__(256) peer_exchange_kernel(const PeerTable t, int rank, int world, int slot_words,
+                                                            unsigned int epoch, long long timeout_cycles) {
+    const long long deadline = clock64() + timeout_cycles;
+    const unsigned int* mine = reinterpret_cast<const unsigned int*>(t.acc[rank]) + (size_t)rank * slot_words;
+    for (int p = 0; p < world; ++p) {
+        if (p == rank) continue;
+        unsigned int* dst = reinterpret_cast<unsigned int*>(t.out[p]) + (size_t)rank * slot_words;
+        for (int i = threadIdx.x; i < slot_words; i += blockDim.x) dst[i] = mine[i];
+    }
+    __threadfence_system();
+    __syncthreads();
+    cross_rank_barrier(t, FLG_XCHG, rank, world, epoch, deadline);
 }
 
 __global__ void __launch_bounds__(32) peer_barrier_kernel(const PeerTable t, int rank, int world, unsigned int epoch,
@@ -197,22 +281,58 @@ static long long timeout_to_cycles(int timeout_ms) {
     return (long long)timeout_ms * 2000000LL;      // ~2 GHz SM clock
 }
 
+static int fill_table(PeerTable& t, const void* const* acc_ptrs, void* const* out_ptrs, void* const* shadow_ptrs,
+                      unsigned int* const* flag_ptrs, int world) {
+    for (int p = 0; p < FEDB200_MAX_RANKS; ++p) {
+        t.acc[p] = (p < world && acc_ptrs) ? (const float*)acc_ptrs[p] : nullptr;
+        t.out[p] = (p < world && out_ptrs) ? (float*)out_ptrs[p] : nullptr;
+        t.shadow[p] = (p < world && shadow_ptrs) ? (__nv_bfloat16*)shadow_ptrs[p] : nullptr;
+        t.flags[p] = p < world ? flag_ptrs[p] : nullptr;
+    }
+    return 0;
+}
+
+extern "C" int fedb200_fedavg_reduce_ex(const float* const* acc_ptrs, float* const* out_ptrs, void* const* shadow_ptrs,
+                                        unsigned int* const* flag_ptrs, int rank, int world, size_t n, float my_weight,
+                                        float inv_total_weight, unsigned int epoch, int timeout_ms, int oneshot,
+                                        int max_ctas, void* stream) {
+    FEDB_REQUIRE(world >= 1 && world <= FEDB200_MAX_RANKS && rank >= 0 && rank < world, "fedavg_reduce: rank %d / world %d", rank, world);
+    PeerTable t;
+    fill_table(t, (const void* const*)acc_ptrs, (void* const*)out_ptrs, shadow_ptrs, flag_ptrs, world);
+    for (int p = 0; p < world; ++p)
+        FEDB_REQUIRE(((uintptr_t)t.acc[p] & 15) == 0 && ((uintptr_t)t.out[p] & 15) == 0, "fedavg_reduce: 16-byte alignment");
+    // No CTA of this kernel waits for another CTA of the same launch (claim-based start barrier), so any grid size is safe.
+    // Default: one CTA per SM when the kernel has the GPU to itself; callers that overlap it with compute pass max_ctas.
+    const size_t n4 = n / 4;
+    const size_t work = oneshot ? n4 : (n4 + world - 1) / world;
+    int grid = (int)((work + 2 * 512 - 1) / (2 * 512));
+    const int cap = max_ctas > 0 ? max_ctas : sm_count();
+    if (grid > cap) grid = cap;
+    if (grid < 1) grid = 1;
+    if (oneshot)
+        fedavg_reduce_kernel<true><<<grid, 512, 0, (cudaStream_t)stream>>>(t, rank, world, n, my_weight, inv_total_weight, epoch,
+                                                                          timeout_to_cycles(timeout_ms));
+    else
+        fedavg_reduce_kernel<false><<<grid, 512, 0, (cudaStream_t)stream>>>(t, rank, world, n, my_weight, inv_total_weight, epoch,
+                                                                           timeout_to_cycles(timeout_ms));
+    FEDB_LAUNCH_CHECK();
+    return 0;
+}
+
 extern "C" int fedb200_fedavg_reduce(const float* const* acc_ptrs, float* const* out_ptrs, void* const* shadow_ptrs,
                                      unsigned int* const* flag_ptrs, int rank, int world, size_t n, float my_weight,
                                      float inv_total_weight, unsigned int epoch, int timeout_ms, void* stream) {
-    FEDB_REQUIRE(world >= 1 && world <= FEDB200_MAX_RANKS && rank >= 0 && rank < world, "fedavg_reduce: rank %d / world %d", rank, world);
+    return fedb200_fedavg_reduce_ex(acc_ptrs, out_ptrs, shadow_ptrs, flag_ptrs, rank, world, n, my_weight, inv_total_weight,
+                                    epoch, timeout_ms, 0, 0, stream);
+}
+
+extern "C" int fedb200_peer_exchange(void* const* table_ptrs, unsigned int* const* flag_ptrs, int rank, int world,
+                                     int slot_bytes, unsigned int epoch, int timeout_ms, void* stream) {
+    FEDB_REQUIRE(world >= 1 && world <= FEDB200_MAX_RANKS && rank >= 0 && rank < world, "peer_exchange: rank %d / world %d", rank, world);
+    FEDB_REQUIRE(slot_bytes > 0 && slot_bytes % 4 == 0, "peer_exchange: slot_bytes must be a positive multiple of 4");
     PeerTable t;
-    for (int p = 0; p < FEDB200_MAX_RANKS; ++p) {
-        t.acc[p] = p < world ? acc_ptrs[p] : nullptr;
-        t.out[p] = p < world ? out_ptrs[p] : nullptr;
-        t.shadow[p] = (p < world && shadow_ptrs) ? (__nv_bfloat16*)shadow_ptrs[p] : nullptr;
-        t.flags[p] = p < world ? flag_ptrs[p] : nullptr;
-        if (p < world) FEDB_REQUIRE(((uintptr_t)t.acc[p] & 15) == 0 && ((uintptr_t)t.out[p] & 15) == 0, "fedavg_reduce: 16-byte alignment");
-    }
-    // every block must be co-resident (blocks of one rank wait on block 0): one 512-thread block per SM
-    const int grid = sm_count();
-    fedavg_reduce_kernel<<<grid, 512, 0, (cudaStream_t)stream>>>(t, rank, world, n, my_weight, inv_total_weight,
-                                                                 epoch, timeout_to_cycles(timeout_ms));
+    fill_table(t, (const void* const*)table_ptrs, table_ptrs, nullptr, flag_ptrs, world);
+    peer_exchange_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(t, rank, world, slot_bytes / 4, epoch, timeout_to_cycles(timeout_ms));
     FEDB_LAUNCH_CHECK();
     return 0;
 }

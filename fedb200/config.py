@@ -124,6 +124,7 @@ class FedConfig:
     ignore_mismatched_sizes: bool = False   # server_noniid_medical_transcriptions.py:146-148
     vocab_path: Optional[str] = None   # vocab.txt (or its directory) for the WordPiece tokenizer; default: init_checkpoint
     deterministic: bool = False        # bit-reproducible training (ordered split-K wgrad reduction): ledger roots re-derivable
+    aggregate_ctas: int = 32           # grid of the fused FedAvg reduce when it overlaps the local evaluation (side stream)
     placement: str = "balanced"        # balanced (token-count LPT) | block (contiguous id blocks)
     checkpoint_dir: Optional[str] = None
     checkpoint_async: bool = True      # background writer: the round loop only pays a device->pinned-host copy

@@ -70,10 +70,15 @@ class Comm:
         return [float(v) for v in values]
 
     # -- collectives over flat arenas -----------------------------------------------------------
-    def weighted_mean(self, acc: torch.Tensor, weight: float, out: torch.Tensor, shadow=None) -> None:
+    def weighted_mean(self, acc: torch.Tensor, weight: float, out: torch.Tensor, shadow=None, **kw) -> None:
         """``out = sum_r acc_r / sum_r weight_r`` on every rank (``acc_r`` = local sum n_k w_k);
         ``shadow`` optionally receives the bf16 copy in the same pass."""
         raise NotImplementedError
+
+    def exchange_slots(self, table: torch.Tensor) -> None:
+        """All-gather of small per-rank records: ``table`` is ``[world, k]`` with row ``rank`` filled locally; afterwards
+        every rank holds every row.  World 1: nothing to do."""
+        return None
 
     def mix_rows(self, slots: torch.Tensor, w_rows: np.ndarray, out: torch.Tensor, num_peers: int) -> None:
         """``out[i] = sum_j w_rows[i, j] * slot(j)`` for the local peers i; ``slots`` is the local
@@ -111,7 +116,7 @@ class LoopbackComm(Comm):
     buffers live on a GPU, plain torch on the CPU."""
     name = "loopback"
 
-    def weighted_mean(self, acc, weight, out, shadow=None):
+    def weighted_mean(self, acc, weight, out, shadow=None, **kw):
         if float(weight) <= 0.0:              # every contributor masked out: keep the previous global model
             return
         if acc.is_cuda:
@@ -172,7 +177,13 @@ class TorchDistComm(Comm):
         dist.all_reduce(t, op=dist.ReduceOp.SUM if op == "sum" else dist.ReduceOp.MAX)
         return t.tolist()
 
-    def weighted_mean(self, acc, weight, out, shadow=None):
+    def exchange_slots(self, table):
+        rows = [torch.empty_like(table[0]) for _ in range(self.world)]
+        dist.all_gather(rows, table[self.rank].contiguous())
+        for r, row in enumerate(rows):
+            table[r].copy_(row)
+
+    def weighted_mean(self, acc, weight, out, shadow=None, **kw):
         w = torch.tensor([float(weight)], dtype=torch.float64, device=self.device)
         dist.all_reduce(w)
         if float(w.item()) <= 0.0:            # every contributor masked out: keep the previous global model

@@ -17,7 +17,7 @@ from ..ops._lib import call, count
 from .comm import Comm
 from .placement import owner_of, peers_per_rank
 
-FLAG_WORDS = 64
+FLAG_WORDS = 128              # FEDB200_FLAG_WORDS (include/fedb200.h)
 
 
 class _RawCuda:
@@ -51,6 +51,8 @@ class PeerComm(Comm):
         self._own: List[int] = []
         self._mapped: List[int] = []
         self.epoch = 0
+        self.os_epoch = 0
+        self.xchg_epoch = 0
         self.bar_epoch = 0
         self.flags = self._alloc_symmetric("__flags__", FLAG_WORDS * 4)
         self.gram_part = None
@@ -75,6 +77,8 @@ class PeerComm(Comm):
                 ptrs.append(mp.value)
         t = torch.as_tensor(_RawCuda(ptr.value, nbytes), device=self.device)
         buf = SymmetricBuffer(name, t, ptrs, nbytes)
+        while name in self.bufs:                  # a second runtime on the same backend re-uses buffer names
+            name += "'"
         self.bufs[name] = buf
         dist.barrier()
         return buf
@@ -144,17 +148,38 @@ class PeerComm(Comm):
 
     # ---- collectives ---------------------------------------------------------------------------------------------
     def weighted_mean(self, acc: torch.Tensor, weight: float, out: torch.Tensor, shadow: Optional[torch.Tensor] = None,
-                      inv_total: float = 0.0) -> None:
+                      inv_total: float = 0.0, oneshot: Optional[bool] = None, max_ctas: int = 0) -> None:
+        """Fused FedAvg over peer memory.  ``oneshot`` (default: payloads <= 64 KB) reads every peer's whole buffer and
+        writes only the local ``out``; otherwise two-shot reduce-scatter + push.  ``max_ctas`` caps the grid for overlap
+        with compute on a side stream."""
         ab, ao = self._locate(acc)
         ob, oo = self._locate(out)
         sh = None
         if shadow is not None:
             sb, so = self._locate(shadow)
             sh = C.cast(sb.table(so), C.c_void_p)
-        self.epoch += 1
-        call("fedb200_fedavg_reduce", C.cast(ab.table(ao), C.c_void_p), C.cast(ob.table(oo), C.c_void_p), sh,
+        if oneshot is None:
+            oneshot = acc.numel() * 4 <= (64 << 10)
+        if oneshot:
+            self.os_epoch += 1
+            ep = self.os_epoch
+        else:
+            self.epoch += 1
+            ep = self.epoch
+        call("fedb200_fedavg_reduce_ex", C.cast(ab.table(ao), C.c_void_p), C.cast(ob.table(oo), C.c_void_p), sh,
              C.cast(self.flags.table(), C.c_void_p), self.rank, self.world, acc.numel(), float(weight), float(inv_total),
-             self.epoch, self.timeout_ms, torch.cuda.current_stream().cuda_stream)
+             ep, self.timeout_ms, int(bool(oneshot)), int(max_ctas), torch.cuda.current_stream().cuda_stream)
+        count()
+        self.launches += 1
+
+    def exchange_slots(self, table: torch.Tensor) -> None:
+        """``table`` is a symmetric ``[world, k]`` buffer (``comm.alloc``) whose row ``rank`` this rank has filled; after the
+        call (stream-ordered, no host involvement) every rank's copy holds every rank's row."""
+        tb, to = self._locate(table)
+        slot_bytes = table[0].numel() * table.element_size()
+        self.xchg_epoch += 1
+        call("fedb200_peer_exchange", C.cast(tb.table(to), C.c_void_p), C.cast(self.flags.table(), C.c_void_p), self.rank,
+             self.world, slot_bytes, self.xchg_epoch, self.timeout_ms, torch.cuda.current_stream().cuda_stream)
         count()
         self.launches += 1
 

@@ -41,7 +41,9 @@ from contextlib import nullcontext as _nullctx
 
 
 class FedRuntime:
-    def __init__(self, cfg: FedConfig, logger: Optional[MetricsLogger] = None, echo: bool = True):
+    def __init__(self, cfg: FedConfig, logger: Optional[MetricsLogger] = None, echo: bool = True, comm=None):
+        """``comm``: an already bootstrapped communication backend to share (several runtimes in one process, tests);
+        the runtime then does not close it."""
         self.cfg = cfg
         dev = resolve_device(cfg)
         self.rank, self.world, self.local_rank = init_distributed(dev)
@@ -50,7 +52,8 @@ class FedRuntime:
             torch.cuda.set_device(self.device)
         self.overhead = OverheadMeter()                                   # before data/model load, like :59-63
         self.log = logger or MetricsLogger(cfg.metrics_path, echo=echo, rank=self.rank)
-        self.comm = make_comm(cfg.comm, self.device, self.rank, self.world)
+        self._own_comm = comm is None
+        self.comm = comm if comm is not None else make_comm(cfg.comm, self.device, self.rank, self.world)
         self.N = cfg.num_clients
         self.local_ids = local_peer_ids(self.N, self.rank, self.world)
         self.P = peers_per_rank(self.N, self.world)
@@ -82,6 +85,11 @@ class FedRuntime:
         self.start_round = 0
         self.peer_state = None
         self.ckpt_writer = None
+        from .utils.records import RoundRecords
+        self.records = RoundRecords(self.comm, self.world, self.rank, self.P, self.device)
+        self._route_cache: Dict = {}
+        self._agg_pending = None
+        self._agg_stream = torch.cuda.Stream(self.device, priority=-1) if self.device.type == "cuda" else None
         if cfg.mode == "serverless" and cfg.serverless_semantics == "parallel" and not self._full_uniform():
             self.peer_state = self.comm.alloc("state", self.P * self.D).view(self.P, self.D)
         if cfg.resume and cfg.checkpoint_dir and os.path.exists(os.path.join(cfg.checkpoint_dir, "config.json")):
@@ -252,67 +260,97 @@ class FedRuntime:
         self.log.log("score", round=rnd, masked=bad, ranks=[round(float(x), 6) for x in ranks], band=band)
         return bad
 
-    def _ledger_append(self, rnd: int, infos: List[Dict], route_of=None, extra=None):
-        """Append this round's blocks on every rank.  ``extra`` (any picklable) rides on the same cross-rank gather; the
-        list of all ranks' extras is returned (one host collective per round instead of two)."""
+    def _route_of(self, peer: int) -> List[int]:
+        """Route recorded in the ledger block of ``peer``'s update: the slowest destination's path chosen by the optimiser
+        (a pure function of topology, size and masked set, so every rank derives the same route for every peer)."""
+        if not (self.cfg.route_optimizer and self.ledger is not None):
+            return []
+        key = (peer, tuple(sorted(self.masked)))
+        r = self._route_cache.get(key)
+        if r is None:
+            plan = optimise_route(self.topo, self.nbytes, peer, removed=self.masked)
+            r = list(plan.routes[max(plan.routes, key=lambda j: plan.latency[j])]) if plan.routes else []
+            self._route_cache[key] = r
+        return r
+
+    def _ledger_append(self, rnd: int, records: List[Dict]) -> None:
+        """Append this round's blocks (one per peer, every rank appends the same blocks).  ``records`` is the parsed round
+        table (:mod:`fedb200.utils.records`) — it came over NVLink inside the round's kernels, no host collective."""
         if self.ledger is None:
-            return self.comm.all_gather_object(extra) if extra is not None else None
+            return
         with self.timer.phase("ledger"):
-            # every rank contributes (peer, root, n_k, route) of its own peers; all ranks append the same blocks
-            mine = [(i["peer"], i["root"].hex(), i["batches"], list(route_of(i["peer"])) if route_of else [])
-                    for i in infos]
-            gathered = self.comm.all_gather_object((mine, extra))
-            every = sorted(sum((g[0] for g in gathered), []))
-            extras = [g[1] for g in gathered]
-            for peer, root_hex, n, route in every:
-                self.ledger.append(rnd, peer, BROADCAST, bytes.fromhex(root_hex), self.nbytes, n, route,
-                                   timestamp_ns=rnd * 1_000_000 + peer)
+            for r in records:
+                self.ledger.append(rnd, r["peer"], BROADCAST, r["root"], self.nbytes, r["batches"], self._route_of(r["peer"]),
+                                   timestamp_ns=rnd * 1_000_000 + r["peer"])
             if self.cfg.num_rounds <= 4 or rnd % 5 == 0:
                 self.ledger.assert_valid()
-        return extras if extra is not None else None
+
+    def _aggregate(self, ws: List[float], total: float, overlap: bool) -> None:
+        """Global model = weighted mean over every rank's peers.  ``overlap``: issue it on the side stream (SM-light grid) so
+        it runs underneath whatever the main stream does next; :meth:`_aggregate_join` orders later work after it."""
+        cuda = self.device.type == "cuda"
+        side = self._agg_stream if (overlap and cuda and self.world > 1) else None
+        if side is not None:
+            side.wait_stream(torch.cuda.current_stream())
+        with (torch.cuda.stream(side) if side is not None else _nullctx()):
+            kw = {"max_ctas": self.cfg.aggregate_ctas} if side is not None else {}
+            if self.P == 1 and self.N == self.world and not self.masked:
+                # one peer per GPU and nobody masked anywhere: the slot IS the rank's accumulator.  Every rank must take
+                # the same branch — the fused reduce reads the SAME symmetric buffer on all peers.
+                self.comm.weighted_mean(self.slots[0], 1.0, self.global_flat, **kw)
+            else:
+                self._local_weighted_sum(ws)
+                self.comm.weighted_mean(self.acc, total, self.global_flat, **kw)
+        self._agg_pending = side
+
+    def _aggregate_join(self) -> None:
+        if getattr(self, "_agg_pending", None) is not None:
+            torch.cuda.current_stream().wait_stream(self._agg_pending)
+            self._agg_pending = None
 
     # ---- server mode -----------------------------------------------------------------------------
     def round_server(self, rnd: int) -> Dict:
+        from .utils import records as R
         infos = [self._train_peer(li, k, rnd, self.global_flat, lazy=True) for li, k in enumerate(self.local_ids)]
-        rb = self.readback                               # one device -> host synchronisation per round (see round_serverless)
+        rb, rec = self.readback, self.records            # one device -> host synchronisation per round (see round_serverless)
         rb.reset()
         rb_bytes0 = rb.bytes_read
-        for i in infos:
-            if isinstance(i["loss"], torch.Tensor):
-                i["loss"] = rb.push(i["loss"].to(torch.float32))
-            if isinstance(i["root"], torch.Tensor):
-                i["root"] = rb.push(i["root"])
+        rec.begin(infos)
+        for li, i in enumerate(infos):
+            rec.set_f32(li, R.R_LOSS, i["loss"])
+            rec.set_root(li, i["root"])
         self.masked = self._score(rnd)
         with self.timer.phase("aggregate"):
             ws = [0.0 if i["peer"] in self.masked else float(i["batches"]) for i in infos]   # n_k = len(trainloader)
-            self._local_weighted_sum(ws)
-            self.comm.weighted_mean(self.acc, sum(ws), self.global_flat)
+            self._aggregate(ws, sum(ws), overlap=False)
         with self.timer.phase("evaluate"):
-            pend = []
             self.runner.load_flat(self.global_flat)
             self.runner.sync_shadow()
-            for i in infos:
+            for li, i in enumerate(infos):
                 te = i["testloader"]
                 ls, co, n_ds, tot = self.runner.evaluate_lazy(te)
-                pend.append((rb.push(ls.to(torch.float32)), rb.push(co.to(torch.int64)), n_ds, tot, len(te)))
+                rec.set_f32(li, R.R_ELOSS, ls)
+                rec.set_i32(li, R.R_ECORRECT, co)
+                for w, v in ((R.R_ENDS, n_ds), (R.R_ETOTAL, tot), (R.R_EBATCHES, len(te))):
+                    rec.set_i32(li, w, v)
+        rec.exchange()
+        h_tab = rb.push(rec.table)
         ew = self.comm.error_word()
         h_err = rb.push(ew) if ew is not None else None
         rb.sync()
         self._raise_on_peer_error(rb, h_err)             # a timed-out peer barrier fails the round before it is recorded
         self.runner.d2h_bytes = getattr(self.runner, "d2h_bytes", 0) + (rb.bytes_read - rb_bytes0)
-        for i in infos:
-            if isinstance(i["loss"], tuple):
-                i["loss"] = float(rb.get(i["loss"]))
-            if isinstance(i["root"], tuple):
-                i["root"] = bytes(rb.get(i["root"]).numpy().tobytes())
+        allrec = rec.parse(rb.get(h_tab))
         ev = []
-        for h_l, h_c, n_ds, tot, n_batches in pend:
-            loss, acc = float(rb.get(h_l)) / n_ds, (int(rb.get(h_c)) / tot if tot else 0.0)
-            ev.append((float(loss), n_batches, {"accuracy": float(acc), "loss": float(loss)}))
-        ev = sum(self._ledger_append(rnd, infos, extra=ev), [])
+        for r in allrec:
+            loss = r["eval_loss_sum"] / max(r["eval_n_ds"], 1)
+            acc = r["eval_correct"] / r["eval_total"] if r["eval_total"] else 0.0
+            ev.append((float(loss), r["eval_batches"], {"accuracy": float(acc), "loss": float(loss)}))
+        self._ledger_append(rnd, allrec)
         loss, metrics = self.strategy.aggregate_evaluate(rnd, ev)
         self.global_accuracies.append(metrics.get("accuracy", float("nan")))
-        return {"loss_distributed": loss, **metrics, "train_loss": float(np.mean([i["loss"] for i in infos])) if infos else None,
+        mine = [r["loss"] for r in allrec if r["peer"] in self.local_ids]
+        return {"loss_distributed": loss, **metrics, "train_loss": float(np.mean(mine)) if mine else None,
                 "samples": sum(i["samples"] for i in infos), "tokens": sum(i["tokens"] for i in infos)}
 
     def _local_weighted_sum(self, ws: List[float]) -> None:
@@ -333,6 +371,7 @@ class FedRuntime:
 
     # ---- serverless mode ---------------------------------------------------------------------------
     def round_serverless(self, rnd: int) -> Dict:
+        from .utils import records as R
         cfg = self.cfg
         infos = []
         if cfg.serverless_semantics == "handoff":
@@ -346,45 +385,46 @@ class FedRuntime:
             for li, k in enumerate(self.local_ids):
                 start = self.global_flat if self.peer_state is None else self.peer_state[li]
                 infos.append(self._train_peer(li, k, rnd, start, lazy=True))
-        # Device results of this round (last training loss, Merkle root, evaluation sums) are queued on the readback and
-        # resolved by ONE stream synchronisation after the global evaluation has been issued; the ledger bookkeeping and
-        # the cross-rank gather then run on the host while the GPU finishes that evaluation.
-        rb = self.readback
+        # Device results of this round (training loss, Merkle root, evaluation sums of every peer of every rank) travel in
+        # the round-record table: filled with device-side copies, exchanged over NVLink by one small kernel, read back by
+        # ONE stream synchronisation after the global evaluation has been issued.
+        rb, rec = self.readback, self.records
         rb.reset()
         rb_bytes0 = rb.bytes_read
-        for i in infos:
-            if isinstance(i["loss"], torch.Tensor):
-                i["loss"] = rb.push(i["loss"].to(torch.float32))
-            if isinstance(i["root"], torch.Tensor):
-                i["root"] = rb.push(i["root"])
-        local_ev = []
+        rec.begin(infos)
+        for li, i in enumerate(infos):
+            rec.set_f32(li, R.R_LOSS, i["loss"])
+            rec.set_root(li, i["root"])
+        online = cfg.anomaly_detector == "cosine_pagerank"
+        if not online:
+            # the mask is static, so the aggregate depends only on the published slots: start it now on the side stream and
+            # let it run underneath the local evaluation (which reads the runner's weights, not the global model)
+            self.masked = list(self.static_masked)
+            with self.timer.phase("aggregate"):
+                ws = [0.0 if i["peer"] in self.masked else 1.0 for i in infos]      # unweighted mean (:269)
+                self._aggregate(ws, sum(ws), overlap=self.peer_state is None)
         with self.timer.phase("evaluate_local"):
             for li, i in enumerate(infos):                   # client.evaluate_model() after training (:264)
                 if not (len(infos) == 1 and not i["corrupted"] and cfg.serverless_semantics != "handoff"):
                     self.runner.load_flat(self.slots[li])    # with one local peer the runner still holds exactly these
                     self.runner.sync_shadow()                # weights (and AdamW kept the bf16 shadow current)
                 ls, co, n_ds, tot = self.runner.evaluate_lazy(i["testloader"])
-                local_ev.append((rb.push(co.to(torch.int64)), tot))
-        self.masked = self._score(rnd)
+                rec.set_i32(li, R.R_LCORRECT, co)
+                rec.set_i32(li, R.R_LTOTAL, tot)
+        if online:
+            self.masked = self._score(rnd)
+            with self.timer.phase("aggregate"):
+                ws = [0.0 if i["peer"] in self.masked else 1.0 for i in infos]
+                self._aggregate(ws, sum(ws), overlap=False)
         with self.timer.phase("aggregate"):
-            ws = [0.0 if i["peer"] in self.masked else 1.0 for i in infos]          # unweighted mean (:269)
-            if self.P == 1 and self.N == self.world and not self.masked:
-                # one peer per GPU and nobody masked anywhere: the slot IS the rank's accumulator.  Every rank must take
-                # the same branch — the fused reduce reads the SAME symmetric buffer on all peers.
-                self.comm.weighted_mean(self.slots[0], 1.0, self.global_flat)
-            else:
-                self._local_weighted_sum(ws)
-                self.comm.weighted_mean(self.acc, sum(ws), self.global_flat)         # consensus / global model
+            self._aggregate_join()
             if self.peer_state is not None:
                 w = apply_mask(mixing_matrix(self.topo.adjacency(), "metropolis"), self.masked)
                 rows = w[self.local_ids[0]: self.local_ids[0] + self.P] if self.local_ids else w[:0]
                 if rows.shape[0] < self.P:
                     rows = np.concatenate([rows, np.zeros((self.P - rows.shape[0], self.N))], 0)
                 self.comm.mix_rows(self.slots, rows, self.peer_state, self.N)
-        routes = {}
-        if cfg.route_optimizer and self.ledger is not None:
-            for i in infos:
-                routes[i["peer"]] = optimise_route(self.topo, self.nbytes, i["peer"], removed=self.masked)
+        rec.exchange()
         with self.timer.phase("evaluate_global"):
             self.runner.load_flat(self.global_flat)
             self.runner.sync_shadow()
@@ -396,26 +436,21 @@ class FedRuntime:
         if rnd + 1 < cfg.num_rounds:
             for k in self.local_ids:
                 self._loader_cache[(k, rnd + 1)] = client_loaders(self.corpus, cfg.data, k, rnd + 1, pin=self.device.type == "cuda")
+        h_tab = rb.push(rec.table)
         ew = self.comm.error_word()
         h_err = rb.push(ew) if ew is not None else None
         rb.sync()                                            # the round's only device -> host synchronisation
         self._raise_on_peer_error(rb, h_err)                 # a timed-out peer barrier fails the round before it is recorded
         self.runner.d2h_bytes = getattr(self.runner, "d2h_bytes", 0) + (rb.bytes_read - rb_bytes0)
-        for i in infos:
-            if isinstance(i["loss"], tuple):
-                i["loss"] = float(rb.get(i["loss"]))
-            if isinstance(i["root"], tuple):
-                i["root"] = bytes(rb.get(i["root"]).numpy().tobytes())
-        local_acc = [(int(rb.get(h)) / tot if tot else 0.0) for h, tot in local_ev]
+        allrec = rec.parse(rb.get(h_tab))
         gl = float(rb.get(h_gl)) / g_nds
         ga = int(rb.get(h_gc)) / g_tot if g_tot else 0.0
-        locs = self._ledger_append(rnd, infos, (lambda p: []) if not routes else
-                                   (lambda p: routes[p].routes[max(routes[p].routes, key=lambda j: routes[p].latency[j])]
-                                    if p in routes and routes[p].routes else []), extra=[float(a) for a in local_acc])
-        locs = sum(locs, [])
+        self._ledger_append(rnd, allrec)
+        locs = [(r["local_correct"] / r["local_total"] if r["local_total"] else 0.0) for r in allrec]
+        mine = [r["loss"] for r in allrec if r["peer"] in self.local_ids]
         self.global_accuracies.append(float(ga))
         return {"accuracy": float(ga), "loss": float(gl), "local_accuracy": locs,
-                "train_loss": float(np.mean([i["loss"] for i in infos])) if infos else None,
+                "train_loss": float(np.mean(mine)) if mine else None,
                 "samples": sum(i["samples"] for i in infos), "tokens": sum(i["tokens"] for i in infos)}
 
     # ---- asynchronous serverless (virtual-time event engine) -------------------------------------------
@@ -704,7 +739,8 @@ class FedRuntime:
             self.ckpt_writer.close()
             self.ckpt_writer = None
         self.log.close()
-        self.comm.close()
+        if self._own_comm:
+            self.comm.close()
 
 
 def run_experiment(cfg: FedConfig, echo: bool = True) -> Dict:

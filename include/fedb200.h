@@ -18,6 +18,7 @@ extern "C" {
 #define FEDB200_ABI_VERSION 1
 #define FEDB200_MAX_MIX_SOURCES 64
 #define FEDB200_MAX_RANKS 8
+#define FEDB200_FLAG_WORDS 128      /* uint32 words of the per-rank flag buffer of the peer-memory collectives */
 
 /* GEMM epilogues */
 #define FEDB200_EPI_BIAS 0          /* out = acc + bias                                  (QKV projection)        */
@@ -178,10 +179,25 @@ int fedb200_peer_free(void* dev_ptr);
  * its clients), scales by 1 / sum over ranks of `my_weight` (exchanged through the flag words; pass
  * inv_total_weight > 0 to override) and writes the result to every rank's `out` buffer (and optional bf16
  * shadow); start/end barriers are flag words in peer memory.  acc_ptrs / out_ptrs / flag_ptrs: HOST arrays of
- * `world` peer-mapped device pointers (own rank included); flag buffers need >= 64 zero-initialised words. */
+ * `world` peer-mapped device pointers (own rank included); flag buffers need FEDB200_FLAG_WORDS zero-initialised words. */
 int fedb200_fedavg_reduce(const float* const* acc_ptrs, float* const* out_ptrs, void* const* shadow_ptrs,
                           unsigned int* const* flag_ptrs, int rank, int world, size_t n, float my_weight,
                           float inv_total_weight, unsigned int epoch, int timeout_ms, void* stream);
+/* Same, with two more knobs.  oneshot != 0: every rank reduces the WHOLE range from all peers and writes only its own
+ * `out` (one pass; for payloads of a few KB such as the N x N Gram partials or scalar metrics, where the second hop of the
+ * two-shot form dominates); its flag words are separate, so one-shot and two-shot calls may interleave (each family counts
+ * its own epochs).  max_ctas > 0 caps the grid: no CTA waits for another CTA of the same launch, so a small grid (e.g. 32)
+ * can run on a side stream beside compute kernels; 0 = one CTA per SM.  If the summed weight is 0 (every contributor masked
+ * out) or the start barrier timed out, `out` is left untouched.  Reference: serverless_IID_IMDB.py:269-270. */
+int fedb200_fedavg_reduce_ex(const float* const* acc_ptrs, float* const* out_ptrs, void* const* shadow_ptrs,
+                             unsigned int* const* flag_ptrs, int rank, int world, size_t n, float my_weight,
+                             float inv_total_weight, unsigned int epoch, int timeout_ms, int oneshot, int max_ctas,
+                             void* stream);
+/* Slot exchange (device-side all-gather of small per-round records): `table_ptrs` are the `world` peer-mapped copies of a
+ * [world, slot_bytes] table; this rank's slot is pushed into every peer's copy, then a cross-rank barrier.  Replaces the host
+ * all_gather_object of roots / counts / metrics (no counterpart in the reference, which has no communication layer). */
+int fedb200_peer_exchange(void* const* table_ptrs, unsigned int* const* flag_ptrs, int rank, int world, int slot_bytes,
+                          unsigned int epoch, int timeout_ms, void* stream);
 /* Device-side barrier across ranks (flag words in peer memory), usable between any two kernels. */
 int fedb200_peer_barrier(unsigned int* const* flag_ptrs, int rank, int world, unsigned int epoch, int timeout_ms,
                          void* stream);

@@ -42,6 +42,41 @@ def main():
         ref /= world
         torch.testing.assert_close(out, ref, rtol=1e-5, atol=1e-6)
 
+    # small grid (the form that overlaps compute on a side stream): same result, no co-residency requirement
+    acc.copy_(x * w)
+    comm.weighted_mean(acc, w, out, shadow, max_ctas=8)
+    ref = (x * w).clone()
+    dist.all_reduce(ref)
+    ref /= sum(range(1, world + 1))
+    torch.testing.assert_close(out, ref, rtol=1e-5, atol=1e-6)
+    # every contributor masked out (weight 0 on every rank): the previous global model is kept
+    keep = out.clone()
+    acc.zero_()
+    comm.weighted_mean(acc, 0.0, out)
+    torch.testing.assert_close(out, keep, rtol=0, atol=0)
+    # one-shot variant for small payloads (odd length -> scalar tail), interleaved with two-shot epochs
+    ns = 4099
+    sa, so = comm.alloc("t_small_acc", ns), comm.alloc("t_small_out", ns)
+    for it in range(3):
+        xs = torch.randn(ns, device=dev)
+        sa.copy_(xs)
+        comm.weighted_mean(sa, 1.0, so)                     # auto: <= 64 KB -> one-shot
+        rs = xs.clone()
+        dist.all_reduce(rs)
+        rs /= world
+        torch.testing.assert_close(so, rs, rtol=1e-5, atol=1e-6)
+        comm.weighted_mean(acc, 1.0, out)                   # a two-shot call in between must not disturb the epochs
+    # slot exchange: device-side all-gather of small per-rank records
+    tab = comm.alloc("t_tab", world * 48, torch.int32).view(world, 48)
+    for it in range(2):
+        tab[rank].copy_(torch.arange(48, device=dev, dtype=torch.int32) + 1000 * rank + it)
+        comm.exchange_slots(tab)
+        want = torch.stack([torch.arange(48, dtype=torch.int32) + 1000 * r + it for r in range(world)]).to(dev)
+        torch.cuda.synchronize()
+        assert torch.equal(tab, want), "slot exchange mismatch"
+        dist.barrier()                                      # nobody rewrites its row while a peer still compares
+    comm.check_errors()
+
     # ---- K4 all-gather-fused Gram over peer memory ---------------------------------------------------------
     P, D = 3, 64 * 997 + 8
     deltas = comm.alloc("t_deltas", P * D, torch.bfloat16).view(P, D)
@@ -93,12 +128,7 @@ def main():
     cfg.data.population, cfg.data.train_per_client, cfg.data.test_per_client = 800, 32, 32
     cfg.data.max_seq_len, cfg.data.batch_size, cfg.ledger = 128, 16, True
     cfg.anomaly_detector = "cosine_pagerank"
-    rt = FedRuntime(cfg, echo=False)
-    rt.comm.close()
-    rt.comm = comm                                            # reuse the already-bootstrapped backend
-    rt.global_flat = comm.alloc("r_global", rt.D); rt.global_flat.copy_(rt.runner.flat)
-    rt.slots = comm.alloc("r_slots", rt.P * rt.D).view(rt.P, rt.D)
-    rt.acc = comm.alloc("r_acc", rt.D)
+    rt = FedRuntime(cfg, echo=False, comm=comm)               # reuse the already-bootstrapped backend
     res = rt.run()
     torch.cuda.synchronize()
     comm.check_errors()
@@ -115,6 +145,23 @@ def main():
     heads = [None] * world
     dist.all_gather_object(heads, rt.ledger.head.hex())
     assert len(set(heads)) == 1, "ledgers diverged across ranks"
+    # ---- same with a static mask: the aggregate overlaps the local evaluation on the side stream, 2 peers per GPU --------
+    cfg1 = FedConfig(mode="serverless", num_clients=2 * world, num_rounds=2, device="cuda", backend="fused", comm="peer")
+    cfg1.model = ModelConfig.preset("bert-mini", num_labels=2)
+    cfg1.data.population, cfg1.data.train_per_client, cfg1.data.test_per_client = 800, 32, 32
+    cfg1.data.max_seq_len, cfg1.data.batch_size, cfg1.ledger = 128, 16, True
+    rt1 = FedRuntime(cfg1, echo=False, comm=comm)
+    res1 = rt1.run()
+    torch.cuda.synchronize()
+    comm.check_errors()
+    mine = rt1.slots[: len(rt1.local_ids)].sum(0)
+    dist.all_reduce(mine)
+    torch.testing.assert_close(rt1.global_flat, mine / (2 * world), rtol=1e-5, atol=1e-6)
+    assert rt1.ledger.height == 2 * 2 * world and rt1.ledger.validate() == -1
+    heads = [None] * world
+    dist.all_gather_object(heads, (rt1.ledger.head.hex(), res1["last"]["local_accuracy"]))
+    assert len(set(h[0] for h in heads)) == 1 and all(h[1] == heads[0][1] for h in heads), "records diverged across ranks"
+    assert len(heads[0][1]) == 2 * world
     # ---- asynchronous gossip across GPUs: schedule-driven executor, device-side pub/done flags ---------------------
     cfg2 = FedConfig(mode="serverless", num_clients=2 * world, num_rounds=3, device="cuda", backend="fused", comm="peer",
                      asynchronous=True, ledger=True, topology="full")
@@ -122,11 +169,7 @@ def main():
     cfg2.data.population, cfg2.data.train_per_client, cfg2.data.test_per_client = 800, 32, 32
     cfg2.data.max_seq_len, cfg2.data.batch_size = 128, 16
     cfg2.async_epoch_s, cfg2.async_spread = 0.001, 1.0          # short modelled epochs so versions overlap and slots recycle
-    rt2 = FedRuntime(cfg2, echo=False)
-    rt2.comm.close()
-    rt2.comm = comm
-    rt2.global_flat = comm.alloc("a_global", rt2.D); rt2.global_flat.copy_(rt2.runner.flat)
-    rt2.acc = comm.alloc("a_acc", rt2.D)
+    rt2 = FedRuntime(cfg2, echo=False, comm=comm)
     ares = rt2.run()["last"]
     torch.cuda.synchronize()
     comm.check_errors()
