@@ -42,6 +42,10 @@ class Comm:
     world: int = 1
     name: str = "base"
     launches: int = 0          # number of this repo's kernels launched by the comm layer
+    placement = None           # peer -> (rank, slot) table set by the runtime (None: block placement)
+
+    def owner(self, peer: int, num_peers: int):
+        return self.placement.owner(peer) if self.placement is not None else owner_of(peer, num_peers, self.world)
 
     def __init__(self, device):
         self.device = torch.device(device)
@@ -131,16 +135,17 @@ class LoopbackComm(Comm):
     def mix_rows(self, slots, w_rows, out, num_peers):
         P = slots.shape[0]
         assert P == num_peers, "loopback holds every peer locally"
+        slot = lambda j: slots[self.owner(j, num_peers)[1]]
         for i in range(P):
             js = [j for j in range(P) if w_rows[i, j] != 0.0]
             if slots.is_cuda:
                 from ..ops import cuda_ops
-                cuda_ops.mix_n([slots[j] for j in js], [float(w_rows[i, j]) for j in js], out[i])
+                cuda_ops.mix_n([slot(j) for j in js], [float(w_rows[i, j]) for j in js], out[i])
                 self.launches += 1
             else:
                 out[i].zero_()
                 for j in js:
-                    out[i].add_(slots[j], alpha=float(w_rows[i, j]))
+                    out[i].add_(slot(j), alpha=float(w_rows[i, j]))
 
     def gram(self, deltas, num_peers):
         if deltas.is_cuda:
@@ -204,7 +209,7 @@ class TorchDistComm(Comm):
             for j in range(num_peers):
                 w = float(w_rows[i, j])
                 if w != 0.0:
-                    r, l = owner_of(j, num_peers, self.world)
+                    r, l = self.owner(j, num_peers)
                     out[i].add_(gathered[r][l], alpha=w)
 
     def gram(self, deltas, num_peers):

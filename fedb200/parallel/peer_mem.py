@@ -193,7 +193,7 @@ class PeerComm(Comm):
             for j in range(num_peers):
                 w = float(w_rows[i, j])
                 if w != 0.0:
-                    r, l = owner_of(j, num_peers, self.world)
+                    r, l = self.owner(j, num_peers)
                     srcs.append(sb.ptrs[r] + so + l * D * 4)
                     ws.append(w)
             if srcs:

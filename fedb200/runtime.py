@@ -55,10 +55,12 @@ class FedRuntime:
         self._own_comm = comm is None
         self.comm = comm if comm is not None else make_comm(cfg.comm, self.device, self.rank, self.world)
         self.N = cfg.num_clients
-        self.local_ids = local_peer_ids(self.N, self.rank, self.world)
         self.P = peers_per_rank(self.N, self.world)
         cfg.data.max_seq_len = min(cfg.data.max_seq_len, cfg.model.max_position)
         self.corpus = build_corpus(cfg.data, cfg.model, self.N, cfg.seed, vocab_path=cfg.vocab_path or cfg.init_checkpoint)
+        self.placement = self._make_placement()
+        self.comm.placement = self.placement
+        self.local_ids = self.placement.local_ids(self.rank)
         self.runner = make_runner(cfg, self.device, cfg.seed)
         self.D = self.runner.flat.numel()
         self.nbytes = self.D * 4
@@ -99,11 +101,28 @@ class FedRuntime:
                 self.peer_state[li].copy_(self.global_flat)
         static = detect(self.topo, cfg.anomaly_detector) if cfg.anomaly_detector not in ("none", "cosine_pagerank") else []
         self.static_masked = static
+        if getattr(self, "_placement_loads", None):
+            blk, bal = self._placement_loads
+            self.log.log("placement", kind="balanced", max_tokens_block=max(blk), max_tokens_balanced=max(bal),
+                         mean_tokens=sum(bal) / len(bal))
         self.log.log("init", mode=cfg.mode, clients=self.N, world=self.world, device=str(self.device),
                      backend=self.runner.backend, comm=self.comm.name, params=self.D, model=cfg.model.name,
                      static_masked=static)
 
     # ------------------------------------------------------------------------------------------
+    def _make_placement(self):
+        """Token-balanced (LPT) client -> GPU placement for the synchronous modes when clients outnumber GPUs; the cost of
+        a client is the token count of its round-0 training set (static for the shard / Dirichlet splits, representative
+        for IID resampling).  The asynchronous executors keep the block placement their schedules are written for."""
+        from .parallel import Placement
+        cfg = self.cfg
+        if cfg.placement != "balanced" or self.world == 1 or self.N <= self.world or cfg.asynchronous:
+            return Placement.block(self.N, self.world)
+        cost = [client_loaders(self.corpus, cfg.data, k, 0)[0].num_tokens() for k in range(self.N)]
+        pl = Placement.balanced(self.N, self.world, cost)
+        self._placement_loads = (Placement.block(self.N, self.world).loads(cost), pl.loads(cost))
+        return pl
+
     def _full_uniform(self) -> bool:
         return self.cfg.topology == "full" and not self.cfg.asynchronous
 
@@ -247,6 +266,10 @@ class FedRuntime:
                 else:
                     torch.sub(self.slots[li], self.global_flat, out=self.deltas[li][: self.D])
             g = self.comm.gram(self.deltas, self.N)
+            if self.placement.kind != "block":             # rows come in (rank, slot) order: bring them into peer-id order
+                perm = torch.tensor([self.placement.owner(k)[0] * self.P + self.placement.owner(k)[1] for k in range(self.N)],
+                                    device=g.device)
+                g = g[perm][:, perm]
             if on_gpu and self.N <= 128:
                 from .ops import cuda_ops
                 ranks_d, mask_d, info_d = cuda_ops.pagerank(g[: self.N, : self.N].contiguous(), mode=1, low_only=True)
@@ -420,7 +443,7 @@ class FedRuntime:
             self._aggregate_join()
             if self.peer_state is not None:
                 w = apply_mask(mixing_matrix(self.topo.adjacency(), "metropolis"), self.masked)
-                rows = w[self.local_ids[0]: self.local_ids[0] + self.P] if self.local_ids else w[:0]
+                rows = w[self.local_ids] if self.local_ids else w[:0]
                 if rows.shape[0] < self.P:
                     rows = np.concatenate([rows, np.zeros((self.P - rows.shape[0], self.N))], 0)
                 self.comm.mix_rows(self.slots, rows, self.peer_state, self.N)

@@ -278,3 +278,19 @@ def test_async_visibility_lag_breaks_the_dependency_chain():
     assert g1 >= world and n1 > 0                   # lag: nothing more recent than a full sweep of the ranks
     verify_schedule(lagged, n, world, trials=4)
     assert lagged.slots_per_peer <= 4
+
+
+def test_balanced_placement_equalises_token_load_and_respects_slots():
+    from fedb200.parallel import Placement
+    rng = np.random.default_rng(3)
+    cost = rng.lognormal(10, 0.8, size=32)
+    blk, bal = Placement.block(32, 8), Placement.balanced(32, 8, cost)
+    assert sorted(sum((bal.local_ids(r) for r in range(8)), [])) == list(range(32))
+    assert all(len(bal.local_ids(r)) == 4 for r in range(8))                      # never more than P peers per GPU
+    for k in range(32):
+        r, l = bal.owner(k)
+        assert bal.local_ids(r)[l] == k
+        assert blk.owner(k) == (k // 4, k % 4)
+    # the straggler shrinks to (about) the largest single client plus the smallest ones, the other ranks even out
+    assert max(bal.loads(cost)) < max(blk.loads(cost)) and max(bal.loads(cost)) < 1.1 * max(cost)
+    assert np.std(sorted(bal.loads(cost))[:-1]) < 0.5 * np.std(sorted(blk.loads(cost))[:-1])
