@@ -34,11 +34,17 @@ def headers_mtime():
     return max(os.path.getmtime(h) for h in hs)
 
 
+# IEEE division / sqrt and denormals are kept where fp32 master state is updated (AdamW: sqrt(v) + eps on v ~ 1e-40 for
+# tiny gradients) and in the fp64/fp32 PageRank scorer; everything else is bf16-rounded anyway and uses --use_fast_math.
+PRECISE = {"elementwise.cu", "pagerank.cu"}
+
+
 def compile_one(name: str, force: bool, verbose_ptxas: bool):
     src, obj = os.path.join(SRC, name), os.path.join(OBJ_DIR, name[:-3] + ".o")
     if not force and os.path.exists(obj) and os.path.getmtime(obj) > max(os.path.getmtime(src), headers_mtime()):
         return name, 0, "", False
-    cmd = [NVCC, *FLAGS, "-c", src, "-o", obj]
+    flags = [f for f in FLAGS if not (name in PRECISE and f == "--use_fast_math")]
+    cmd = [NVCC, *flags, "-c", src, "-o", obj]
     if verbose_ptxas:
         cmd[1:1] = ["-Xptxas", "-v"]
     r = subprocess.run(cmd, capture_output=True, text=True)

@@ -33,6 +33,27 @@ def test_adamw_flat_matches_hf_semantics(cuda_lib):
     torch.testing.assert_close(shadow.float(), pr.bfloat16().float(), rtol=0, atol=1e-2)
 
 
+def test_adamw_flat_tiny_gradients_denormal_second_moment(cuda_lib):
+    """Gradients ~1e-20 give v ~ 1e-43 (a denormal): with flush-to-zero / approximate sqrt the update would become
+    m / (0 + eps); elementwise.cu is compiled without --use_fast_math so the kernel follows the IEEE reference."""
+    from fedb200.trainer.adamw import hf_adamw_reference_step
+    ops = _ops()
+    torch.manual_seed(1)
+    n = 262_147
+    p = torch.randn(n, device="cuda")
+    g = torch.randn(n, device="cuda") * 1e-20
+    g[::7] = torch.randn(n, device="cuda")[::7] * 1e-3           # mixed magnitudes in one launch
+    m = torch.zeros(n, device="cuda"); v = torch.zeros(n, device="cuda")
+    pr, mr, vr = p.clone(), m.clone(), v.clone()
+    for step in (1, 2, 3, 4):
+        ops.adamw_flat(p, g.clone(), m, v, None, step, 5e-5, 0.9, 0.999, 1e-6, 0.0, 1.0, True)
+        hf_adamw_reference_step(pr, g, mr, vr, step, 5e-5, 0.9, 0.999, 1e-6, 0.0)
+    assert float(vr[vr > 0].min()) < 1.2e-38                       # the reference really holds denormals
+    torch.testing.assert_close(v, vr, rtol=1e-5, atol=0)
+    torch.testing.assert_close(m, mr, rtol=1e-5, atol=0)
+    torch.testing.assert_close(p, pr, rtol=1e-6, atol=1e-9)
+
+
 def test_mix_n_weighted_sum(cuda_lib):
     ops = _ops()
     torch.manual_seed(1)
