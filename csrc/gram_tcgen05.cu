@@ -14,7 +14,7 @@
 // There is no reference counterpart (the reference scores a latency graph offline, All_graphs_IMDB_dataset
 // .ipynb:168-176); this is the north-star "anomaly scorer" of BASELINE.json.
 #include "common.cuh"
-#include "../include/fedb200.h"
+#include "peer_flags.cuh"
 
 namespace fedb {
 
@@ -26,6 +26,16 @@ struct GramMaps {
     CUtensorMap map[FEDB200_MAX_RANKS];
 };
 
+// Fused (single-launch) form: cross-rank barriers, zeroing and the N x N cross-rank sum happen inside the kernel.
+//   t.flags[p] : rank p's flag words;  t.acc[p] : rank p's partial buffers, fp32 [2][nn] (double-buffered by epoch parity);
+//   t.out[rank]: this rank's result, fp32 [nn].  world == 0 selects the plain form (caller zeroes `out`, no barriers).
+struct GramFused {
+    PeerTable t;
+    int rank, world;
+    unsigned int epoch;
+    long long timeout_cycles;
+};
+
 // Segment stacking (S > 1): with few clients a [rows x 64] tile is tiny (8 clients = 1 KB per TMA box) and the kernel
 // becomes TMA-issue bound.  Each delta row is therefore cut into segments that are stacked as extra tile rows: the
 // buffer is viewed as [rows * nseg_total, seg_len], one box brings S segments of one client ([S x 64], 2 KB at S = 16),
@@ -34,7 +44,8 @@ struct GramMaps {
 __global__ void __launch_bounds__(GR_THREADS, 1) gram_tcgen05_kernel(const __grid_constant__ GramMaps maps, int n_ranks,
                                                                      int boxes_per_rank, int box_rows, int n_pad,
                                                                      int kb_begin, int kb_end, float* __restrict__ out,
-                                                                     int n_out, int S, int nseg_total, int seg_begin) {
+                                                                     int n_out, int S, int nseg_total, int seg_begin,
+                                                                     const GramFused f) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     __shared__ __align__(8) uint64_t full_bar[GR_STAGES];
@@ -44,6 +55,18 @@ __global__ void __launch_bounds__(GR_THREADS, 1) gram_tcgen05_kernel(const __gri
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int rows_total = n_ranks * boxes_per_rank * box_rows;      // tile rows (clients x segments)
+    const bool fused = f.world > 0;
+    const int nn = n_out * n_out;
+    const long long deadline = clock64() + f.timeout_cycles;
+    if (fused) {
+        // every rank's delta rows are written, and every rank has left the previous call (so nobody still reads the
+        // partial buffer of the other parity, which this call clears for the next one)
+        start_barrier(f.t, FB_GRAM, f.rank, f.world, f.epoch, deadline, 0, 0.f);
+        asm volatile("fence.proxy.async;" ::: "memory");     // the acquire above orders generic accesses; TMA reads are async-proxy
+        out = const_cast<float*>(f.t.acc[f.rank]) + (size_t)(f.epoch & 1u) * nn;
+        float* nxt = const_cast<float*>(f.t.acc[f.rank]) + (size_t)((f.epoch + 1u) & 1u) * nn;
+        for (int i = blockIdx.x * GR_THREADS + threadIdx.x; i < nn; i += gridDim.x * GR_THREADS) nxt[i] = 0.f;
+    }
     const uint32_t tmem_cols = n_pad <= 32 ? 32u : (n_pad <= 64 ? 64u : 128u);
 
     // rows >= rows_total are never written by TMA: clear the ring once so the unused A rows are finite
@@ -124,11 +147,37 @@ __global__ void __launch_bounds__(GR_THREADS, 1) gram_tcgen05_kernel(const __gri
     tc_fence_before_sync();
     __syncthreads();
     if (warp == 1) tmem_dealloc(tmem_d, tmem_cols);
+    if (fused) {
+        // the last CTA of this rank to finish publishes "my partial is complete", waits for every rank's, and sums the
+        // partials in rank order (fixed order => every rank computes the bit-identical matrix, so their masks agree)
+        unsigned int* my = f.t.flags[f.rank];
+        __threadfence();
+        __syncthreads();
+        __shared__ unsigned int is_last;
+        if (threadIdx.x == 0) is_last = atomicAdd(my + FLG_GR_DONE, 1u) == gridDim.x - 1 ? 1u : 0u;
+        __syncthreads();
+        if (is_last) {
+            if (threadIdx.x == 0) my[FLG_GR_DONE] = 0u;
+            cross_rank_barrier(f.t, FLG_GR_READY, f.rank, f.world, f.epoch, deadline);
+            __syncthreads();
+            const size_t off = (size_t)(f.epoch & 1u) * nn;
+            for (int i = threadIdx.x; i < nn; i += GR_THREADS) {
+                float sum = 0.f;
+                for (int p = 0; p < f.world; ++p) sum += __ldcv(f.t.acc[p] + off + i);
+                f.t.out[f.rank][i] = sum;
+            }
+        }
+    }
 }
 
 }  // namespace fedb
 
 using namespace fedb;
+
+static thread_local GramFused g_fused_arg;
+static thread_local bool g_use_fused = false;          // set by the fedb200_gram_fused* wrappers around the plain entry points
+static GramFused make_plain() { GramFused f = {}; return f; }
+#define g_fused (g_use_fused ? g_fused_arg : make_plain())
 
 // rows_ptrs[r]: base of rank r's [rows_per_rank, ld] bf16 buffer (local or peer-mapped).  Accumulates G[i, j]
 // (i, j < n_out = n_ranks * rows_per_rank) over columns [col_begin, col_end) into `out` (fp32 [n_out, n_out], caller
@@ -156,7 +205,7 @@ extern "C" int fedb200_gram_bf16(const void* const* rows_ptrs, int n_ranks, int 
     FEDB_CHECK(cudaFuncSetAttribute(gram_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // S = 1: every client row is one tile row; the single box per rank covers all of the rank's rows (row coordinate 0)
     gram_tcgen05_kernel<<<grid, GR_THREADS, smem, (cudaStream_t)stream>>>(maps, n_ranks, 1, rows_per_rank, n_pad, kb_begin, kb_end, out,
-                                                                         rows_total, 1, 0, 0);
+                                                                         rows_total, 1, 0, 0, g_fused);
     FEDB_LAUNCH_CHECK();
     return 0;
 }
@@ -184,7 +233,52 @@ extern "C" int fedb200_gram_bf16_seg(const void* const* rows_ptrs, int n_ranks, 
     const size_t smem = (size_t)GR_STAGES * GR_TILE_BYTES + 1024;
     FEDB_CHECK(cudaFuncSetAttribute(gram_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     gram_tcgen05_kernel<<<grid, GR_THREADS, smem, (cudaStream_t)stream>>>(maps, n_ranks, rows_per_rank, S, n_pad, 0, kb_end, out, clients,
-                                                                         S, nseg_total, seg_begin);
+                                                                         S, nseg_total, seg_begin, g_fused);
     FEDB_LAUNCH_CHECK();
     return 0;
+}
+
+// Single-launch forms: the same kernels with the cross-rank start barrier, the clearing of the partial buffer, and the
+// one-shot N x N cross-rank sum inside the launch.  `part_ptrs[p]`: rank p's partial buffer, fp32 [2][n_out * n_out],
+// zero-initialised once (the kernel alternates between the halves by epoch parity and clears the idle half itself);
+// `flag_ptrs[p]`: rank p's flag words; `result`: this rank's [n_out, n_out] output.  Every rank must call with the same
+// epoch (1, 2, 3, ...).  One rank (`world` == 1) works too: the barriers then only involve the rank's own words.
+static int set_fused(const float* const* part_ptrs, unsigned int* const* flag_ptrs, float* result, int rank, int world,
+                     unsigned int epoch, int timeout_ms) {
+    FEDB_REQUIRE(world >= 1 && world <= FEDB200_MAX_RANKS && rank >= 0 && rank < world, "gram_fused: rank %d / world %d", rank, world);
+    GramFused& f = g_fused_arg;
+    for (int p = 0; p < FEDB200_MAX_RANKS; ++p) {
+        f.t.acc[p] = p < world ? part_ptrs[p] : nullptr;
+        f.t.flags[p] = p < world ? flag_ptrs[p] : nullptr;
+        f.t.out[p] = nullptr;
+        f.t.shadow[p] = nullptr;
+    }
+    f.t.out[rank] = result;
+    f.rank = rank; f.world = world; f.epoch = epoch;
+    f.timeout_cycles = (long long)(timeout_ms > 0 ? timeout_ms : 20000) * 2000000LL;
+    return 0;
+}
+
+extern "C" int fedb200_gram_fused(const void* const* rows_ptrs, int n_ranks, int rows_per_rank, size_t D, size_t ld,
+                                  size_t col_begin, size_t col_end, const float* const* part_ptrs,
+                                  unsigned int* const* flag_ptrs, float* result, int rank, unsigned int epoch,
+                                  int timeout_ms, int max_ctas, void* stream) {
+    int e = set_fused(part_ptrs, flag_ptrs, result, rank, n_ranks, epoch, timeout_ms);
+    if (e) return e;
+    g_use_fused = true;
+    e = fedb200_gram_bf16(rows_ptrs, n_ranks, rows_per_rank, D, ld, col_begin, col_end, nullptr, max_ctas, stream);
+    g_use_fused = false;
+    return e;
+}
+
+extern "C" int fedb200_gram_fused_seg(const void* const* rows_ptrs, int n_ranks, int rows_per_rank, size_t seg_len,
+                                      int nseg_total, int seg_begin, int S, const float* const* part_ptrs,
+                                      unsigned int* const* flag_ptrs, float* result, int rank, unsigned int epoch,
+                                      int timeout_ms, int max_ctas, void* stream) {
+    int e = set_fused(part_ptrs, flag_ptrs, result, rank, n_ranks, epoch, timeout_ms);
+    if (e) return e;
+    g_use_fused = true;
+    e = fedb200_gram_bf16_seg(rows_ptrs, n_ranks, rows_per_rank, seg_len, nseg_total, seg_begin, S, nullptr, max_ctas, stream);
+    g_use_fused = false;
+    return e;
 }

@@ -58,3 +58,41 @@ def mix_flat(flats: Sequence[torch.Tensor], weights: Sequence[float], out: Optio
         if w != 0.0:
             acc.add_(f.to(torch.float32), alpha=float(w))
     return acc
+
+
+class RelayPlan:
+    """Which two-hop routes of one gossip round are executed through a relay GPU, decided identically on every rank.
+
+    ``relays[(i, j)] = r`` says the path optimiser routes source peer ``j`` to destination peer ``i`` through peer ``r``
+    (worked example 1 -> 4 via 3, Medical_Transcriptions_All_graphs.ipynb:984-996).  A relay is executed when ``r`` lives on
+    a third GPU and that GPU still has a free relay slot: its rank copies ``j``'s slot into ``(rank, slot)`` of the symmetric
+    relay buffer (first hop) and ``i``'s row reads that copy (second hop).  One copy of ``j`` on a relay rank serves every
+    destination routed through it.  Everything else goes direct."""
+
+    def __init__(self, W: np.ndarray, owner, relays: dict, max_slots: int):
+        n = W.shape[0]
+        self.copies: dict = {}                 # relay rank -> [(source peer, slot), ...]
+        self.via: dict = {}                    # (dst peer, src peer) -> (relay rank, slot)
+        self.executed: dict = {}               # (dst peer, src peer) -> executed route [src, (relay,) dst]
+        slot_of: dict = {}
+        for i in range(n):
+            for j in range(n):
+                if i == j or W[i, j] == 0.0:
+                    continue
+                r = relays.get((i, j)) if relays else None
+                route = [j, i]
+                if r is not None and r not in (i, j):
+                    rr = owner(r)[0]
+                    if rr != owner(i)[0] and rr != owner(j)[0] and owner(i)[0] != owner(j)[0]:    # a real third GPU
+                        key = (j, rr)
+                        if key not in slot_of and len(self.copies.get(rr, [])) < max_slots:
+                            slot_of[key] = len(self.copies.setdefault(rr, []))
+                            self.copies[rr].append((j, slot_of[key]))
+                        if key in slot_of:
+                            self.via[(i, j)] = (rr, slot_of[key])
+                            route = [j, r, i]
+                self.executed[(i, j)] = route
+
+    @property
+    def any(self) -> bool:
+        return bool(self.copies)

@@ -41,6 +41,7 @@ class Comm:
     rank: int = 0
     world: int = 1
     name: str = "base"
+    executes_relays: bool = False   # True: two-hop routes of a RelayPlan really move through a relay GPU (peer backend)
     launches: int = 0          # number of this repo's kernels launched by the comm layer
     placement = None           # peer -> (rank, slot) table set by the runtime (None: block placement)
 
@@ -84,7 +85,7 @@ class Comm:
         every rank holds every row.  World 1: nothing to do."""
         return None
 
-    def mix_rows(self, slots: torch.Tensor, w_rows: np.ndarray, out: torch.Tensor, num_peers: int) -> None:
+    def mix_rows(self, slots: torch.Tensor, w_rows: np.ndarray, out: torch.Tensor, num_peers: int, plan=None) -> None:
         """``out[i] = sum_j w_rows[i, j] * slot(j)`` for the local peers i; ``slots`` is the local
         ``[P_local, D]`` symmetric buffer, j ranges over all ``num_peers`` global peers."""
         raise NotImplementedError
@@ -132,7 +133,7 @@ class LoopbackComm(Comm):
             if shadow is not None:
                 shadow.copy_(out)
 
-    def mix_rows(self, slots, w_rows, out, num_peers):
+    def mix_rows(self, slots, w_rows, out, num_peers, plan=None):
         P = slots.shape[0]
         assert P == num_peers, "loopback holds every peer locally"
         slot = lambda j: slots[self.owner(j, num_peers)[1]]
@@ -200,7 +201,7 @@ class TorchDistComm(Comm):
         if shadow is not None:
             shadow.copy_(out)
 
-    def mix_rows(self, slots, w_rows, out, num_peers):
+    def mix_rows(self, slots, w_rows, out, num_peers, plan=None):
         ppr = peers_per_rank(num_peers, self.world)
         gathered = [torch.empty_like(slots) for _ in range(self.world)]
         dist.all_gather(gathered, slots.contiguous())

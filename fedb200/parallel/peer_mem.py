@@ -38,6 +38,7 @@ class SymmetricBuffer:
 
 class PeerComm(Comm):
     name = "peer"
+    executes_relays = True
 
     def __init__(self, device, timeout_ms: int = 20000):
         super().__init__(device)
@@ -56,6 +57,8 @@ class PeerComm(Comm):
         self.bar_epoch = 0
         self.flags = self._alloc_symmetric("__flags__", FLAG_WORDS * 4)
         self.gram_part = None
+        self.relay_slots = 4                     # first-hop relay copies a rank can hold per gossip round (433 MB each)
+        self.gram_epoch = 0                      # monotone over the life of the flag words, whatever N is
 
     # ---- symmetric memory -------------------------------------------------------------------------------
     def _alloc_symmetric(self, name: str, nbytes: int) -> SymmetricBuffer:
@@ -183,49 +186,92 @@ class PeerComm(Comm):
         count()
         self.launches += 1
 
-    def mix_rows(self, slots: torch.Tensor, w_rows: np.ndarray, out: torch.Tensor, num_peers: int) -> None:
-        from ..ops import cuda_ops
+    def mix_rows(self, slots: torch.Tensor, w_rows: np.ndarray, out: torch.Tensor, num_peers: int, plan=None) -> None:
+        """``out[i] = sum_j w_rows[i, j] * slot(j)`` for this rank's rows, ONE fused launch (``csrc/gossip.cu``): start
+        barrier, optional first-hop relay copies + mid barrier, every distinct source read once for all local rows, end
+        barrier.  ``plan`` (:class:`fedb200.p2p.gossip.RelayPlan`, identical on every rank) names the two-hop routes to
+        execute through relay GPUs; ``row i`` of ``w_rows`` / ``out`` belongs to the rank's i-th local peer."""
         sb, so = self._locate(slots)
         D = slots.shape[1]
-        self.device_barrier()                                   # every peer's slot is published
-        for i in range(out.shape[0]):
-            srcs, ws = [], []
+        rows = [i for i in range(out.shape[0]) if i < w_rows.shape[0] and np.any(w_rows[i] != 0.0)]
+        local_ids = self.placement.local_ids(self.rank) if self.placement is not None else \
+            [self.rank * slots.shape[0] + i for i in range(slots.shape[0])]
+        relay_srcs, relay_dsts, any_relay = [], [], 0
+        if plan is not None and plan.any:
+            any_relay = 1
+            if getattr(self, "relay_buf", None) is None or self.relay_buf.shape[1] != D:
+                self.relay_buf = self.alloc("relay", self.relay_slots * D).view(self.relay_slots, D)
+            for j, slot in plan.copies.get(self.rank, []):
+                r, l = self.owner(j, num_peers)
+                relay_srcs.append(sb.ptrs[r] + so + l * D * 4)
+                relay_dsts.append(self.relay_buf[slot].data_ptr())
+            rb, ro = self._locate(self.relay_buf)
+        src_index, srcs = {}, []
+        W = np.zeros((max(len(rows), 1), 0), dtype=np.float32)
+        cols = []
+        for ri, i in enumerate(rows):
+            dst_peer = local_ids[i] if i < len(local_ids) else -1
             for j in range(num_peers):
                 w = float(w_rows[i, j])
-                if w != 0.0:
+                if w == 0.0:
+                    continue
+                via = plan.via.get((dst_peer, j)) if plan is not None else None
+                if via is not None:
+                    key = ("relay",) + via
+                    ptr = rb.ptrs[via[0]] + ro + via[1] * D * 4
+                else:
                     r, l = self.owner(j, num_peers)
-                    srcs.append(sb.ptrs[r] + so + l * D * 4)
-                    ws.append(w)
-            if srcs:
-                cuda_ops.mix_n(srcs, ws, out[i])
-                self.launches += 1
-        self.device_barrier()                                   # nobody overwrites a slot that is still being read
+                    key = ("slot", r, l)
+                    ptr = sb.ptrs[r] + so + l * D * 4
+                if key not in src_index:
+                    src_index[key] = len(srcs)
+                    srcs.append(ptr)
+                    cols.append(np.zeros(len(rows), dtype=np.float32))
+                cols[src_index[key]][ri] += w
+        if not rows:                       # nothing to mix on this rank: still take part in the barriers
+            rows, srcs, cols = [0], [slots[0].data_ptr()], [np.zeros(1, dtype=np.float32)]
+            keep = out[0].clone()
+        if len(srcs) > 48:
+            raise ValueError(f"{len(srcs)} distinct gossip sources on one rank exceed the fused kernel's 48; lower the topology degree")
+        wmat = np.ascontiguousarray(np.stack(cols, axis=1), dtype=np.float32)      # [n_rows, n_src]
+        self.mix_epoch = getattr(self, "mix_epoch", 0) + 1
+        vp = lambda xs: C.cast((C.c_void_p * max(len(xs), 1))(*xs), C.c_void_p)
+        call("fedb200_gossip_mix", vp(srcs), wmat.ctypes.data_as(C.c_void_p), len(srcs), vp([out[i].data_ptr() for i in rows]),
+             len(rows), vp(relay_srcs), vp(relay_dsts), len(relay_srcs), any_relay, C.cast(self.flags.table(), C.c_void_p),
+             self.rank, self.world, D, self.mix_epoch, self.timeout_ms, torch.cuda.current_stream().cuda_stream)
+        count()
+        self.launches += 1
+        if not np.any(w_rows[: out.shape[0]] != 0.0):
+            out[0].copy_(keep)
 
     def gram(self, deltas: torch.Tensor, num_peers: int) -> torch.Tensor:
-        """All-gather-fused Gram: every rank reduces ITS column slice of every rank's rows (TMA reads over
-        NVLink), then the tiny [N, N] partials are summed with the fused reduce."""
+        """All-gather-fused Gram in ONE launch: start barrier, TMA reads of this rank's column slice of every rank's rows
+        over NVLink, tcgen05 accumulation, and the one-shot cross-rank sum of the tiny [N, N] partials all happen inside
+        ``gram_tcgen05_kernel`` (round 1 needed zero_ + barrier kernel + Gram + two-shot reduce)."""
         db, do = self._locate(deltas)
         P, D = deltas.shape
         n = self.world * P
-        if self.gram_part is None or self.gram_part.numel() != n * n:
-            self.gram_part = self.alloc(f"gram_part_{n}", n * n)
+        if self.gram_part is None or self.gram_out.numel() != n * n:
+            self.gram_part = self.alloc(f"gram_part_{n}", 2 * n * n)          # [2][n*n], zero-initialised by the allocator
             self.gram_out = self.alloc(f"gram_out_{n}", n * n)
-        self.gram_part.zero_()
-        self.device_barrier()                                   # all delta rows are written
+        self.gram_epoch += 1
+        pb, po = self._locate(self.gram_part)
+        rows = (C.c_void_p * self.world)(*[p + do for p in db.ptrs])
+        stream = torch.cuda.current_stream().cuda_stream
         lay = getattr(self, "_gram_layout", None)
         if lay is not None and lay["S"] > 1 and D == lay["D_pad"]:
-            from ..ops import cuda_ops
-            cuda_ops.gram_seg([p + do for p in db.ptrs], P, lay, self.rank * lay["S"], self.gram_part)
+            call("fedb200_gram_fused_seg", C.cast(rows, C.c_void_p), self.world, P, lay["seg_len"], lay["nseg_total"],
+                 self.rank * lay["S"], lay["S"], C.cast(pb.table(po), C.c_void_p), C.cast(self.flags.table(), C.c_void_p),
+                 self.gram_out.data_ptr(), self.rank, self.gram_epoch, self.timeout_ms, 0, stream)
         else:
             kb = (D + 63) // 64
             per = (kb + self.world - 1) // self.world
             lo, hi = min(D, self.rank * per * 64), min(D, (self.rank + 1) * per * 64)
-            ptrs = (C.c_void_p * self.world)(*[p + do for p in db.ptrs])
-            call("fedb200_gram_bf16", C.cast(ptrs, C.c_void_p), self.world, P, D, D, lo, hi, self.gram_part.data_ptr(), 0,
-                 torch.cuda.current_stream().cuda_stream)
-            count()
+            call("fedb200_gram_fused", C.cast(rows, C.c_void_p), self.world, P, D, D, lo, hi,
+                 C.cast(pb.table(po), C.c_void_p), C.cast(self.flags.table(), C.c_void_p), self.gram_out.data_ptr(),
+                 self.rank, self.gram_epoch, self.timeout_ms, 0, stream)
+        count()
         self.launches += 1
-        self.weighted_mean(self.gram_part, 1.0, self.gram_out, inv_total=1.0)
         return self.gram_out.view(n, n)
 
     def close(self) -> None:

@@ -31,7 +31,7 @@ from .data.build import build_corpus, client_loaders, global_test_loader
 from .ledger import Ledger
 from .ledger.block import BROADCAST
 from .models.hf_io import load_state, save_pretrained
-from .p2p import AsyncGossipEngine, Topology, apply_mask, info_passing_time, mixing_matrix, optimise_route
+from .p2p import AsyncGossipEngine, RelayPlan, Topology, apply_mask, info_passing_time, mixing_matrix, optimise_route
 from .parallel import init_distributed, local_peer_ids, make_comm, peers_per_rank
 from .server.fedavg import FedAvg, weighted_average
 from .trainer.local import make_runner, resolve_device
@@ -283,11 +283,44 @@ class FedRuntime:
         self.log.log("score", round=rnd, masked=bad, ranks=[round(float(x), 6) for x in ranks], band=band)
         return bad
 
+    def _relay_plan(self, w: np.ndarray):
+        """Two-hop routes of this round's gossip exchange (path optimiser: Dijkstra on size / bandwidth) turned into an
+        executable relay plan; None when routing is off, nothing is routed, or the backend has no links to route over."""
+        if not (self.cfg.route_optimizer and self.comm.executes_relays and self.world > 2):
+            return None
+        key = ("relays", tuple(sorted(self.masked)))
+        relays = self._route_cache.get(key)
+        if relays is None:
+            relays = {}
+            for j in range(self.N):
+                if j in self.masked:
+                    continue
+                rp = optimise_route(self.topo, self.nbytes, j, removed=self.masked)
+                for i, path in rp.routes.items():
+                    if len(path) >= 3:
+                        relays[(i, j)] = int(path[-2])          # last hop's sender relays (longer paths: earlier hops direct)
+            self._route_cache[key] = relays
+        if not relays:
+            return None
+        plan = RelayPlan(w, self.placement.owner, relays, getattr(self.comm, "relay_slots", 4))
+        return plan if plan.any else None
+
     def _route_of(self, peer: int) -> List[int]:
-        """Route recorded in the ledger block of ``peer``'s update: the slowest destination's path chosen by the optimiser
-        (a pure function of topology, size and masked set, so every rank derives the same route for every peer)."""
+        """Route recorded in the ledger block of ``peer``'s update.  Gossip topologies: the route that was EXECUTED to the
+        peer's slowest mixing neighbour this round (direct, or through the relay GPU the fused mix kernel used).  Full
+        topology: the optimiser's path to the slowest destination (the aggregate itself is a direct all-to-all reduce)."""
         if not (self.cfg.route_optimizer and self.ledger is not None):
             return []
+        w = getattr(self, "_gossip_w", None)
+        if self.peer_state is not None and w is not None:
+            hop = self.topo.hop_seconds(self.nbytes)
+            dests = [i for i in range(self.N) if i != peer and w[i, peer] != 0.0]
+            if not dests:
+                return []
+            plan = getattr(self, "_gossip_plan", None)
+            route_to = lambda i: (plan.executed.get((i, peer), [peer, i]) if plan is not None else [peer, i])
+            cost = lambda r: sum(hop[a][b] for a, b in zip(r[:-1], r[1:]))
+            return list(max((route_to(i) for i in dests), key=cost))
         key = (peer, tuple(sorted(self.masked)))
         r = self._route_cache.get(key)
         if r is None:
@@ -446,7 +479,9 @@ class FedRuntime:
                 rows = w[self.local_ids] if self.local_ids else w[:0]
                 if rows.shape[0] < self.P:
                     rows = np.concatenate([rows, np.zeros((self.P - rows.shape[0], self.N))], 0)
-                self.comm.mix_rows(self.slots, rows, self.peer_state, self.N)
+                plan = self._relay_plan(w)
+                self.comm.mix_rows(self.slots, rows, self.peer_state, self.N, plan=plan)
+                self._gossip_plan, self._gossip_w = plan, w
         rec.exchange()
         with self.timer.phase("evaluate_global"):
             self.runner.load_flat(self.global_flat)

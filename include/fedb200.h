@@ -149,6 +149,17 @@ int fedb200_gram_bf16(const void* const* rows_ptrs, int n_ranks, int rows_per_ra
  * with ld = nseg_total * seg_len, zero padded; reduces segments [seg_begin, seg_begin + S) of every client. */
 int fedb200_gram_bf16_seg(const void* const* rows_ptrs, int n_ranks, int rows_per_rank, size_t seg_len, int nseg_total,
                           int seg_begin, int S, float* out, int max_ctas, void* stream);
+/* K4, single launch: the same kernels with everything a multi-GPU call needs inside the launch — cross-rank start barrier
+ * (all delta rows written), clearing of the partial buffer, the column-slice Gram, and the one-shot N x N cross-rank sum in
+ * rank order (bit-identical result on every rank).  part_ptrs[p]: rank p's partial buffer, fp32 [2][n * n] zero-initialised
+ * once (halves alternate by epoch parity); flag_ptrs[p]: rank p's FEDB200_FLAG_WORDS flag words; result: this rank's [n, n]
+ * fp32 output; every rank calls with the same epoch 1, 2, 3, ...  n_ranks == 1 is allowed (single GPU). */
+int fedb200_gram_fused(const void* const* rows_ptrs, int n_ranks, int rows_per_rank, size_t D, size_t ld, size_t col_begin,
+                       size_t col_end, const float* const* part_ptrs, unsigned int* const* flag_ptrs, float* result,
+                       int rank, unsigned int epoch, int timeout_ms, int max_ctas, void* stream);
+int fedb200_gram_fused_seg(const void* const* rows_ptrs, int n_ranks, int rows_per_rank, size_t seg_len, int nseg_total,
+                           int seg_begin, int S, const float* const* part_ptrs, unsigned int* const* flag_ptrs,
+                           float* result, int rank, unsigned int epoch, int timeout_ms, int max_ctas, void* stream);
 /* K5. PageRank power iteration + mean±k·sigma mask (reference: All_graphs_IMDB_dataset.ipynb:168-176). */
 int fedb200_pagerank(const float* mat, int n, int mode, double alpha, double tol, int max_iter, double k_sigma,
                      int low_only, double* ranks, int* mask, double* info, void* stream);
@@ -198,6 +209,15 @@ int fedb200_fedavg_reduce_ex(const float* const* acc_ptrs, float* const* out_ptr
  * all_gather_object of roots / counts / metrics (no counterpart in the reference, which has no communication layer). */
 int fedb200_peer_exchange(void* const* table_ptrs, unsigned int* const* flag_ptrs, int rank, int world, int slot_bytes,
                           unsigned int epoch, int timeout_ms, void* stream);
+/* K2. Fused gossip mix, one launch per rank and round: start barrier -> (first-hop relay copies -> mid barrier) ->
+ * out[r] = sum_j weights[r][j] * srcs[j] for all local rows r at once, every distinct source read once -> end barrier.
+ * srcs / relay_srcs may be peer-mapped; weights is a HOST [n_rows][n_src] row-major array; any_relay must be the same on
+ * every rank (it enables the mid barrier).  Limits: 48 sources, 8 rows, 8 relay copies.  Reference: the shared-model hand-off
+ * + numpy mean, src/Serverlesscase/serverless_IID_IMDB.py:257-270; routed paths Medical_Transcriptions_All_graphs.ipynb:984-996. */
+int fedb200_gossip_mix(const float* const* srcs, const float* weights, int n_src, float* const* outs, int n_rows,
+                       const float* const* relay_srcs, float* const* relay_dsts, int n_relay, int any_relay,
+                       unsigned int* const* flag_ptrs, int rank, int world, size_t n, unsigned int epoch, int timeout_ms,
+                       void* stream);
 /* Device-side barrier across ranks (flag words in peer memory), usable between any two kernels. */
 int fedb200_peer_barrier(unsigned int* const* flag_ptrs, int rank, int world, unsigned int epoch, int timeout_ms,
                          void* stream);

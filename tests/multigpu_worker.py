@@ -120,6 +120,29 @@ def main():
     comm.check_errors()
     torch.testing.assert_close(outm, refm, rtol=1e-4, atol=1e-5)
 
+    # same exchange again (second epoch of the fused kernel's flag words) and, with >= 3 GPUs, two-hop routes executed
+    # through a relay GPU: the result must not depend on how the bytes travelled
+    from fedb200.p2p import RelayPlan
+    from fedb200.parallel import Placement
+    comm.placement = Placement.block(N, world)
+    slots.copy_(torch.randn(2, Dm, device=dev))
+    relays = {}
+    if world >= 3:
+        for i in range(N):
+            for j in range(N):
+                if W[i, j] != 0.0 and i != j and (i + j) % 3 == 0:
+                    relays[(i, j)] = (max(i, j) + 2) % N           # some third peer
+    plan = RelayPlan(W, comm.placement.owner, relays, comm.relay_slots)
+    comm.mix_rows(slots, W[rank * 2: rank * 2 + 2], outm, N, plan=plan if plan.any else None)
+    dist.all_gather(alls, slots.contiguous())
+    refm = torch.tensor(W[rank * 2: rank * 2 + 2], dtype=torch.float32, device=dev) @ torch.cat(alls, 0)
+    torch.cuda.synchronize()
+    comm.check_errors()
+    torch.testing.assert_close(outm, refm, rtol=1e-4, atol=1e-5)
+    n_relayed = len(plan.via)
+    assert world < 3 or n_relayed > 0, "the relay path was not exercised"
+    comm.placement = None
+
     # ---- whole serverless round through the runtime on the fused backend ------------------------------------------
     from fedb200.config import FedConfig, ModelConfig
     from fedb200.runtime import FedRuntime
@@ -185,6 +208,28 @@ def main():
     mine = rt2.async_state[: len(rt2.local_ids)].sum(0)
     dist.all_reduce(mine)
     torch.testing.assert_close(rt2.global_flat, mine / (2 * world), rtol=1e-5, atol=1e-6)
+    # ---- ring gossip through the runtime: per-peer states, fused mix kernel, executed routes in the ledger ----------------
+    cfg3 = FedConfig(mode="serverless", num_clients=2 * world, num_rounds=2, device="cuda", backend="fused", comm="peer",
+                     topology="reference10" if 2 * world == 10 else "ring", ledger=True)
+    cfg3.model = ModelConfig.preset("bert-mini", num_labels=2)
+    cfg3.data.population, cfg3.data.train_per_client, cfg3.data.test_per_client = 800, 32, 32
+    cfg3.data.max_seq_len, cfg3.data.batch_size = 128, 16
+    rt3 = FedRuntime(cfg3, echo=False, comm=comm)
+    rt3.run()
+    torch.cuda.synchronize()
+    comm.check_errors()
+    from fedb200.p2p import apply_mask, mixing_matrix
+    Wr = apply_mask(mixing_matrix(rt3.topo.adjacency(), "metropolis"), rt3.masked)
+    alls3 = [torch.empty_like(rt3.slots) for _ in range(world)]
+    dist.all_gather(alls3, rt3.slots.contiguous())
+    cat3 = torch.cat(alls3, 0)                                # (rank, slot) order -> peer-id order
+    S3 = torch.stack([cat3[rt3.placement.owner(k)[0] * rt3.P + rt3.placement.owner(k)[1]] for k in range(2 * world)])
+    want3 = torch.tensor(Wr[rt3.local_ids], dtype=torch.float32, device=dev) @ S3
+    torch.testing.assert_close(rt3.peer_state[: len(rt3.local_ids)], want3, rtol=1e-4, atol=1e-5)
+    assert rt3.ledger.validate() == -1 and rt3.ledger.height == 2 * 2 * world
+    heads = [None] * world
+    dist.all_gather_object(heads, rt3.ledger.head.hex())
+    assert len(set(heads)) == 1, "gossip ledgers diverged across ranks"
     if rank == 0:
         print("MULTIGPU_OK", world, res["global_accuracies"], "async slots", ares["outbox_slots"], "mixes", ares["mixes"])
     comm.close()

@@ -294,3 +294,29 @@ def test_balanced_placement_equalises_token_load_and_respects_slots():
     # the straggler shrinks to (about) the largest single client plus the smallest ones, the other ranks even out
     assert max(bal.loads(cost)) < max(blk.loads(cost)) and max(bal.loads(cost)) < 1.1 * max(cost)
     assert np.std(sorted(bal.loads(cost))[:-1]) < 0.5 * np.std(sorted(blk.loads(cost))[:-1])
+
+
+def test_relay_plan_executes_two_hop_routes_through_a_third_gpu():
+    from fedb200.p2p import RelayPlan
+    from fedb200.parallel import Placement
+    pl = Placement.block(8, 4)                                   # peers 0-1 on rank 0, 2-3 on rank 1, ...
+    W = np.zeros((8, 8))
+    for i in range(8):
+        W[i, i], W[i, (i + 1) % 8], W[i, (i + 3) % 8] = 0.5, 0.25, 0.25
+    relays = {(0, 3): 5, (1, 4): 5, (2, 5): 3, (6, 7): 0, (4, 5): 6}
+    plan = RelayPlan(W, pl.owner, relays, max_slots=1)
+    # 3 -> 5 -> 0: relay peer 5 lives on rank 2, neither the source's (1) nor the destination's (0) GPU -> executed
+    assert plan.via[(0, 3)] == (2, 0) and plan.executed[(0, 3)] == [3, 5, 0] and plan.copies[2] == [(3, 0)]
+    # 4 -> 5 -> 1: the relay shares the source's GPU (rank 2) -> direct
+    assert (1, 4) not in plan.via and plan.executed[(1, 4)] == [4, 1]
+    # 5 -> 3 -> 2: the relay shares the destination's GPU -> direct;  7 -> 0 -> 6: the relay's GPU is also the ... source 7 on rank 3, dst 6 on rank 3
+    assert (2, 5) not in plan.via and (6, 7) not in plan.via
+    # W[4, 5] is a real edge (4 hears from 5) but both live on rank 2 -> never relayed
+    assert plan.executed[(4, 5)] == [5, 4]
+    # every nonzero off-diagonal edge has an executed route that starts at the source and ends at the destination
+    for (i, j), r in plan.executed.items():
+        assert r[0] == j and r[-1] == i and W[i, j] != 0.0
+    # slot budget: a second distinct source through rank 2 does not fit with max_slots = 1 -> direct
+    plan2 = RelayPlan(W, pl.owner, {(0, 3): 5, (7, 0): 4}, max_slots=1)
+    assert plan2.via == {(0, 3): (2, 0)} and plan2.executed[(7, 0)] == [0, 7]
+    assert not RelayPlan(W, pl.owner, {}, 4).any

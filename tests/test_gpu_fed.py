@@ -94,6 +94,43 @@ def test_gram_segment_stacked_for_few_clients(cuda_lib, N, D):
     assert err <= 2e-3 * ref.abs().max().item() + 1e-3, f"segmented gram max err {err}"
 
 
+def test_gram_fused_single_launch_one_rank_three_epochs(cuda_lib):
+    """The single-launch form (barriers, partial clearing and the cross-rank sum inside the kernel) on one GPU: three calls
+    in a row with different data must each give the plain Gram — the partial buffers alternate by epoch parity and are
+    cleared by the kernel itself, never by the caller."""
+    import ctypes as C
+    ops = _ops()
+    lib = cuda_lib
+    N, D = 8, 64 * 3000
+    lay = ops.gram_layout(D, 1, N)
+    flags = torch.zeros(128, dtype=torch.int32, device="cuda")
+    part = torch.zeros(2 * N * N, device="cuda")
+    res = torch.full((N, N), 7.0, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    arr = lambda t: C.cast((C.c_void_p * 1)(t.data_ptr()), C.c_void_p)
+    for epoch in (1, 2, 3):
+        torch.manual_seed(epoch)
+        d = torch.zeros(N, lay["D_pad"], dtype=torch.bfloat16, device="cuda")
+        d[:, :D] = (torch.randn(N, D, device="cuda") * 0.1).bfloat16()
+        rc = lib.fedb200_gram_fused_seg(arr(d), 1, N, lay["seg_len"], lay["nseg_total"], 0, lay["S"], arr(part), arr(flags),
+                                        res.data_ptr(), 0, epoch, 2000, 0, stream)
+        assert rc == 0, lib.fedb200_last_error().decode()
+        ref = d.float() @ d.float().T
+        torch.cuda.synchronize()
+        err = (res - ref).abs().max().item()
+        assert err <= 2e-3 * ref.abs().max().item() + 1e-3, f"epoch {epoch}: fused gram max err {err}"
+    # column-range form (S = 1)
+    d = (torch.randn(40, 64 * 500, device="cuda") * 0.1).bfloat16()
+    part2, res2 = torch.zeros(2 * 1600, device="cuda"), torch.empty(40, 40, device="cuda")
+    rc = lib.fedb200_gram_fused(arr(d), 1, 40, d.shape[1], d.shape[1], 0, d.shape[1], arr(part2), arr(flags), res2.data_ptr(),
+                                0, 4, 2000, 0, stream)
+    assert rc == 0, lib.fedb200_last_error().decode()
+    torch.cuda.synchronize()
+    ref = d.float() @ d.float().T
+    assert (res2 - ref).abs().max().item() <= 2e-3 * ref.abs().max().item() + 1e-3
+    assert int(flags[18]) == 0                                  # no barrier timed out
+
+
 def test_gram_pagerank_flags_poisoned_update(cuda_lib):
     from fedb200.anomaly import score_updates
     ops = _ops()
