@@ -71,8 +71,11 @@ def main():
     ms = timed(lambda: comm.weighted_mean(acc, 1.0, out, max_ctas=32), dev)
     rows.append(("fedavg_reduce (fp32 in/out), 32-CTA grid (the form overlapped with compute)", ms, bytes_dir / LINK * 1e3))
     small_a, small_o = comm.alloc("b_small_a", 4096), comm.alloc("b_small_o", 4096)
-    ms = timed(lambda: comm.weighted_mean(small_a, 1.0, small_o), dev, iters=20)
-    rows.append(("one-shot all-reduce, 16 KB (latency-bound; roofline = one NVLink round trip ~2 us x 2 barriers)", ms, 0.004))
+    def small50():                      # 50 back-to-back calls: a single call's event time is dominated by the launch skew between ranks
+        for _ in range(50):
+            comm.weighted_mean(small_a, 1.0, small_o)
+    ms = timed(small50, dev, iters=5) / 50
+    rows.append(("one-shot all-reduce, 16 KB, per call over 50 back-to-back (latency-bound; roofline ~ 2 barriers x NVLink round trip)", ms, 0.004))
     buf = acc.clone()
     def nccl():
         dist.all_reduce(buf); buf.mul_(1.0 / G); shadow.copy_(buf)
@@ -81,9 +84,14 @@ def main():
     deltas = comm.delta_buffer(1, D, torch.bfloat16)
     deltas[:, :D].copy_((torch.randn(1, D, device=dev) * 0.01).bfloat16())
     ms = timed(lambda: comm.gram(deltas, G), dev)
+    def gram10():
+        for _ in range(10):
+            comm.gram(deltas, G)
+    ms10 = timed(gram10, dev, iters=5) / 10
     remote = G * D * (G - 1) / (G * G) * 2                               # remote bytes read per GPU
     local_hbm = G * D / G * 2 / 6555e9 * 1e3
-    rows.append((f"cosine_gram {G} peers (bf16, all-gather fused)", ms, max(remote / LINK * 1e3, local_hbm)))
+    rows.append((f"cosine_gram {G} peers (bf16, all-gather fused, single launch incl. N x N reduce)", ms, max(remote / LINK * 1e3, local_hbm)))
+    rows.append((f"cosine_gram {G} peers, per call over 10 back-to-back (no inter-rank launch skew)", ms10, max(remote / LINK * 1e3, local_hbm)))
     gl = [torch.empty_like(deltas) for _ in range(G)]
     def nccl_gram():
         dist.all_gather(gl, deltas)

@@ -20,8 +20,8 @@ static inline int stream_grid(size_t work_items, int threads, int per_sm = 8) {
 __global__ void __launch_bounds__(256) adamw_flat_kernel(float* __restrict__ p, float* __restrict__ g,
                                                          float* __restrict__ m, float* __restrict__ v,
                                                          __nv_bfloat16* __restrict__ shadow, size_t n4, size_t n,
-                                                         float step_size, float b1, float b2, float eps,
-                                                         float lr_wd, float gscale, int zero_grad) {
+                                                         float step_size, float b1, float b2, float omb1, float omb2,
+                                                         float eps, float lr_wd, float gscale, int zero_grad) {
     pdl_sync();
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
@@ -33,8 +33,8 @@ __global__ void __launch_bounds__(256) adamw_flat_kernel(float* __restrict__ p, 
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
             const float gr = ge[k] * gscale;
-            me[k] = b1 * me[k] + (1.0f - b1) * gr;
-            ve[k] = b2 * ve[k] + (1.0f - b2) * gr * gr;
+            me[k] = b1 * me[k] + omb1 * gr;                        // omb = 1 - beta evaluated in double on the host, as
+            ve[k] = b2 * ve[k] + omb2 * gr * gr;                   // HF's `value=1.0 - beta2` is (1.0f - 0.999f is 4.7e-5 off)
             pe[k] -= step_size * me[k] / (sqrtf(ve[k]) + eps);     // eps outside the bias correction (HF AdamW)
             pe[k] -= lr_wd * pe[k];
         }
@@ -52,8 +52,8 @@ __global__ void __launch_bounds__(256) adamw_flat_kernel(float* __restrict__ p, 
     // scalar tail (n not a multiple of 4)
     for (size_t i = n4 * 4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const float gr = g[i] * gscale;
-        float mm = b1 * m[i] + (1.0f - b1) * gr;
-        float vv = b2 * v[i] + (1.0f - b2) * gr * gr;
+        float mm = b1 * m[i] + omb1 * gr;
+        float vv = b2 * v[i] + omb2 * gr * gr;
         float pp = p[i] - step_size * mm / (sqrtf(vv) + eps);
         pp -= lr_wd * pp;
         p[i] = pp; m[i] = mm; v[i] = vv;
@@ -182,7 +182,8 @@ extern "C" int fedb200_adamw_flat(float* p, float* g, float* m, float* v, void* 
     const float step_size = (float)((double)lr * sqrt(bc2) / bc1);
     const size_t n4 = n / 4;
     FEDB_CHECK(launch_pdl(adamw_flat_kernel, dim3(stream_grid(n4 ? n4 : 1, 256, 8)), dim3(256), 0, (cudaStream_t)stream, 
-        p, g, m, v, (__nv_bfloat16*)shadow_bf16, n4, n, step_size, beta1, beta2, eps, lr * weight_decay, grad_scale,
+        p, g, m, v, (__nv_bfloat16*)shadow_bf16, n4, n, step_size, beta1, beta2, (float)(1.0 - (double)beta1),
+        (float)(1.0 - (double)beta2), eps, lr * weight_decay, grad_scale,
         zero_grad));
     return 0;
 }

@@ -69,11 +69,18 @@ __device__ __forceinline__ void sha_finish(uint32_t (&s)[8], uint32_t (&tail)[16
 
 constexpr int SHA_CHUNKS_PER_CTA = 128;
 
+// BLK = 64-byte message blocks fetched per chunk and step.  BLK = 2 (chunk_bytes % 128 == 0) makes 8 neighbouring lanes
+// load — and, for the fused send, store — 128 contiguous bytes: full cache lines over NVLink instead of 64-byte fragments,
+// whose packet overhead capped the fused send well below the link rate.  BLK = 1 serves the other chunk sizes.
+template <int BLK>
 __global__ void __launch_bounds__(SHA_CHUNKS_PER_CTA) sha256_leaves_kernel(const uint32_t* __restrict__ src,
                                                                            uint32_t* __restrict__ dst, size_t nbytes,
                                                                            uint32_t chunk_bytes, uint32_t n_chunks,
                                                                            uint32_t* __restrict__ leaves) {
-    __shared__ uint32_t tile[2][SHA_CHUNKS_PER_CTA][17];
+    constexpr int ROW = 16 * BLK + 1;                    // words per chunk row in the tile (+1: conflict-free column reads)
+    constexpr int NV = 4 * BLK;                          // 16-byte vectors per thread and step
+    constexpr int LPC = 4 * BLK;                         // lanes that cover one chunk's step bytes
+    __shared__ uint32_t tile[2][SHA_CHUNKS_PER_CTA][ROW];
     const uint32_t t = threadIdx.x;
     const size_t chunk0 = (size_t)blockIdx.x * SHA_CHUNKS_PER_CTA;
     const size_t my_chunk = chunk0 + t;
@@ -83,7 +90,7 @@ __global__ void __launch_bounds__(SHA_CHUNKS_PER_CTA) sha256_leaves_kernel(const
         my_len = nbytes - off < chunk_bytes ? nbytes - off : chunk_bytes;
     }
     const uint32_t full_blocks = (uint32_t)(my_len / 64), rem_words = (uint32_t)((my_len % 64) / 4);
-    const uint32_t steps = chunk_bytes / 64;
+    const uint32_t steps = chunk_bytes / (64 * BLK);
     const size_t nwords = nbytes / 4;
 
     uint32_t st[8];
@@ -92,19 +99,19 @@ __global__ void __launch_bounds__(SHA_CHUNKS_PER_CTA) sha256_leaves_kernel(const
 #pragma unroll
     for (int i = 0; i < 16; ++i) tail[i] = 0u;
 
-    // Loads of message block `step + 1` are issued before the 64 compression rounds of block `step` and consumed after
-    // them; the copy to `dst` (peer memory over NVLink for the fused hash + send) is issued one iteration later, from the
-    // registers that are already there.  Round 1 stored right behind each load, which made every thread wait for its
-    // load before hashing (push and hash serialised: 1.22 ms = 0.60 hash + 0.56 push); now the stores are
-    // fire-and-forget work between two compressions.
-    uint4 pre[4];
+    // Loads of step + 1 are issued before the compression rounds of step and consumed after them; the copy to `dst`
+    // (peer memory over NVLink for the fused hash + send) is issued one iteration later, from the registers that are
+    // already there.  Round 1 stored right behind each load, which made every thread wait for its load before hashing
+    // (push and hash serialised: 1.22 ms = 0.60 hash + 0.56 push); now the stores are fire-and-forget work between
+    // two compressions.
+    uint4 pre[NV];
     auto word_of = [&](uint32_t step, int i) -> size_t {
         const uint32_t p = t + SHA_CHUNKS_PER_CTA * i;
-        return ((chunk0 + (p >> 2)) * (size_t)chunk_bytes + (size_t)step * 64 + (p & 3) * 16) / 4;
+        return ((chunk0 + p / LPC) * (size_t)chunk_bytes + (size_t)step * (64 * BLK) + (p % LPC) * 16) / 4;
     };
     auto fetch = [&](uint32_t step) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
+        for (int i = 0; i < NV; ++i) {
             const size_t word = word_of(step, i);
             uint4 v = make_uint4(0u, 0u, 0u, 0u);
             if (word + 4 <= nwords) {
@@ -119,7 +126,7 @@ __global__ void __launch_bounds__(SHA_CHUNKS_PER_CTA) sha256_leaves_kernel(const
     };
     auto push = [&](uint32_t step) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
+        for (int i = 0; i < NV; ++i) {
             const size_t word = word_of(step, i);
             if (word + 4 <= nwords) {
                 __stcs(reinterpret_cast<uint4*>(dst + word), pre[i]);
@@ -135,21 +142,25 @@ __global__ void __launch_bounds__(SHA_CHUNKS_PER_CTA) sha256_leaves_kernel(const
         const int buf = step & 1;
         if (dst) push(step);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
+        for (int i = 0; i < NV; ++i) {
             const uint32_t p = t + SHA_CHUNKS_PER_CTA * i;
-            uint32_t* row = &tile[buf][p >> 2][(p & 3) * 4];
+            uint32_t* row = &tile[buf][p / LPC][(p % LPC) * 4];
             row[0] = pre[i].x; row[1] = pre[i].y; row[2] = pre[i].z; row[3] = pre[i].w;
         }
         __syncthreads();
         if (step + 1 < steps) fetch(step + 1);
-        if (step < full_blocks) {
-            uint32_t w[16];
 #pragma unroll
-            for (int i = 0; i < 16; ++i) w[i] = bswap(tile[buf][t][i]);
-            sha_compress(st, w);
-        } else if (step == full_blocks && rem_words != 0) {
+        for (int b = 0; b < BLK; ++b) {
+            const uint32_t blk = step * BLK + b;
+            if (blk < full_blocks) {
+                uint32_t w[16];
 #pragma unroll
-            for (int i = 0; i < 16; ++i) tail[i] = bswap(tile[buf][t][i]);
+                for (int i = 0; i < 16; ++i) w[i] = bswap(tile[buf][t][b * 16 + i]);
+                sha_compress(st, w);
+            } else if (blk == full_blocks && rem_words != 0) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) tail[i] = bswap(tile[buf][t][b * 16 + i]);
+            }
         }
     }
     if (my_chunk < n_chunks) {
@@ -233,8 +244,12 @@ extern "C" int fedb200_sha256_leaves(const void* src, void* dst, size_t nbytes, 
     const size_t n_chunks = (nbytes + chunk_bytes - 1) / chunk_bytes;
     FEDB_REQUIRE(n_chunks < (1ull << 31), "sha256_leaves: too many chunks");
     const unsigned grid = (unsigned)((n_chunks + SHA_CHUNKS_PER_CTA - 1) / SHA_CHUNKS_PER_CTA);
-    sha256_leaves_kernel<<<grid, SHA_CHUNKS_PER_CTA, 0, (cudaStream_t)stream>>>(
-        (const uint32_t*)src, (uint32_t*)dst, nbytes, chunk_bytes, (uint32_t)n_chunks, (uint32_t*)leaves);
+    if (chunk_bytes % 128 == 0)
+        sha256_leaves_kernel<2><<<grid, SHA_CHUNKS_PER_CTA, 0, (cudaStream_t)stream>>>(
+            (const uint32_t*)src, (uint32_t*)dst, nbytes, chunk_bytes, (uint32_t)n_chunks, (uint32_t*)leaves);
+    else
+        sha256_leaves_kernel<1><<<grid, SHA_CHUNKS_PER_CTA, 0, (cudaStream_t)stream>>>(
+            (const uint32_t*)src, (uint32_t*)dst, nbytes, chunk_bytes, (uint32_t)n_chunks, (uint32_t*)leaves);
     FEDB_LAUNCH_CHECK();
     return 0;
 }
@@ -344,7 +359,7 @@ extern "C" int fedb200_sha256_root_static(const void* src, size_t nbytes, unsign
     uint32_t* b = reinterpret_cast<uint32_t*>(scratch + fedb::STATIC_LEAF_BYTES);     // odd levels
     cudaStream_t s = (cudaStream_t)stream;
     const unsigned grid = (unsigned)((n_chunks + SHA_CHUNKS_PER_CTA - 1) / SHA_CHUNKS_PER_CTA);
-    sha256_leaves_kernel<<<grid, SHA_CHUNKS_PER_CTA, 0, s>>>((const uint32_t*)src, nullptr, nbytes, chunk_bytes,
+    sha256_leaves_kernel<1><<<grid, SHA_CHUNKS_PER_CTA, 0, s>>>((const uint32_t*)src, nullptr, nbytes, chunk_bytes,
                                                             (uint32_t)n_chunks, a);
     FEDB_LAUNCH_CHECK();
     unsigned n = (unsigned)n_chunks;
