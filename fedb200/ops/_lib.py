@@ -53,6 +53,9 @@ _PROTOS = {
     "fedb200_gram_fused": (i32, [vp, i32, i32, sz, sz, sz, sz, vp, vp, vp, i32, u32, i32, i32, vp]),
     "fedb200_gram_fused_seg": (i32, [vp, i32, i32, sz, i32, i32, i32, vp, vp, vp, i32, u32, i32, i32, vp]),
     "fedb200_gossip_mix": (i32, [vp, vp, i32, vp, i32, vp, vp, i32, i32, vp, i32, i32, sz, u32, i32, vp]),
+    "fedb200_gossip_mix_async": (i32, [vp, vp, vp, vp, vp, vp, i32, vp, vp, vp, vp, i32, sz, sz, u32, u32, vp, i32, i32, vp]),
+    "fedb200_copy_flagged": (i32, [vp, vp, sz, sz, vp, u32, vp]),
+    "fedb200_set_flags": (i32, [vp, u32, i32, vp]),
     "fedb200_fedavg_reduce_ex": (i32, [vp, vp, vp, vp, i32, i32, sz, f32, f32, u32, i32, i32, i32, vp]),
     "fedb200_peer_exchange": (i32, [vp, vp, i32, i32, i32, u32, i32, vp]),
     "fedb200_peer_barrier": (i32, [vp, i32, i32, u32, i32, vp]),

@@ -68,6 +68,35 @@ def mix_n(srcs: Sequence, weights: Sequence[float], out: torch.Tensor, shadow: O
     count()
 
 
+def _ptr(x) -> int:
+    return x.data_ptr() if isinstance(x, torch.Tensor) else int(x)
+
+
+def gossip_mix_async(self_src: torch.Tensor, out: torch.Tensor, rings: Sequence, chunk_flags: Sequence, pubs: Sequence,
+                     src_peers: Sequence[int], mask: Optional[torch.Tensor], decision: torch.Tensor, log: torch.Tensor,
+                     err, R: int, chunk_elems: int, my_epoch: int, launch_id: int, stale_w: Sequence[float],
+                     max_ctas: int = 0, timeout_ms: int = 20000) -> None:
+    """One asynchronous mix from observed versions (``csrc/gossip.cu::gossip_mix_async_kernel``); pointers may be peer-mapped."""
+    n = len(rings)
+    arr = lambda xs: C.cast((C.c_void_p * max(n, 1))(*[_ptr(x) for x in xs]), C.c_void_p)
+    peers = (C.c_int * max(n, 1))(*[int(p) for p in src_peers])
+    sw = (C.c_float * 32)(*[float(w) for w in stale_w])
+    call("fedb200_gossip_mix_async", _p(self_src), _p(out), arr(rings), arr(chunk_flags), arr(pubs), C.cast(peers, C.c_void_p),
+         n, _p(mask), _p(decision), _p(log), _ptr(err), R, out.numel(), chunk_elems, int(my_epoch), int(launch_id),
+         C.cast(sw, C.c_void_p), max_ctas, timeout_ms, _stream())
+    count()
+
+
+def copy_flagged(src: torch.Tensor, dst, chunk_elems: int, flags, value: int) -> None:
+    call("fedb200_copy_flagged", _p(src), _ptr(dst), src.numel(), chunk_elems, _ptr(flags), int(value), _stream())
+    count()
+
+
+def set_flags(flags, value: int, n: int) -> None:
+    call("fedb200_set_flags", _ptr(flags), int(value), n, _stream())
+    count()
+
+
 def colsum_bf16(x: torch.Tensor, out: torch.Tensor) -> None:
     _chk(x, torch.bfloat16, "x")
     _chk(out, torch.float32, "out")

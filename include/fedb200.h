@@ -218,6 +218,23 @@ int fedb200_gossip_mix(const float* const* srcs, const float* weights, int n_src
                        const float* const* relay_srcs, float* const* relay_dsts, int n_relay, int any_relay,
                        unsigned int* const* flag_ptrs, int rank, int world, size_t n, unsigned int epoch, int timeout_ms,
                        void* stream);
+/* K3. One asynchronous, staleness-weighted mix from OBSERVED versions, applied chunk by chunk as the peers' publishes land:
+ * w_i <- (1 - sum a_j) w_i + sum a_j w_j(v_j), a_j = stale_w[e_i - v_j] / n_live.  rings / chunk_flags / pubs: per source, the
+ * (peer-mapped) outbox ring [R][D], its chunk flags [R][n_chunks] and its publish-started version word; the first CTA fixes
+ * the versions (whatever the pub words hold: nobody waits for a peer to reach an epoch) and writes them to log[0 .. n_src),
+ * log[n_src] counts chunks whose producer lapped the reader (must stay 0); mask (device int32 [num_peers] or NULL) zeroes
+ * eliminated peers; decision: >= 2 + n_src zeroed local words, launch_id increasing by 1 per launch; stale_w: HOST float[32].
+ * Formula only in the reference: Medical_Transcriptions_All_graphs.ipynb:979-980, 997-999. */
+int fedb200_gossip_mix_async(const float* self_src, float* out, const float* const* rings,
+                             const unsigned int* const* chunk_flags, const unsigned int* const* pubs, const int* src_peers,
+                             int n_src, const int* mask, unsigned int* decision, unsigned int* log, unsigned int* err, int R,
+                             size_t D, size_t chunk_elems, unsigned int my_epoch, unsigned int launch_id,
+                             const float* stale_w, int max_ctas, int timeout_ms, void* stream);
+/* Publish copy for K3: CTA c copies chunk c of src into dst (an outbox slot, local or peer-mapped) and releases flags[c] = value. */
+int fedb200_copy_flagged(const float* src, float* dst, size_t n, size_t chunk_elems, unsigned int* flags, unsigned int value,
+                         void* stream);
+/* flags[0 .. n) = value with a system-scope release (marks a slot written by another kernel, e.g. the fused hash + copy). */
+int fedb200_set_flags(unsigned int* flags, unsigned int value, int n, void* stream);
 /* Device-side barrier across ranks (flag words in peer memory), usable between any two kernels. */
 int fedb200_peer_barrier(unsigned int* const* flag_ptrs, int rank, int world, unsigned int epoch, int timeout_ms,
                          void* stream);
