@@ -109,6 +109,14 @@ class FedConfig:
     async_epoch_s: float = 0.05        # modelled local-epoch duration of the schedule's virtual clock
     async_spread: float = 0.5          # peer heterogeneity of the modelled durations
     async_fanout: Optional[int] = None # destinations per publish (None = every reachable peer)
+    # multi-GPU asynchronous executor: "observed" = every mix takes whatever versions its sources have published by then
+    # (device-side decision, chunk flags, no schedule, nobody waits for a peer); "scheduled" = the deterministic virtual-time
+    # schedule of round 1 (modelled epoch durations)
+    async_mode: str = "auto"           # auto: observed across GPUs, the virtual-time event engine in one process
+    async_fanin: int = 4               # sources per mix in observed mode (bounded fan-in: a mix reads <= 4 remote models)
+    async_ring: int = 3                # outbox versions kept per peer (slot = version % ring)
+    async_chunk_kb: int = 4096         # landing-flag granularity of a publish (KB)
+    async_score_every: int = 0         # observed mode + cosine_pagerank: re-score every K epochs (0 = never)
     async_time: str = "measured"       # single-process engine clock: measured epoch durations | modelled (async_epoch_s, async_spread)
     async_min_latency_s: float = 0.0   # visibility lag of a publish in the schedule's virtual time (see AsyncGossipEngine)
     topology: str = "full"             # full | ring | reference10 | random
@@ -163,6 +171,10 @@ def build_parser(defaults: Optional[FedConfig] = None, description: str = "") ->
     p.add_argument("--async", dest="asynchronous", action="store_true", default=d.asynchronous)
     p.add_argument("--async-scheduled", action="store_true", default=d.async_scheduled)
     p.add_argument("--async-fanout", type=int, default=d.async_fanout)
+    p.add_argument("--async-mode", default=d.async_mode, choices=["auto", "observed", "scheduled", "engine"])
+    p.add_argument("--async-fanin", type=int, default=d.async_fanin)
+    p.add_argument("--async-ring", type=int, default=d.async_ring)
+    p.add_argument("--async-score-every", type=int, default=d.async_score_every)
     p.add_argument("--async-epoch-s", type=float, default=d.async_epoch_s)
     p.add_argument("--async-min-latency-s", type=float, default=d.async_min_latency_s)
     p.add_argument("--async-time", default=d.async_time, choices=["measured", "modelled"])
@@ -219,6 +231,8 @@ def config_from_args(args: argparse.Namespace, defaults: Optional[FedConfig] = N
     cfg.serverless_semantics, cfg.asynchronous = args.semantics, args.asynchronous
     cfg.async_scheduled, cfg.async_fanout, cfg.async_epoch_s = args.async_scheduled, args.async_fanout, args.async_epoch_s
     cfg.async_min_latency_s, cfg.async_time = args.async_min_latency_s, args.async_time
+    cfg.async_mode, cfg.async_fanin, cfg.async_ring = args.async_mode, args.async_fanin, args.async_ring
+    cfg.async_score_every = args.async_score_every
     cfg.topology, cfg.route_optimizer = args.topology, args.route_optimizer
     cfg.anomaly_detector, cfg.inject_anomalies, cfg.inject_kind = (
         args.anomaly_detector, args.inject_anomalies, args.inject_kind)

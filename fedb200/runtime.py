@@ -635,8 +635,11 @@ class FedRuntime:
         return res
 
     def run_async(self) -> Dict:
-        if self.world != 1 or self.cfg.async_scheduled:
+        if self.cfg.async_scheduled or self.cfg.async_mode == "scheduled":
             return self.run_async_scheduled()
+        if self.cfg.async_mode == "observed" or (self.world != 1 and self.cfg.async_mode != "engine"):
+            from .p2p.observed import run_async_observed
+            return run_async_observed(self)
         cfg = self.cfg
         state = self.comm.alloc("async_state", self.N * self.D).view(self.N, self.D)
         inbox = {}

@@ -192,10 +192,13 @@ def main():
     cfg2.data.population, cfg2.data.train_per_client, cfg2.data.test_per_client = 800, 32, 32
     cfg2.data.max_seq_len, cfg2.data.batch_size = 128, 16
     cfg2.async_epoch_s, cfg2.async_spread = 0.001, 1.0          # short modelled epochs so versions overlap and slots recycle
+    cfg2.async_fanin, cfg2.async_chunk_kb = 3, 256            # several landing flags per publish even for the small model
     rt2 = FedRuntime(cfg2, echo=False, comm=comm)
+    rt2._audit_async = True
     ares = rt2.run()["last"]
     torch.cuda.synchronize()
     comm.check_errors()
+    assert ares["async_mode"] == "observed" and ares["torn_chunks"] == 0
     assert ares["mixes"] == 3 * 2 * world and rt2.ledger.height == ares["mixes"] and rt2.ledger.validate() == -1
     chk = torch.tensor([float(rt2.global_flat.double().sum())], device=dev, dtype=torch.float64)
     lo, hi = chk.clone(), chk.clone()
@@ -208,6 +211,33 @@ def main():
     mine = rt2.async_state[: len(rt2.local_ids)].sum(0)
     dist.all_reduce(mine)
     torch.testing.assert_close(rt2.global_flat, mine / (2 * world), rtol=1e-5, atol=1e-6)
+    # replay: every mix equals the host oracle evaluated on the versions the device kernel OBSERVED and logged
+    from fedb200.p2p.observed import replay_mix
+    pubs = [None] * world
+    dist.all_gather_object(pubs, rt2.async_audit["published"])
+    published = {k: v for d in pubs for k, v in d.items()}
+    cross = 0
+    for r in rt2.async_records:
+        want = replay_mix(rt2.async_audit["trained"][(r["peer"], r["epoch"])], r["versions"], published, r["sources"],
+                          r["epoch"], rt2.async_table)
+        torch.testing.assert_close(rt2.async_audit["published"][(r["peer"], r["epoch"])], want, rtol=1e-5, atol=1e-6)
+        cross += sum(1 for j, v in zip(r["sources"], r["versions"]) if v > 0 and j not in rt2.local_ids)
+    tot = torch.tensor([float(cross)], device=dev)
+    dist.all_reduce(tot)
+    assert tot.item() > 0, "no mix consumed a version published on another GPU"
+    # on-line scoring in asynchronous mode: fused Gram + device PageRank every epoch, mask consumed on the device
+    cfg4 = FedConfig(mode="serverless", num_clients=2 * world, num_rounds=3, device="cuda", backend="fused", comm="peer",
+                     asynchronous=True, topology="full", anomaly_detector="cosine_pagerank", inject_anomalies=1,
+                     inject_kind="signflip", async_score_every=1)
+    cfg4.model = ModelConfig.preset("bert-mini", num_labels=2)
+    cfg4.data.population, cfg4.data.train_per_client, cfg4.data.test_per_client = 800, 32, 32
+    cfg4.data.max_seq_len, cfg4.data.batch_size = 128, 16
+    rt4 = FedRuntime(cfg4, echo=False, comm=comm)
+    a4 = rt4.run()["last"]
+    comm.check_errors()
+    allm = [None] * world
+    dist.all_gather_object(allm, a4["masked"])
+    assert all(m == allm[0] for m in allm), "ranks disagree on the anomaly mask"
     # ---- ring gossip through the runtime: per-peer states, fused mix kernel, executed routes in the ledger ----------------
     cfg3 = FedConfig(mode="serverless", num_clients=2 * world, num_rounds=2, device="cuda", backend="fused", comm="peer",
                      topology="reference10" if 2 * world == 10 else "ring", ledger=True)
@@ -231,7 +261,8 @@ def main():
     dist.all_gather_object(heads, rt3.ledger.head.hex())
     assert len(set(heads)) == 1, "gossip ledgers diverged across ranks"
     if rank == 0:
-        print("MULTIGPU_OK", world, res["global_accuracies"], "async slots", ares["outbox_slots"], "mixes", ares["mixes"])
+        print("MULTIGPU_OK", world, res["global_accuracies"], "async mixes", ares["mixes"], "mean staleness",
+              round(ares["mean_staleness"], 2), "async masked", a4["masked"], "targets", rt4.injector.targets())
     comm.close()
     dist.destroy_process_group()
 

@@ -258,3 +258,24 @@ def test_async_checkpoint_writer_latest_wins_and_all_masked_keeps_model(tmp_path
     rt.comm.weighted_mean(rt.acc, 0.0, rt.global_flat)     # every contributor masked: the global model is kept
     torch.testing.assert_close(rt.global_flat, g)
     rt.close()
+
+
+def test_async_observed_mode_replays_from_logged_versions():
+    """Observed-version asynchronous gossip (CPU twin of the K3 device path): every mix must equal the host replay from the
+    versions it logged, the fan-in is bounded, later epochs mix the sources' latest published versions."""
+    from fedb200.p2p.observed import replay_mix
+    cfg = _cfg(asynchronous=True, async_mode="observed", num_clients=5, num_rounds=3, ledger=True, async_fanin=2,
+               topology="reference10" if False else "full")
+    rt = FedRuntime(cfg, echo=False)
+    rt._audit_async = True
+    out = rt.run()
+    recs, aud, table = rt.async_records, rt.async_audit, rt.async_table
+    rt.close()
+    assert out["last"]["mixes"] == 15 and out["last"]["torn_chunks"] == 0 and out["ledger_height"] == 15
+    assert all(len(r["sources"]) == 2 for r in recs)
+    assert any(v > 0 for r in recs for v in r["versions"])
+    for r in recs:
+        want = replay_mix(aud["trained"][(r["peer"], r["epoch"])], r["versions"], aud["published"], r["sources"],
+                          r["epoch"], table)
+        torch.testing.assert_close(aud["published"][(r["peer"], r["epoch"])], want, rtol=1e-6, atol=1e-7)
+        assert all(0 <= v <= r["epoch"] for v in r["versions"])
