@@ -6,6 +6,7 @@
 // Replaces: the python-loop transformers.AdamW (src/Servercase/server_IID_IMDB.py:109,117) and the host
 // numpy averaging `sum(param)/len(param)` (src/Serverlesscase/serverless_IID_IMDB.py:269).
 #include "common.cuh"
+#include <stdlib.h>
 #include "../include/fedb200.h"
 
 namespace fedb {
@@ -172,6 +173,15 @@ __global__ void __launch_bounds__(256) delta_bf16_kernel(const float* __restrict
 
 using namespace fedb;
 
+// 1 - beta as HF computes it: `value=1.0 - beta2` in Python doubles on the DECIMAL the user wrote (0.999 -> 0.001).  The ABI
+// carries beta as a float (0.999f = 0.99900001287...), so the decimal is recovered through its shortest 7-digit form first;
+// 1.0f - 0.999f, or 1.0 - (double)0.999f, would both be 1.3e-5 (relative) away from the reference's second-moment weight.
+static float one_minus(float beta) {
+    char buf[32];
+    snprintf(buf, sizeof(buf), "%.7g", (double)beta);
+    return (float)(1.0 - strtod(buf, nullptr));
+}
+
 extern "C" int fedb200_adamw_flat(float* p, float* g, float* m, float* v, void* shadow_bf16, size_t n, int step,
                                   float lr, float beta1, float beta2, float eps, float weight_decay,
                                   float grad_scale, int zero_grad, void* stream) {
@@ -182,8 +192,8 @@ extern "C" int fedb200_adamw_flat(float* p, float* g, float* m, float* v, void* 
     const float step_size = (float)((double)lr * sqrt(bc2) / bc1);
     const size_t n4 = n / 4;
     FEDB_CHECK(launch_pdl(adamw_flat_kernel, dim3(stream_grid(n4 ? n4 : 1, 256, 8)), dim3(256), 0, (cudaStream_t)stream, 
-        p, g, m, v, (__nv_bfloat16*)shadow_bf16, n4, n, step_size, beta1, beta2, (float)(1.0 - (double)beta1),
-        (float)(1.0 - (double)beta2), eps, lr * weight_decay, grad_scale,
+        p, g, m, v, (__nv_bfloat16*)shadow_bf16, n4, n, step_size, beta1, beta2, one_minus(beta1),
+        one_minus(beta2), eps, lr * weight_decay, grad_scale,
         zero_grad));
     return 0;
 }
