@@ -56,8 +56,43 @@ static EncodeTiledFn encode_fn() {
     return fn;
 }
 
+static int encode_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems,
+                               uint32_t box_rows, uint32_t box_cols);
+
+// A tensor map is a pure function of (base, rows, cols, ld, box): the trainer issues ~120 GEMMs per step on a fixed set of
+// buffers and only a handful of token counts, so the ~600 driver encodes per step are memoised.  Direct-mapped, 1024
+// entries per host thread; a colliding key simply re-encodes.
+struct TmapKey { const void* base; uint64_t rows, cols, ld; uint32_t br, bc; };
+struct TmapEntry { TmapKey key; CUtensorMap map; bool valid; };
+static thread_local TmapEntry g_tmap_cache[1024];
+static unsigned long long g_tmap_hits = 0, g_tmap_misses = 0;
+
+static inline size_t tmap_slot(const TmapKey& k) {
+    uint64_t h = (uint64_t)(uintptr_t)k.base * 0x9E3779B97F4A7C15ull;
+    h ^= (k.rows + 0x7F4A7C15ull) * 0xC2B2AE3D27D4EB4Full;
+    h ^= (k.cols << 20) ^ (k.ld << 40) ^ ((uint64_t)k.br << 8) ^ k.bc;
+    h ^= h >> 29;
+    return (size_t)(h * 0xBF58476D1CE4E5B9ull >> 54);          // top 10 bits
+}
+
 int make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems,
                       uint32_t box_rows, uint32_t box_cols) {
+    const TmapKey key = {base, rows, cols, ld_elems, box_rows, box_cols};
+    TmapEntry& ent = g_tmap_cache[tmap_slot(key)];
+    if (ent.valid && ent.key.base == base && ent.key.rows == rows && ent.key.cols == cols && ent.key.ld == ld_elems &&
+        ent.key.br == box_rows && ent.key.bc == box_cols) {
+        *out = ent.map;
+        ++g_tmap_hits;
+        return 0;
+    }
+    ++g_tmap_misses;
+    int rc = encode_tmap_bf16_2d(out, base, rows, cols, ld_elems, box_rows, box_cols);
+    if (rc == 0) { ent.key = key; ent.map = *out; ent.valid = true; }
+    return rc;
+}
+
+static int encode_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems,
+                               uint32_t box_rows, uint32_t box_cols) {
     EncodeTiledFn fn = encode_fn();
     FEDB_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
     FEDB_REQUIRE(((uintptr_t)base & 15) == 0 && (ld_elems * 2) % 16 == 0, "TMA needs 16-byte aligned base/stride");
@@ -88,9 +123,17 @@ int make_tmap_bf16_3d(CUtensorMap* out, const void* base, uint64_t d0, uint64_t 
     return 0;
 }
 
+unsigned long long tmap_cache_hits() { return g_tmap_hits; }
+unsigned long long tmap_cache_misses() { return g_tmap_misses; }
+
 }  // namespace fedb
 
 extern "C" const char* fedb200_last_error(void) { return fedb::g_err; }
 extern "C" int fedb200_abi_version(void) { return FEDB200_ABI_VERSION; }
 extern "C" int fedb200_sm_count(void) { return fedb::sm_count(); }
 extern "C" int fedb200_set_pdl(int on) { fedb::g_pdl = on ? 1 : 0; return 0; }
+extern "C" int fedb200_tmap_cache_stats(unsigned long long* hits, unsigned long long* misses) {
+    if (hits) *hits = fedb::tmap_cache_hits();
+    if (misses) *misses = fedb::tmap_cache_misses();
+    return 0;
+}

@@ -34,6 +34,8 @@ int fedb200_abi_version(void);
 int fedb200_sm_count(void);
 /* programmatic dependent launch between this library's kernels (default on; FEDB200_PDL=0 also disables) */
 int fedb200_set_pdl(int on);
+/* TMA tensor maps are memoised per (pointer, shape, box): counters of the per-thread cache (host pointers, may be NULL). */
+int fedb200_tmap_cache_stats(unsigned long long* hits, unsigned long long* misses);
 
 /* ---- flat-arena kernels ------------------------------------------------------------------------------------ */
 /* K13. One pass of HF-semantics AdamW over the whole flat arena (reference: transformers.AdamW python loop,
