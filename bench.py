@@ -97,8 +97,8 @@ def stage_round(rt, rnd, device):
 
     to_dev = lambda b: {k: (v.to(device) if isinstance(v, torch.Tensor) else v) for k, v in b.items()}
 
-    def dev(loader):
-        return [to_dev(collate_packed(loader.dataset, idx)) for idx in loader.batch_indices()]
+    def dev(loader):          # same collation as FusedRunner.train_epochs
+        return [to_dev(collate_packed(loader.dataset, idx, longest_first=True)) for idx in loader.batch_indices()]
 
     def dev_eval(loader):          # evaluation goes through the runner's packing (same as FusedRunner.evaluate)
         micro, sizes = rt.runner.eval_plan(loader)

@@ -25,7 +25,7 @@ if a.full_len:
     from fedb200.data.dataset import TokenDataset
     rng = np.random.default_rng(0)
     ds = TokenDataset.from_sequences([rng.integers(1000, 20000, size=512) for _ in range(32)], rng.integers(0, 2, size=32), 2)
-batch = collate_packed(ds, np.arange(a.batch))
+batch = collate_packed(ds, np.arange(a.batch), longest_first=os.environ.get('FEDB200_SORT', '1') == '1')
 dev_batch = {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in batch.items()}
 print("tokens", batch["num_tokens"], "max_len", batch["max_len"])
 for _ in range(a.warmup):

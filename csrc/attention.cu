@@ -26,7 +26,8 @@
 
 namespace fedb {
 
-constexpr int AT_THREADS = 192;
+constexpr int AT_SOFTMAX_THREADS = 256;      // two threads per q row
+constexpr int AT_THREADS = 64 + AT_SOFTMAX_THREADS;   // warp 0 TMA, warp 1 MMA, warps 2-9 softmax
 constexpr int AT_TILE = 128 * 64 * 2;        // 16 KB: [128 rows x 64 bf16]
 constexpr float LOG2E = 1.4426950408889634f;
 
@@ -53,8 +54,14 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attn_fwd_kernel(const __grid_co
                                                                  const int* __restrict__ cu_seqlens, int T, int H,
                                                                  float scale_log2, uint64_t seed, uint32_t keep_thresh,
                                                                  float inv_keep, int use_dropout,
-                                                                 uint32_t* __restrict__ drop_bits, int bits_stride) {
+                                                                 uint32_t* __restrict__ drop_bits, int bits_stride,
+                                                                 long long* __restrict__ trace) {
+    // trace (diagnostics, normally null): 32 clock64() stamps per CTA written by the first softmax thread
+    long long* tr = trace ? trace + ((size_t)(blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 32 : nullptr;
+    const bool tracer = tr != nullptr && threadIdx.x == 64;
+    if (tracer) { tr[0] = clock64(); unsigned sm; asm volatile("mov.u32 %0, %%smid;" : "=r"(sm)); tr[31] = sm; }
     pdl_sync();
+    if (tracer) tr[1] = clock64();
     const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * 128;
     const int tok0 = cu_seqlens[b], len = cu_seqlens[b + 1] - tok0;
     if (q0 >= len) return;
@@ -68,13 +75,14 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attn_fwd_kernel(const __grid_co
     uint8_t* sP = sV + AT_TILE;              // 2 tiles (kv 0-63 | 64-127)
     __shared__ __align__(8) uint64_t q_full, k_full, v_full, k_empty, v_empty, s_full, p_ready, o_full;
     __shared__ uint32_t tmem_slot;
+    __shared__ float s_xchg[2][2][128];      // [tile parity][column half][row]: row maxima, then (slot 0) the row sums
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tm_qkv);
         mbar_init(&q_full, 1);
         mbar_init(&k_full, 1); mbar_init(&v_full, 1); mbar_init(&k_empty, 1); mbar_init(&v_empty, 1);
-        mbar_init(&s_full, 1); mbar_init(&p_ready, 128); mbar_init(&o_full, 1);
+        mbar_init(&s_full, 1); mbar_init(&p_ready, AT_SOFTMAX_THREADS); mbar_init(&o_full, 1);
         mbar_fence_init();
     }
     if (warp == 1) tmem_alloc(&tmem_slot, 256);
@@ -121,17 +129,9 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attn_fwd_kernel(const __grid_co
         }
         __syncwarp();
         for (int j = 0; j < n_kv; ++j) {
-            mbar_wait(&p_ready, (uint32_t)j & 1u);
-            mbar_wait(&v_full, (uint32_t)j & 1u);
-            tc_fence_after_sync();
-            if (elect_one()) {
-#pragma unroll
-                for (int k = 0; k < 8; ++k)
-                    umma_bf16(tmem_o, desc_kmajor(aP + (k >> 2) * AT_TILE, k & 3), desc_mnmajor(aV, k, 8192), idesc_o, k > 0);
-                umma_commit(&o_full);
-                umma_commit(&v_empty);
-            }
-            __syncwarp();
+            mbar_wait(&p_ready, (uint32_t)j & 1u);            // S(j) has been consumed (and P(j) is in shared memory)
+            // S(j+1) goes first: the softmax warps run their max pass over it while P(j) V(j) executes, so neither the
+            // QK^T nor the PV latency sits on their critical path any more
             if (j + 1 < n_kv) {
                 mbar_wait(&k_full, (uint32_t)(j + 1) & 1u);
                 tc_fence_after_sync();
@@ -143,31 +143,68 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attn_fwd_kernel(const __grid_co
                 }
                 __syncwarp();
             }
+            mbar_wait(&v_full, (uint32_t)j & 1u);
+            tc_fence_after_sync();
+            if (elect_one()) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    umma_bf16(tmem_o, desc_kmajor(aP + (k >> 2) * AT_TILE, k & 3), desc_mnmajor(aV, k, 8192), idesc_o, k > 0);
+                umma_commit(&o_full);
+                umma_commit(&v_empty);
+            }
+            __syncwarp();
         }
     } else {
-        // ---------------- softmax / output warps: one thread per q row ----------------
+        // ---------------- softmax / output warps: TWO threads per q row ----------------
+        // Warps 2-5 take kv columns 0-63 of every S tile, warps 6-9 columns 64-127 (a warp may only touch the TMEM lanes
+        // of its quadrant, warp % 4, so the two threads of a row sit in warps w and w + 4).  The pair exchanges its row
+        // maximum through shared memory once per tile (one named barrier); row sums stay per thread until the end; the
+        // running output is split the same way (head-dim columns 0-31 | 32-63).  Round 1 had ONE thread per row: 8 softmax
+        // warps per SM (two CTAs), i.e. two per scheduler, each a long dependent chain — the kernel was issue-latency
+        // bound at 10.7 % tensor-pipe utilisation.
         const int quad = warp & 3;
+        const int half = (warp - 2) >> 2;                     // 0: kv columns 0-63 / d columns 0-31, 1: the rest
         const int r = quad * 32 + lane;                       // row within the q tile == TMEM lane
         const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
         const int q_tok = tok0 + q0 + r;
         const bool q_ok = q0 + r < len;
         const uint32_t drop_row = (uint32_t)(h * T + q_tok);
         const uint32_t drop_key = dropout_key(seed);
-        float o[64];
+        const float log2_inv_keep = use_dropout ? log2f(inv_keep) : 0.f;
+        const bool keep_all = keep_thresh >= 65536u;                  // p == 0 through the dropout path
+        const uint32_t thr_hi = keep_thresh << 16;                    // lane < thresh16  <=>  (lane << 16) < (thresh16 << 16)
+        float o[32];
 #pragma unroll
-        for (int d = 0; d < 64; ++d) o[d] = 0.f;
-        float m_run = -INFINITY, l_run = 0.f;
+        for (int d = 0; d < 32; ++d) o[d] = 0.f;
+        float m_run = -INFINITY, l_part = 0.f, alpha_prev = 1.f;
+        uint8_t* tile = sP + half * AT_TILE;                  // this thread's 64 kv columns are exactly one P tile
+        // running output <- running output * alpha + P(jj) V(jj) (this thread's 32 head-dim columns); also the point after which
+        // the P buffer may be overwritten (the PV product has been read out of shared memory)
+        auto fold_o = [&](int jj, float a) {
+            mbar_wait(&o_full, (uint32_t)jj & 1u);
+            tc_fence_after_sync();
+            if (tracer) tr[6 + 5 * jj] = clock64();
+            uint32_t raw[32];
+            tmem_ld_32x32(tmem_o + lane_addr + half * 32, raw);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = o[i] * a + __uint_as_float(raw[i]);
+            tc_fence_before_sync();
+            if (tracer) tr[7 + 5 * jj] = clock64();
+        };
+        if (tracer) tr[2] = clock64();
         for (int j = 0; j < n_kv; ++j) {
             mbar_wait(&s_full, (uint32_t)j & 1u);
             tc_fence_after_sync();
-            const int kv_valid = min(128, len - j * 128);
-            const bool full = kv_valid == 128;            // interior kv tile: no per-element masking (warp-uniform)
-            // pass 1: row max
+            if (tracer) tr[3 + 5 * j] = clock64();
+            const int kv_valid = min(128, len - j * 128) - half * 64;      // valid columns among this thread's 64
+            const bool full = kv_valid >= 64;             // interior: no per-element masking (warp-uniform)
+            // pass 1: maximum over this thread's 64 columns
             float mx = -INFINITY;
 #pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
+            for (int c = 0; c < 2; ++c) {
                 uint32_t raw[32];
-                tmem_ld_32x32(tmem_s + lane_addr + c * 32, raw);
+                tmem_ld_32x32(tmem_s + lane_addr + half * 64 + c * 32, raw);
                 tmem_ld_wait();
                 if (full) {
 #pragma unroll
@@ -178,72 +215,90 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attn_fwd_kernel(const __grid_co
                         if (c * 32 + i < kv_valid) mx = fmaxf(mx, __uint_as_float(raw[i]));
                 }
             }
+            s_xchg[j & 1][half][r] = mx;
+            asm volatile("bar.sync 1, %0;" ::"n"(AT_SOFTMAX_THREADS) : "memory");
+            mx = fmaxf(mx, s_xchg[j & 1][half ^ 1][r]);
+            if (tracer) tr[4 + 5 * j] = clock64();
             const float m_new = fmaxf(m_run, mx * scale_log2);
             const float alpha = exp2f(m_run - m_new);
-            l_run *= alpha;
-            // pass 2: probabilities -> smem (bf16, swizzled K-major), row sum
+            const float m_eff = m_new - log2_inv_keep;
+            l_part *= alpha;
+            if (j > 0) fold_o(j - 1, alpha_prev);            // P(j-1) V(j-1) finished while the max pass above ran
+            alpha_prev = alpha;
+            // pass 2: probabilities -> smem (bf16, swizzled K-major), partial row sum.  16 columns at a time: with the running
+            // output (32 registers) live, a 32-wide chunk left the compiler no registers to interleave the independent
+            // exp2 / hash chains (the kernel is capped at 96 registers by two 320-thread CTAs per SM)
 #pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
-                uint32_t raw[32];
-                tmem_ld_32x32(tmem_s + lane_addr + c * 32, raw);
-                tmem_ld_wait();
-                float p[32];
-                float rs = 0.f;
-                if (full) {
+            for (int c = 0; c < 2; ++c) {
+                const int chunk = j * 4 + half * 2 + c;                 // 32-column dropout chunk
+                const uint32_t base = use_dropout ? attn_drop_base(drop_key, drop_row, (uint32_t)chunk) : 0u;
+                uint32_t bits = 0u;
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        p[i] = exp2f(fmaf(__uint_as_float(raw[i]), scale_log2, -m_new));
-                        rs += p[i];
+                for (int sub = 0; sub < 2; ++sub) {
+                    uint32_t raw[16];
+                    tmem_ld_32x16(tmem_s + lane_addr + half * 64 + c * 32 + sub * 16, raw);
+                    tmem_ld_wait();
+                    float p[16];
+                    float rs = 0.f;
+                    // with dropout the survivors' scale 1/(1-p) is folded into the exponent (m_eff = m - log2(1/(1-p))): every
+                    // p[i], and so the row sum, carries that factor; it cancels in O / l and is subtracted from lse at the end
+                    if (full) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            p[i] = exp2f(fmaf(__uint_as_float(raw[i]), scale_log2, -m_eff));
+                            rs += p[i];
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            p[i] = (c * 32 + sub * 16 + i < kv_valid) ? exp2f(fmaf(__uint_as_float(raw[i]), scale_log2, -m_eff)) : 0.f;
+                            rs += p[i];
+                        }
                     }
-                } else {
+                    l_part += rs;
+                    if (use_dropout) {
+                        // keep decisions: one full hash per (row, 32-column chunk), a cheap mixing step per column pair
+                        // (common.cuh: attn_drop_*); they are also packed into one word that the backward re-reads
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        p[i] = (c * 32 + i < kv_valid) ? exp2f(fmaf(__uint_as_float(raw[i]), scale_log2, -m_new)) : 0.f;
-                        rs += p[i];
+                        for (int k = 0; k < 8; ++k) {
+                            const int kk = sub * 8 + k;
+                            const uint32_t w = attn_drop_word(base, (uint32_t)kk);
+                            const bool keep_lo = (w << 16) < thr_hi || keep_all;     // (w & 0xFFFF) < thresh16
+                            const bool keep_hi = w < thr_hi || keep_all;             // (w >> 16)   < thresh16
+                            if (keep_lo) bits |= 1u << (2 * kk); else p[2 * k] = 0.f;
+                            if (keep_hi) bits |= 2u << (2 * kk); else p[2 * k + 1] = 0.f;
+                        }
                     }
-                }
-                l_run += rs;
-                if (use_dropout) {
-                    // 32 keep decisions of this row as one word; the backward re-reads the word instead of re-hashing
-                    const uint32_t bits = dropout_bits32(drop_key, drop_row, (uint32_t)(j * 128 + c * 32), keep_thresh);
-                    if (drop_bits != nullptr && q_ok && j * 4 + c < bits_stride)      // chunks past max_seqlen are fully masked
-                        drop_bits[((size_t)h * T + q_tok) * bits_stride + j * 4 + c] = bits;
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) p[i] = (bits >> i) & 1u ? p[i] * inv_keep : 0.f;
+                    for (int g = 0; g < 2; ++g) st_swizzled_chunk(tile, r, c * 4 + sub * 2 + g, p + g * 8);
                 }
-                uint8_t* tile = sP + (c >> 1) * AT_TILE;
-#pragma unroll
-                for (int g = 0; g < 4; ++g) st_swizzled_chunk(tile, r, (c & 1) * 4 + g, p + g * 8);
+                if (use_dropout && drop_bits != nullptr && q_ok && chunk < bits_stride)      // chunks past max_seqlen are fully masked
+                    drop_bits[((size_t)h * T + q_tok) * bits_stride + chunk] = bits;
             }
             fence_async_smem();
             tc_fence_before_sync();
             mbar_arrive(&p_ready);
             m_run = m_new;
-            // fold this block's P V into the running output
-            mbar_wait(&o_full, (uint32_t)j & 1u);
-            tc_fence_after_sync();
-#pragma unroll
-            for (int c = 0; c < 2; ++c) {
-                uint32_t raw[32];
-                tmem_ld_32x32(tmem_o + lane_addr + c * 32, raw);
-                tmem_ld_wait();
-#pragma unroll
-                for (int i = 0; i < 32; ++i) o[c * 32 + i] = o[c * 32 + i] * alpha + __uint_as_float(raw[i]);
-            }
-            tc_fence_before_sync();
+            if (tracer) tr[5 + 5 * j] = clock64();
         }
+        fold_o(n_kv - 1, alpha_prev);
+        // row sum = both halves' partial sums (both were rescaled by the same alphas)
+        s_xchg[n_kv & 1][half][r] = l_part;
+        asm volatile("bar.sync 1, %0;" ::"n"(AT_SOFTMAX_THREADS) : "memory");
+        const float l_run = l_part + s_xchg[n_kv & 1][half ^ 1][r];
         if (q_ok) {
-            const float inv = 1.f / l_run;
-            __nv_bfloat16* dst = ctx + (size_t)q_tok * H + h * 64;
+            const float inv = (use_dropout ? inv_keep : 1.f) / l_run;      // l_run carries the folded 1/(1-p): true sum = l_run * (1-p)
+            __nv_bfloat16* dst = ctx + (size_t)q_tok * H + h * 64 + half * 32;
 #pragma unroll
-            for (int g = 0; g < 8; ++g) {
+            for (int g = 0; g < 4; ++g) {
                 uint4 pk;
                 pk.x = pack_bf16x2(o[g * 8 + 0] * inv, o[g * 8 + 1] * inv); pk.y = pack_bf16x2(o[g * 8 + 2] * inv, o[g * 8 + 3] * inv);
                 pk.z = pack_bf16x2(o[g * 8 + 4] * inv, o[g * 8 + 5] * inv); pk.w = pack_bf16x2(o[g * 8 + 6] * inv, o[g * 8 + 7] * inv);
                 *reinterpret_cast<uint4*>(dst + g * 8) = pk;
             }
-            lse[(size_t)h * T + q_tok] = m_run + log2f(l_run);
+            if (half == 0) lse[(size_t)h * T + q_tok] = m_run + log2f(l_run) - log2_inv_keep;   // true lse (l carries 1/(1-p))
         }
+        if (tracer) { tr[29] = n_kv; tr[30] = clock64(); }
     }
     tc_fence_before_sync();
     __syncthreads();
@@ -466,7 +521,7 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
         const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
         const int kv = kv0 + r;
         const bool kv_ok = kv < len;
-        const uint32_t drop_col = dropout_key(seed) ^ (((uint32_t)kv >> 1) * 0x85EBCA77U);
+        const uint32_t drop_key_b = dropout_key(seed);
         const uint32_t drop_lane = (uint32_t)kv & 1u;
         const uint32_t drop_row0 = (uint32_t)(h * T + tok0);
         const int kv_chunk = kv >> 5;                         // warp-uniform (kv0 and quad*32 are multiples of 32)
@@ -550,7 +605,8 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
                             const uint32_t w = __shfl_sync(0xffffffffu, my_bits, hc * 16 + jq);
                             mk = (w >> lane) & 1u ? inv_keep : 0.f;
                         } else if (DROP == 2) {
-                            mk = dropout_lane(hash32(drop_col ^ ((drop_row0 + (uint32_t)q) * 0x9E3779B1U)), drop_lane, keep_thresh, inv_keep);
+                            mk = dropout_lane(attn_drop_word(attn_drop_base(drop_key_b, drop_row0 + (uint32_t)q, (uint32_t)kv >> 5),
+                                                             ((uint32_t)kv & 31u) >> 1), drop_lane, keep_thresh, inv_keep);
                         }
                         pd[jq] = p * mk;
                         ds[jq] = p * (__uint_as_float(rp[jq]) * mk - delta_q) * scale;
@@ -610,6 +666,8 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
 
 using namespace fedb;
 
+static long long* g_attn_trace = nullptr;
+
 extern "C" int fedb200_attn_fwd(const void* qkv, void* ctx, float* lse, const int* cu_seqlens, int B, int T, int heads,
                                 int max_seqlen, float scale, unsigned long long seed, float dropout_p, void* drop_bits,
                                 void* stream) {
@@ -627,9 +685,13 @@ extern "C" int fedb200_attn_fwd(const void* qkv, void* ctx, float* lse, const in
     dim3 grid((max_seqlen + 127) / 128, heads, B);
     FEDB_CHECK(launch_pdl(attn_fwd_kernel, dim3(grid), dim3(AT_THREADS), smem, (cudaStream_t)stream, 
         tm, (__nv_bfloat16*)ctx, lse, cu_seqlens, T, H, scale * LOG2E, seed, dropout_thresh16(dropout_p),
-        1.0f / (1.0f - dropout_p), dropout_p > 0.f, (uint32_t*)drop_bits, (max_seqlen + 31) / 32));
+        1.0f / (1.0f - dropout_p), dropout_p > 0.f, (uint32_t*)drop_bits, (max_seqlen + 31) / 32, g_attn_trace));
     return 0;
 }
+
+// Diagnostics: when set, every attention-forward CTA writes 32 clock64() stamps (see the kernel) at trace[cta * 32 ...];
+// the buffer must hold ceil(max_seqlen / 128) * heads * B * 32 int64.  NULL switches tracing off.
+extern "C" int fedb200_attn_set_trace(void* trace) { g_attn_trace = (long long*)trace; return 0; }
 
 extern "C" int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dctx, const float* lse, float* delta,
                                 void* dqkv, float* dq_accum, float* dbias_qkv, const int* cu_seqlens, int B, int T,

@@ -70,10 +70,17 @@ def collate_padded(ds: TokenDataset, idx: np.ndarray, pin: bool = False) -> Dict
     return out
 
 
-def collate_packed(ds: TokenDataset, idx: np.ndarray, pin: bool = False) -> Dict[str, torch.Tensor]:
+def collate_packed(ds: TokenDataset, idx: np.ndarray, pin: bool = False, longest_first: bool = False) -> Dict[str, torch.Tensor]:
     """Packed (pad-free) collation for the fused trainer: ``ids/pos/tt`` are ``[T]`` int32 with the
     sequences laid end to end, ``cu_seqlens`` is ``[B+1]``.  Same samples as :func:`collate_padded`, none
-    of the pad tokens."""
+    of the pad tokens.  ``longest_first`` lays the sequences out by decreasing length: the attention kernels launch one
+    CTA per (tile, head, sequence) in sequence order, so the long sequences' CTAs start first and the short ones fill the
+    tail of the grid (a training batch's loss is a mean over sequences, so their order is free)."""
+    idx = np.asarray(idx)
+    perm = None
+    if longest_first and len(idx) > 1:
+        perm = np.argsort(-(ds.offsets[idx + 1] - ds.offsets[idx]), kind="stable")     # packed position -> caller's position
+        idx = idx[perm]
     lens = (ds.offsets[idx + 1] - ds.offsets[idx]).astype(np.int64)
     B, T = len(idx), int(lens.sum())
     cu = np.zeros(B + 1, dtype=np.int32)
@@ -88,6 +95,9 @@ def collate_packed(ds: TokenDataset, idx: np.ndarray, pin: bool = False) -> Dict
            "cu_seqlens": torch.from_numpy(cu), "labels": torch.from_numpy(ds.labels[idx].astype(np.int32))}
     if pin and torch.cuda.is_available():
         out = {k: v.pin_memory() for k, v in out.items()}
+    if perm is not None:
+        pt = torch.from_numpy(perm.astype(np.int64))
+        out["perm"] = pt.pin_memory() if (pin and torch.cuda.is_available()) else pt
     out["max_len"] = int(lens.max()) if B else 0
     out["num_tokens"] = T
     return out

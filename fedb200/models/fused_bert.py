@@ -458,7 +458,7 @@ class FusedRunner:
         loss, n = None, 0
         for _ in range(epochs):
             for idx in loader.batch_indices():
-                loss = self.train_step(collate_packed(loader.dataset, idx))
+                loss = self.train_step(collate_packed(loader.dataset, idx, longest_first=True))
                 n += 1
         if lazy:
             return {"loss": loss if loss is not None else torch.full((), float("nan"), device=self.device), "steps": n}
@@ -476,12 +476,12 @@ class FusedRunner:
             for i in idx:
                 n = int(lens[i])
                 if cur and (cur_tok + n > self.max_tokens or len(cur) >= self.max_batch):
-                    micro.append(collate_packed(loader.dataset, np.asarray(cur)))
+                    micro.append(collate_packed(loader.dataset, np.asarray(cur), longest_first=True))
                     cur, cur_tok = [], 0
                 cur.append(int(i))
                 cur_tok += n
         if cur:
-            micro.append(collate_packed(loader.dataset, np.asarray(cur)))
+            micro.append(collate_packed(loader.dataset, np.asarray(cur), longest_first=True))
         return micro, [len(i) for i in ref]
 
     def evaluate_packed(self, micro, ref_sizes) -> Tuple[torch.Tensor, torch.Tensor]:
@@ -491,7 +491,12 @@ class FusedRunner:
         for mb in micro:
             T, B, max_len = self._upload(mb)
             self._forward(T, B, max_len, train=False)
-            losses.append(self.loss_vec[:B].clone())
+            lv = self.loss_vec[:B].clone()
+            if mb.get("perm") is not None:                # packed longest-first: back to the loader's sample order
+                back = torch.empty_like(lv)
+                back[mb["perm"].to(self.device, non_blocking=True)] = lv
+                lv = back
+            losses.append(lv)
             correct += (self.pred[:B] == self.d_labels[:B]).sum()
         per_sample = torch.cat(losses)
         loss_sum = torch.zeros((), device=self.device)

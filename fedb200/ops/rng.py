@@ -48,3 +48,34 @@ def dropout_scale(seed: int, n_rows: int, n_cols: int, p: float, row0: int = 0, 
     cols = (np.arange(n_cols, dtype=np.uint64) + np.uint64(col0))[None, :]
     keep = dropout_keep(seed, rows, cols, p)
     return keep.astype(np.float32) / np.float32(1.0 - p)
+
+
+# ---- attention-probability dropout: one full hash per (row, 32-column chunk), a multiply-xorshift per column pair -------
+# (csrc/common.cuh: attn_drop_base / attn_drop_word).  The attention forward is instruction-issue bound and the two-multiply
+# hash per column pair was a third of its instructions; the chunk base keeps rows / chunks independent, the cheap per-pair
+# step only has to decorrelate 16 Weyl-spaced inputs.
+def attn_drop_base(seed: int, rows: np.ndarray, chunks: np.ndarray) -> np.ndarray:
+    r = np.asarray(rows, dtype=np.uint64)
+    c = np.asarray(chunks, dtype=np.uint64)
+    return hash32(np.uint64(dropout_key(seed)) ^ _mul32(r, 0x9E3779B1) ^ _mul32(c, 0x85EBCA77))
+
+
+def attn_drop_word(base: np.ndarray, pair: np.ndarray) -> np.ndarray:
+    x = (base.astype(np.uint64) + _mul32(np.asarray(pair, dtype=np.uint64), 0x9E3779B9)) & _U32
+    x ^= x >> np.uint64(16)
+    x = _mul32(x, 0x846CA68B)
+    x ^= x >> np.uint64(15)
+    return x
+
+
+def attn_dropout_keep(seed: int, rows: np.ndarray, cols: np.ndarray, p: float) -> np.ndarray:
+    c = np.asarray(cols, dtype=np.uint64)
+    word = attn_drop_word(attn_drop_base(seed, rows, c >> np.uint64(5)), (c & np.uint64(31)) >> np.uint64(1))
+    lane = (word >> (np.uint64(16) * (c & np.uint64(1)))) & np.uint64(0xFFFF)
+    return lane < np.uint64(thresh16(p))
+
+
+def attn_dropout_scale(seed: int, n_rows: int, n_cols: int, p: float, row0: int = 0, col0: int = 0) -> np.ndarray:
+    rows = (np.arange(n_rows, dtype=np.uint64) + np.uint64(row0))[:, None]
+    cols = (np.arange(n_cols, dtype=np.uint64) + np.uint64(col0))[None, :]
+    return attn_dropout_keep(seed, rows, cols, p).astype(np.float32) / np.float32(1.0 - p)

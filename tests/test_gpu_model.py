@@ -64,7 +64,7 @@ def test_attention_fwd_bwd_no_dropout(cuda_lib, lens, heads):
 
 
 def test_attention_dropout_exact_mask(cuda_lib):
-    from fedb200.ops.rng import dropout_scale
+    from fedb200.ops.rng import attn_dropout_scale as dropout_scale
     ops = _ops()
     torch.manual_seed(1)
     lens, heads, p, seed = [200, 70, 333], 2, 0.1, 4242
