@@ -22,7 +22,9 @@ def main(mode: str, split: str, description: str, argv=None) -> dict:
     cfg = config_from_args(args, d)
     if args.sweep:
         res = run_client_sweep(cfg, [int(x) for x in args.sweep.split(",")], echo=not args.quiet)
-        summary = {n: {"global_accuracies": r["global_accuracies"], "latency_min": r["latency_min"]} for n, r in res.items()}
+        summary = {n: {"global_accuracies": r["global_accuracies"], "latency_min": r["latency_min"],
+                       "memory_usage_gb": r["memory_usage_gb"], "cpu_overhead_pct": r["cpu_overhead_pct"],
+                       "ledger_height": r["ledger_height"]} for n, r in res.items()}
     else:
         res = run_experiment(cfg, echo=not args.quiet)
         summary = {"global_accuracies": res["global_accuracies"], "latency_min": res["latency_min"],
