@@ -312,7 +312,9 @@ static __device__ __align__(256) unsigned char g_static_merkle_scratch[STATIC_SC
 constexpr int STATIC_MAX_DEVICES = 64;
 static unsigned char* g_static_scratch_addr[STATIC_MAX_DEVICES] = {nullptr};
 
-// Device address of the scratch array on the current device (looked up on the first call per device).
+// Device address of the scratch array on the current device (looked up on the first call per device).  The host-side
+// table is filled without a lock: two host threads that race on a device's first call both obtain the same address from
+// cudaGetSymbolAddress and store the same pointer value, so the race is benign (an aligned pointer store is not torn).
 static int static_scratch_for_current_device(unsigned char** out) {
     int dev = -1;
     FEDB_CHECK(cudaGetDevice(&dev));

@@ -125,6 +125,7 @@ class FedConfig:
     inject_anomalies: int = 0
     inject_kind: str = "scale"         # scale | signflip | noise
     ledger: bool = False
+    verify_updates: bool = False       # receivers recompute the Merkle root of an update they consume and compare it with the recorded one
     ledger_chunk_bytes: int = 1 << 20
     # fine-tune from a local HF checkpoint directory (config.json + model.safetensors / pytorch_model.bin [+ vocab.txt]):
     # AutoModelForSequenceClassification.from_pretrained(CHECKPOINT, num_labels=...), server_IID_IMDB.py:142-144
@@ -184,6 +185,7 @@ def build_parser(defaults: Optional[FedConfig] = None, description: str = "") ->
     p.add_argument("--inject-anomalies", type=int, default=d.inject_anomalies)
     p.add_argument("--inject-kind", default=d.inject_kind)
     p.add_argument("--ledger", action="store_true", default=d.ledger)
+    p.add_argument("--verify-updates", action="store_true", default=d.verify_updates)
     p.add_argument("--init-checkpoint", default=d.init_checkpoint,
                    help="local HF checkpoint directory to fine-tune from (from_pretrained equivalent)")
     p.add_argument("--ignore-mismatched-sizes", action="store_true", default=d.ignore_mismatched_sizes)
@@ -237,5 +239,6 @@ def config_from_args(args: argparse.Namespace, defaults: Optional[FedConfig] = N
     cfg.anomaly_detector, cfg.inject_anomalies, cfg.inject_kind = (
         args.anomaly_detector, args.inject_anomalies, args.inject_kind)
     cfg.ledger, cfg.checkpoint_dir, cfg.checkpoint_every = args.ledger, args.checkpoint_dir, args.checkpoint_every
+    cfg.verify_updates = args.verify_updates
     cfg.resume, cfg.metrics_path, cfg.seed = args.resume, args.metrics_path, args.seed
     return cfg

@@ -277,6 +277,14 @@ def merkle_root(leaves: torch.Tensor, scratch: Optional[torch.Tensor] = None, ro
 _SHA_WS = {}
 
 
+def sha256_root_static(src, nbytes: int, chunk_bytes: int, root_out: torch.Tensor) -> None:
+    """Merkle root of ``nbytes`` at ``src`` (tensor or raw, possibly peer-mapped, device pointer) into ``root_out`` (32-byte
+    device tensor) with NO workspace: the library's static device array holds the leaves and levels.  This is the call the
+    receive path uses to check an update it is about to mix against the root its sender recorded — no allocation there."""
+    call("fedb200_sha256_root_static", _ptr(src), int(nbytes), int(chunk_bytes), _p(root_out), _stream())
+    count(2)
+
+
 def sha256_copy_root(src: torch.Tensor, dst: Optional[torch.Tensor], chunk_bytes: int = 4096, to_host: bool = True):
     """Copy ``src`` -> ``dst`` hashing on the way; returns the Merkle root as host bytes (syncs the stream) or, with
     ``to_host=False``, as a fresh 32-byte device tensor (no sync)."""

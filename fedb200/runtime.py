@@ -305,6 +305,30 @@ class FedRuntime:
         plan = RelayPlan(w, self.placement.owner, relays, getattr(self.comm, "relay_slots", 4))
         return plan if plan.any else None
 
+    def _verify_received(self, rb: HostReadback):
+        """Receiver-side check of the ledger claim: recompute the Merkle root of the neighbour rank's published slot — the
+        bytes this rank's aggregate consumed, read over NVLink — and compare it on the device with the root that rank put into
+        the exchanged round record.  Uses the allocation-free entry point (the receive path must not cudaMalloc under the
+        other peers' kernels).  Returns the readback handle of the mismatch count."""
+        from .utils import records as R
+        src_rank = (self.rank + 1) % self.world
+        got = torch.empty(32, dtype=torch.uint8, device=self.device)
+        if self.device.type == "cuda":
+            from .ops import cuda_ops
+            ptr = self.comm.peer_ptr(self.slots[0], src_rank)
+            if (self.nbytes + self.ledger.chunk_bytes - 1) // self.ledger.chunk_bytes <= 131072:     # FEDB200_STATIC_MERKLE_MAX_LEAVES
+                cuda_ops.sha256_root_static(ptr, self.nbytes, self.ledger.chunk_bytes, got)
+            else:       # larger than the static workspace (BERT-large at 4 KiB chunks): cached caller-side workspace instead
+                from .parallel.peer_mem import _RawCuda
+                view = torch.as_tensor(_RawCuda(ptr, self.nbytes), device=self.device).view(torch.float32)
+                got = cuda_ops.sha256_copy_root(view, None, self.ledger.chunk_bytes, to_host=False)
+            self.comm.launches += 2
+        else:
+            from .ledger.merkle import merkle_root
+            got.copy_(torch.frombuffer(bytearray(merkle_root(self.slots[0].numpy().tobytes(), self.ledger.chunk_bytes)), dtype=torch.uint8))
+        want = self.records.table[src_rank, R.R_ROOT:R.R_ROOT + 8].view(torch.uint8)
+        return rb.push((got != want).sum().to(torch.int32).reshape(1))
+
     def _route_of(self, peer: int) -> List[int]:
         """Route recorded in the ledger block of ``peer``'s update.  Gossip topologies: the route that was EXECUTED to the
         peer's slowest mixing neighbour this round (direct, or through the relay GPU the fused mix kernel used).  Full
@@ -483,6 +507,7 @@ class FedRuntime:
                 self.comm.mix_rows(self.slots, rows, self.peer_state, self.N, plan=plan)
                 self._gossip_plan, self._gossip_w = plan, w
         rec.exchange()
+        h_ver = self._verify_received(rb) if (cfg.verify_updates and self.ledger is not None) else None
         with self.timer.phase("evaluate_global"):
             self.runner.load_flat(self.global_flat)
             self.runner.sync_shadow()
@@ -499,6 +524,8 @@ class FedRuntime:
         h_err = rb.push(ew) if ew is not None else None
         rb.sync()                                            # the round's only device -> host synchronisation
         self._raise_on_peer_error(rb, h_err)                 # a timed-out peer barrier fails the round before it is recorded
+        if h_ver is not None and int(rb.get(h_ver).view(-1)[0]) != 0:
+            raise RuntimeError("a received update does not hash to the Merkle root its sender recorded (round not recorded)")
         self.runner.d2h_bytes = getattr(self.runner, "d2h_bytes", 0) + (rb.bytes_read - rb_bytes0)
         allrec = rec.parse(rb.get(h_tab))
         gl = float(rb.get(h_gl)) / g_nds
@@ -776,7 +803,8 @@ class FedRuntime:
             W = self.world
             comm_bytes = int(2 * (W - 1) / W * self.nbytes) if W > 1 else 0
             agg_ms = dev.get("aggregate", 0.0)
-            nvlink_frac = (comm_bytes / 2 / 770e9 * 1e3) / agg_ms if comm_bytes and agg_ms > 0 else None
+            # (None when the aggregate ran on the side stream: the main-stream phase timer then only sees its join)
+            nvlink_frac = (comm_bytes / 2 / 770e9 * 1e3) / agg_ms if comm_bytes and agg_ms > 0.2 else None
             self.log.log("round", round=rnd, wall_s=mx, samples_per_s=tot[0] / mx if mx else None,
                          tokens_per_s=tot[1] / mx if mx else None, phases_ms=dev, model_size_gib=size,
                          comm_bytes_per_rank=comm_bytes, aggregate_nvlink_frac=nvlink_frac,

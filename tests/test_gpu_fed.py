@@ -146,3 +146,27 @@ def test_gram_pagerank_flags_poisoned_update(cuda_lib):
     assert set(bad_host) <= set(np.flatnonzero(mask.cpu().numpy()).tolist())      # host adds the min-gap guard
     assert 3 in bad_host and 6 in bad_host
     np.testing.assert_allclose(ranks.cpu().numpy(), r_host, atol=1e-6)
+
+
+def test_runtime_receiver_verification_uses_static_root(cuda_lib):
+    """--verify-updates on the GPU: the consumer's check runs through fedb200_sha256_root_static (no workspace, no allocation
+    in the receive path); an update altered after it was hashed fails the round."""
+    from fedb200.config import FedConfig, ModelConfig
+    from fedb200.runtime import FedRuntime
+    cfg = FedConfig(mode="serverless", num_clients=1, num_rounds=2, device="cuda", backend="fused", comm="loopback",
+                    ledger=True, verify_updates=True)
+    cfg.model = ModelConfig.preset("bert-mini", num_labels=2)
+    cfg.data.population, cfg.data.train_per_client, cfg.data.test_per_client = 400, 32, 32
+    cfg.data.max_seq_len, cfg.data.batch_size = 128, 16
+    rt = FedRuntime(cfg, echo=False)
+    rt.round_serverless(0)
+    orig = rt._publish
+
+    def tampering_publish(li, lazy=False):
+        root = orig(li, lazy=lazy)
+        rt.slots[li][11] += 1.0
+        return root
+    rt._publish = tampering_publish
+    with pytest.raises(RuntimeError, match="does not hash to the Merkle root"):
+        rt.round_serverless(1)
+    rt.close()

@@ -279,3 +279,21 @@ def test_async_observed_mode_replays_from_logged_versions():
                           r["epoch"], table)
         torch.testing.assert_close(aud["published"][(r["peer"], r["epoch"])], want, rtol=1e-6, atol=1e-7)
         assert all(0 <= v <= r["epoch"] for v in r["versions"])
+
+
+def test_receiver_verifies_published_update_against_recorded_root():
+    """--verify-updates: the consumer recomputes the Merkle root of the slot it aggregates and compares it with the root in the
+    exchanged round record; a slot that was altered after hashing fails the round."""
+    cfg = _cfg(ledger=True, verify_updates=True, num_clients=1, num_rounds=1)
+    rt = FedRuntime(cfg, echo=False)
+    rt.round_serverless(0)                                   # honest: passes
+    orig = rt._publish
+
+    def tampering_publish(li, lazy=False):
+        root = orig(li, lazy=lazy)
+        rt.slots[li][7] += 1.0                               # bytes served differ from the bytes hashed
+        return root
+    rt._publish = tampering_publish
+    with pytest.raises(RuntimeError, match="does not hash to the Merkle root"):
+        rt.round_serverless(1)
+    rt.close()
