@@ -58,9 +58,12 @@ def run(args, make_cfg, ClockSampler, published: float) -> None:
     model = BertForSequenceClassification(hc).to(dev)
     K, W = args.steps, args.warmup
     accs = []
-    # FEDB200_TB_SDPA = default | no_cudnn | flash_efficient : which library SDPA kernels torch may pick (diagnostic knob;
-    # the cuDNN backend builds an execution plan per new (batch, seq) shape, which is slow with pad-to-longest batches)
-    sdpa_mode = os.environ.get("FEDB200_TB_SDPA", "default")
+    # Which library SDPA kernels torch may pick.  Measured on this box (B200, torch 2.11): with torch's default choice the
+    # bf16 arms ran at 52 samples/s — the cuDNN SDPA backend builds an execution plan for every new (batch, seq) shape, and
+    # pad-to-longest batches almost never repeat a shape — against 386 samples/s with that backend disabled (flash /
+    # memory-efficient kernels).  The baseline is meant to be the best stock configuration, so the cuDNN backend is off by
+    # default; FEDB200_TB_SDPA=default restores torch's own choice.
+    sdpa_mode = os.environ.get("FEDB200_TB_SDPA", "no_cudnn")
     if sdpa_mode != "default":
         torch.backends.cuda.enable_cudnn_sdp(False)
     phases = {"train": 0.0, "eval": 0.0, "aggregate": 0.0}
