@@ -2,10 +2,11 @@
 // The reference has no ledger code at all (README.md:10 only names it); this is the device half of
 // fedb200/ledger: every weight update is hashed while it is copied into the peer-visible buffer, so the
 // ledger costs no extra pass over the 433 MB model.
-//   * leaves: the span is cut into `chunk_bytes` chunks (multiple of 64 B); leaf_i = SHA256(chunk_i), one thread
+//   * leaves: the span is cut into `chunk_bytes` chunks (multiple of 64 B); leaf_i = SHA256(chunk_i || 0x00), one thread
 //     per chunk, 128 chunks per CTA staged through shared memory so global traffic stays coalesced
 //     (4 lanes fetch one 64 B message block; the same registers feed the copy to `dst`).
-//   * tree : SHA256(left || right) per level, unpaired node promoted — same rule as ledger/merkle.py.
+//   * tree : SHA256(left || right || 0x01) per level (leaves are SHA256(chunk || 0x00): domain separation), unpaired node
+//     promoted — same rule as ledger/merkle.py.
 // Bit-exact against hashlib (tests/test_gpu_fed.py).
 #include "common.cuh"
 #include "../include/fedb200.h"
@@ -52,10 +53,17 @@ __device__ __forceinline__ void sha_compress(uint32_t (&s)[8], uint32_t (&w)[16]
 }
 
 // final padding for a message of `len_bytes` whose last (len % 64) / 4 words are in tail[]
+// Domain separation of the Merkle tree: a leaf is SHA256(chunk || 0x00), an interior node SHA256(left || right || 0x01), so a
+// 64-byte interior pair can never be passed off as a 64-byte leaf (second-preimage splicing).  The tag is a SUFFIX byte:
+// the data words keep their 64-byte block alignment, which is what lets the leaf hash run inside the copy kernel.
+constexpr uint32_t PAD_LEAF = 0x00800000u;    // tag byte 0x00, then the 0x80 padding byte
+constexpr uint32_t PAD_NODE = 0x01800000u;    // tag byte 0x01, then 0x80
+
 __device__ __forceinline__ void sha_finish(uint32_t (&s)[8], uint32_t (&tail)[16], uint32_t tail_words, uint64_t len_bytes) {
     uint32_t w[16];
+    len_bytes += 1;                            // the leaf tag byte
 #pragma unroll
-    for (int i = 0; i < 16; ++i) w[i] = (uint32_t)i < tail_words ? tail[i] : ((uint32_t)i == tail_words ? 0x80000000u : 0u);
+    for (int i = 0; i < 16; ++i) w[i] = (uint32_t)i < tail_words ? tail[i] : ((uint32_t)i == tail_words ? PAD_LEAF : 0u);
     if (tail_words >= 14) {
         sha_compress(s, w);
 #pragma unroll
@@ -188,8 +196,8 @@ __global__ void __launch_bounds__(128) merkle_level_kernel(const uint32_t* __res
     sha_compress(st, w);
 #pragma unroll
     for (int k = 0; k < 16; ++k) w[k] = 0u;
-    w[0] = 0x80000000u;
-    w[15] = 512u;
+    w[0] = PAD_NODE;
+    w[15] = 520u;                              // (64 + 1 tag byte) * 8 bits
     sha_compress(st, w);
 #pragma unroll
     for (int k = 0; k < 8; ++k) out[i * 8 + k] = bswap(st[k]);

@@ -164,11 +164,13 @@ def test_async_engine_staleness_weights_replay_and_max_vs_sum():
 def test_merkle_root_rules_against_hashlib():
     data = bytes(range(256)) * 10
     leaves = leaf_digests(data, 256)
-    assert len(leaves) == 10 and leaves[0] == hashlib.sha256(data[:256]).digest()
+    assert len(leaves) == 10 and leaves[0] == hashlib.sha256(data[:256] + b"\x00").digest()
     lvl = reduce_level(leaves[:3])
-    assert lvl[0] == hashlib.sha256(leaves[0] + leaves[1]).digest() and lvl[1] == leaves[2]      # promotion
-    assert merkle_root(data[:256], 256) == hashlib.sha256(data[:256]).digest()
+    assert lvl[0] == hashlib.sha256(leaves[0] + leaves[1] + b"\x01").digest() and lvl[1] == leaves[2]      # promotion
+    assert merkle_root(data[:256], 256) == hashlib.sha256(data[:256] + b"\x00").digest()
     assert merkle_root(data, 256) != merkle_root(data[:-1] + b"\x00", 256)
+    # domain separation: the 64-byte concatenation of two leaf digests, presented as ONE leaf, does not hash to their parent
+    assert merkle_root(leaves[0] + leaves[1], 64) != reduce_level(leaves[:2])[0]
 
 
 def test_ledger_chain_validation_and_tamper_detection(tmp_path):
