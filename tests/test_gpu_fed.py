@@ -170,3 +170,125 @@ def test_runtime_receiver_verification_uses_static_root(cuda_lib):
     with pytest.raises(RuntimeError, match="does not hash to the Merkle root"):
         rt.round_serverless(1)
     rt.close()
+
+
+# ---- the fused multi-GPU kernels in their one-rank form (the box that runs `-m gpu` has a single GPU; the 2-8 GPU versions
+# ---- of these checks live in tests/multigpu_worker.py) ----------------------------------------------------------------------
+def _arr(xs):
+    import ctypes as C
+    return C.cast((C.c_void_p * max(len(xs), 1))(*[int(x) for x in xs]), C.c_void_p)
+
+
+def test_fedavg_reduce_one_rank_two_shot_one_shot_and_masked(cuda_lib):
+    lib = cuda_lib
+    stream = torch.cuda.current_stream().cuda_stream
+    flags = torch.zeros(128, dtype=torch.int32, device="cuda")
+    n = 1_000_003
+    x = torch.randn(n, device="cuda")
+    out = torch.zeros(n, device="cuda")
+    sh = torch.zeros(n, dtype=torch.bfloat16, device="cuda")
+    for epoch, (w, ctas) in enumerate([(4.0, 0), (2.0, 8)], start=1):          # full grid, then the small overlapped grid
+        rc = lib.fedb200_fedavg_reduce_ex(_arr([x.data_ptr()]), _arr([out.data_ptr()]), _arr([sh.data_ptr()]), _arr([flags.data_ptr()]),
+                                          0, 1, n, w, 0.0, epoch, 2000, 0, ctas, stream)
+        assert rc == 0, lib.fedb200_last_error().decode()
+        torch.testing.assert_close(out, x / w, rtol=1e-6, atol=1e-7)
+        torch.testing.assert_close(sh.float(), (x / w).bfloat16().float(), rtol=0, atol=0)
+    keep = out.clone()                                                             # weight 0: every contributor masked -> untouched
+    assert lib.fedb200_fedavg_reduce_ex(_arr([x.data_ptr()]), _arr([out.data_ptr()]), None, _arr([flags.data_ptr()]),
+                                        0, 1, n, 0.0, 0.0, 3, 2000, 0, 0, stream) == 0
+    assert torch.equal(out, keep)
+    small, so = torch.randn(4099, device="cuda"), torch.zeros(4099, device="cuda")
+    for epoch in (1, 2):                                                           # one-shot family counts its own epochs
+        assert lib.fedb200_fedavg_reduce_ex(_arr([small.data_ptr()]), _arr([so.data_ptr()]), None, _arr([flags.data_ptr()]),
+                                            0, 1, 4099, 1.0, 0.0, epoch, 2000, 1, 0, stream) == 0
+        torch.testing.assert_close(so, small)
+    tab = torch.arange(48, dtype=torch.int32, device="cuda").view(1, 48).clone()
+    assert lib.fedb200_peer_exchange(_arr([tab.data_ptr()]), _arr([flags.data_ptr()]), 0, 1, 48 * 4, 1, 2000, stream) == 0
+    torch.cuda.synchronize()
+    assert torch.equal(tab.view(-1).cpu(), torch.arange(48, dtype=torch.int32)) and int(flags[18]) == 0
+
+
+def test_gossip_mix_fused_rows_and_relay_copy(cuda_lib):
+    """K2 in one launch: 5 sources -> 3 rows (every source read once), with a relay copy executed first (phase 1 + mid
+    barrier): the row that is routed through the relay must read the relay buffer's copy."""
+    lib = cuda_lib
+    stream = torch.cuda.current_stream().cuda_stream
+    flags = torch.zeros(128, dtype=torch.int32, device="cuda")
+    n = 300_003
+    torch.manual_seed(5)
+    srcs = [torch.randn(n, device="cuda") for _ in range(4)]
+    relay = torch.zeros(n, device="cuda")
+    W = np.ascontiguousarray(np.random.default_rng(0).random((3, 5)).astype(np.float32))
+    outs = [torch.empty(n, device="cuda") for _ in range(3)]
+    all_src = srcs + [relay]                                     # source 4 = the relay buffer, filled by phase 1 from srcs[2]
+    rc = lib.fedb200_gossip_mix(_arr([s.data_ptr() for s in all_src]), W.ctypes.data, 5, _arr([o.data_ptr() for o in outs]), 3,
+                                _arr([srcs[2].data_ptr()]), _arr([relay.data_ptr()]), 1, 1, _arr([flags.data_ptr()]), 0, 1, n, 1, 2000,
+                                stream)
+    assert rc == 0, lib.fedb200_last_error().decode()
+    torch.cuda.synchronize()
+    assert torch.equal(relay, srcs[2])
+    S = torch.stack(srcs + [srcs[2]])
+    want = torch.tensor(W, device="cuda") @ S
+    for r in range(3):
+        torch.testing.assert_close(outs[r], want[r], rtol=1e-5, atol=1e-5)
+    assert int(flags[18]) == 0
+
+
+def test_gossip_mix_async_observed_versions_staleness_mask_and_replay(cuda_lib):
+    """K3 one-rank: three 'peers' publish into their rings with per-chunk landing flags; the mix reads the pub words on the
+    device, logs the versions it chose, discounts by staleness, skips a masked peer and a peer that never published."""
+    from fedb200.p2p.observed import replay_mix, stale_table
+    ops = _ops()
+    n, R, chunk = 1_000_004, 3, 65536
+    nch = (n + chunk - 1) // chunk
+    torch.manual_seed(9)
+    rings = [torch.zeros(R, n, device="cuda") for _ in range(4)]
+    cfl = [torch.zeros(R, nch, dtype=torch.int32, device="cuda") for _ in range(4)]
+    pub = torch.zeros(4, dtype=torch.int32, device="cuda")
+    published = {}
+    for peer, versions in ((0, (1, 2, 3, 4)), (1, (1, 2)), (2, (1,))):           # peer 3 never publishes; version 4 reuses slot 1
+        for v in versions:
+            w = torch.randn(n, device="cuda")
+            published[(peer, v)] = w.cpu()
+            pub[peer] = v
+            ops.copy_flagged(w, rings[peer][v % R], chunk, cfl[peer][v % R], v)
+    mask = torch.tensor([0, 0, 1, 0], dtype=torch.int32, device="cuda")             # peer 2 eliminated by the scorer
+    me, out = torch.randn(n, device="cuda"), torch.empty(n, device="cuda")
+    decision = torch.zeros(16, dtype=torch.int32, device="cuda")
+    log = torch.zeros(8, dtype=torch.int32, device="cuda")
+    err = torch.zeros(4, dtype=torch.int32, device="cuda")
+    table = stale_table(0.5, 0.5)
+    ops.gossip_mix_async(me, out, rings, cfl, [pub[i:i + 1] for i in range(4)], [0, 1, 2, 3], mask, decision, log, err.data_ptr(),
+                         R, chunk, 5, 1, table, timeout_ms=2000)
+    torch.cuda.synchronize()
+    vers = log[:4].cpu().tolist()
+    assert vers == [4, 2, 0, 0] and int(log[4]) == 0 and int(err[0]) == 0          # observed versions, no torn chunk, no timeout
+    want = replay_mix(me.cpu(), vers, published, [0, 1, 2, 3], 5, table)
+    torch.testing.assert_close(out.cpu(), want, rtol=1e-5, atol=1e-6)
+    # second launch on the same decision buffer (launch_id 2), nothing new published: same versions, larger staleness
+    ops.gossip_mix_async(me, out, rings, cfl, [pub[i:i + 1] for i in range(4)], [0, 1, 2, 3], None, decision, log, err.data_ptr(),
+                         R, chunk, 7, 2, table, timeout_ms=2000)
+    torch.cuda.synchronize()
+    assert log[:4].cpu().tolist() == [4, 2, 1, 0]
+    torch.testing.assert_close(out.cpu(), replay_mix(me.cpu(), [4, 2, 1, 0], published, [0, 1, 2, 3], 7, table), rtol=1e-5, atol=1e-6)
+
+
+def test_observed_async_runtime_on_one_gpu(cuda_lib):
+    """The observed-version executor end to end on one GPU (4 peers time-sharing it): kernels, ledger, replay."""
+    from fedb200.config import FedConfig, ModelConfig
+    from fedb200.p2p.observed import replay_mix
+    from fedb200.runtime import FedRuntime
+    cfg = FedConfig(mode="serverless", num_clients=4, num_rounds=3, device="cuda", backend="fused", comm="loopback",
+                    asynchronous=True, async_mode="observed", async_fanin=2, ledger=True, async_chunk_kb=256)
+    cfg.model = ModelConfig.preset("bert-mini", num_labels=2)
+    cfg.data.population, cfg.data.train_per_client, cfg.data.test_per_client = 400, 32, 32
+    cfg.data.max_seq_len, cfg.data.batch_size = 128, 16
+    rt = FedRuntime(cfg, echo=False)
+    rt._audit_async = True
+    out = rt.run()["last"]
+    recs, aud, table = rt.async_records, rt.async_audit, rt.async_table
+    rt.close()
+    assert out["mixes"] == 12 and out["torn_chunks"] == 0 and rt.ledger.height == 12 and rt.ledger.validate() == -1
+    for r in recs:
+        want = replay_mix(aud["trained"][(r["peer"], r["epoch"])], r["versions"], aud["published"], r["sources"], r["epoch"], table)
+        torch.testing.assert_close(aud["published"][(r["peer"], r["epoch"])], want, rtol=1e-5, atol=1e-6)
