@@ -57,3 +57,8 @@ for _ in range(a.steps):
 e1.record()
 torch.cuda.synchronize()
 print(f"eval step: gpu {e0.elapsed_time(e1) / a.steps:.3f} ms")
+
+import ctypes as _C
+_h, _m = _C.c_ulonglong(0), _C.c_ulonglong(0)
+_lib.lib().fedb200_tmap_cache_stats(_C.byref(_h), _C.byref(_m))
+print(f"tensor-map cache: {_h.value} hits, {_m.value} encodes (FEDB200_TMAP_CACHE={os.environ.get('FEDB200_TMAP_CACHE', '1')})")

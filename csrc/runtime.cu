@@ -77,6 +77,8 @@ static inline size_t tmap_slot(const TmapKey& k) {
 
 int make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems,
                       uint32_t box_rows, uint32_t box_cols) {
+    static const bool cache_on = [] { const char* e = getenv("FEDB200_TMAP_CACHE"); return !(e && e[0] == '0'); }();
+    if (!cache_on) { ++g_tmap_misses; return encode_tmap_bf16_2d(out, base, rows, cols, ld_elems, box_rows, box_cols); }
     const TmapKey key = {base, rows, cols, ld_elems, box_rows, box_cols};
     TmapEntry& ent = g_tmap_cache[tmap_slot(key)];
     if (ent.valid && ent.key.base == base && ent.key.rows == rows && ent.key.cols == cols && ent.key.ld == ld_elems &&
