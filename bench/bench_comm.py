@@ -70,6 +70,12 @@ def main():
     rows.append(("fedavg_reduce (fp32 in/out)", ms, bytes_dir / LINK * 1e3))
     ms = timed(lambda: comm.weighted_mean(acc, 1.0, out, max_ctas=32), dev)
     rows.append(("fedavg_reduce (fp32 in/out), 32-CTA grid (the form overlapped with compute)", ms, bytes_dir / LINK * 1e3))
+    if comm.nvls_available():
+        nv_a, nv_o = comm.alloc("b_nv_acc", D, multicast=True), comm.alloc("b_nv_out", D, multicast=True)
+        nv_a.copy_(acc)
+        ms = timed(lambda: comm.weighted_mean(nv_a, 1.0, nv_o, nvls=True), dev)
+        # switch-reduced: a GPU sends its replica of every slice once (D) and receives its reduced slice + everyone's results (D/G + D)
+        rows.append(("fedavg_reduce NVLS (multimem.ld_reduce / multimem.st, fp32 in/out)", ms, (1 + 1 / G) * D * 4 / LINK * 1e3))
     small_a, small_o = comm.alloc("b_small_a", 4096), comm.alloc("b_small_o", 4096)
     def small50():                      # 50 back-to-back calls: a single call's event time is dominated by the launch skew between ranks
         for _ in range(50):

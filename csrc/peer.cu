@@ -103,6 +103,72 @@ __global__ void __launch_bounds__(512) fedavg_reduce_kernel(const PeerTable t, i
     end_barrier(t, fb, rank, world, epoch, deadline);
 }
 
+// NVLS form of the two-shot reduce: the buffers are bound to a multicast object (cuMulticastCreate / BindMem — set up on the
+// host by the symmetric-memory allocator), so ONE `multimem.ld_reduce` on the multicast address returns the sum over every
+// GPU's replica, added inside the NVSwitch, and ONE `multimem.st` writes the result into every GPU's copy.  Each GPU then
+// receives D / world reduced elements instead of (world - 1) x D / world operands and sends its result once instead of
+// world - 1 times: the link carries about half the bytes of the P2P form.  Barriers, weights and the masked / timed-out
+// behaviour are those of fedavg_reduce_kernel (same flag words, same epoch sequence).
+__device__ __forceinline__ float4 multimem_ld_reduce_add(const float* mc) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void multimem_st(float* mc, const float4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                 ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+__global__ void __launch_bounds__(512) fedavg_reduce_nvls_kernel(const PeerTable t, const float* __restrict__ mc_acc,
+                                                                 float* __restrict__ mc_out, int rank, int world, size_t n,
+                                                                 float my_weight, float inv_w_arg, unsigned int epoch,
+                                                                 long long timeout_cycles) {
+    unsigned int* my = t.flags[rank];
+    const long long deadline = clock64() + timeout_cycles;
+    start_barrier(t, FB_TWOSHOT, rank, world, epoch, deadline, 1, my_weight);
+    float inv_w = inv_w_arg;
+    bool skip = false;
+    if (inv_w <= 0.f) {
+        float tot = 0.f;
+        for (int p = 0; p < world; ++p) tot += __uint_as_float(ld_acquire_gpu(my + FLG_WEIGHT + p));
+        skip = !(tot > 0.f);
+        inv_w = skip ? 0.f : 1.f / tot;
+    }
+    if (ld_acquire_gpu(my + FLG_ERROR) != 0u) skip = true;
+    if (!skip) {
+        const size_t n4 = n / 4;
+        const size_t per = (n4 + world - 1) / world;
+        const size_t lo = per * rank, hi = lo + per < n4 ? lo + per : n4;
+        const size_t stride = (size_t)gridDim.x * blockDim.x;
+        size_t i = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+        for (; i + 3 * stride < hi; i += 4 * stride) {                 // four switch reductions in flight per thread
+            float4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) v[u] = multimem_ld_reduce_add(mc_acc + 4 * (i + u * stride));
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                v[u].x *= inv_w; v[u].y *= inv_w; v[u].z *= inv_w; v[u].w *= inv_w;
+                multimem_st(mc_out + 4 * (i + u * stride), v[u]);
+            }
+        }
+        for (; i < hi; i += stride) {
+            float4 v = multimem_ld_reduce_add(mc_acc + 4 * i);
+            v.x *= inv_w; v.y *= inv_w; v.z *= inv_w; v.w *= inv_w;
+            multimem_st(mc_out + 4 * i, v);
+        }
+        if (rank == world - 1) {                                       // scalar tail through the unicast (peer) pointers
+            for (size_t k = n4 * 4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) {
+                float s = 0.f;
+                for (int p = 0; p < world; ++p) s += t.acc[p][k];
+                s *= inv_w;
+                for (int p = 0; p < world; ++p) t.out[p][k] = s;
+            }
+        }
+    }
+    end_barrier(t, FB_TWOSHOT, rank, world, epoch, deadline);
+}
+
 // Slot exchange: every rank owns slot `rank` of a [world, slot_words] table that exists on every rank (symmetric buffer).
 // One small kernel pushes the own slot into every peer's copy and runs a cross-rank barrier, after which every rank holds
 // the whole table locally — the device-side replacement of a host all_gather of per-round metadata (Merkle roots, sample
@@ -218,6 +284,29 @@ extern "C" int fedb200_fedavg_reduce(const float* const* acc_ptrs, float* const*
                                      float inv_total_weight, unsigned int epoch, int timeout_ms, void* stream) {
     return fedb200_fedavg_reduce_ex(acc_ptrs, out_ptrs, shadow_ptrs, flag_ptrs, rank, world, n, my_weight, inv_total_weight,
                                     epoch, timeout_ms, 0, 0, stream);
+}
+
+// NVLS variant.  acc_ptrs / out_ptrs / flag_ptrs as for fedb200_fedavg_reduce_ex (the unicast peer pointers of the same
+// buffers: used for the scalar tail); mc_acc / mc_out: the MULTICAST addresses of the accumulator and output buffers (every
+// rank passes its own mapping of the same multicast object).  Shares the two-shot epoch sequence.
+extern "C" int fedb200_fedavg_reduce_nvls(const float* const* acc_ptrs, float* const* out_ptrs, const float* mc_acc, float* mc_out,
+                                          unsigned int* const* flag_ptrs, int rank, int world, size_t n, float my_weight,
+                                          float inv_total_weight, unsigned int epoch, int timeout_ms, int max_ctas,
+                                          void* stream) {
+    FEDB_REQUIRE(world >= 1 && world <= FEDB200_MAX_RANKS && rank >= 0 && rank < world, "fedavg_reduce_nvls: rank %d / world %d", rank, world);
+    FEDB_REQUIRE(mc_acc != nullptr && mc_out != nullptr, "fedavg_reduce_nvls: buffers are not bound to a multicast object");
+    FEDB_REQUIRE((((uintptr_t)mc_acc | (uintptr_t)mc_out) & 15) == 0, "fedavg_reduce_nvls: 16-byte alignment");
+    PeerTable t;
+    fill_table(t, (const void* const*)acc_ptrs, (void* const*)out_ptrs, nullptr, flag_ptrs, world);
+    const size_t work = (n / 4 + world - 1) / world;
+    int grid = (int)((work + 4 * 512 - 1) / (4 * 512));
+    const int cap = max_ctas > 0 ? max_ctas : sm_count();
+    if (grid > cap) grid = cap;
+    if (grid < 1) grid = 1;
+    fedavg_reduce_nvls_kernel<<<grid, 512, 0, (cudaStream_t)stream>>>(t, mc_acc, mc_out, rank, world, n, my_weight, inv_total_weight,
+                                                                     epoch, timeout_to_cycles(timeout_ms));
+    FEDB_LAUNCH_CHECK();
+    return 0;
 }
 
 extern "C" int fedb200_peer_exchange(void* const* table_ptrs, unsigned int* const* flag_ptrs, int rank, int world,

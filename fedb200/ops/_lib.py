@@ -58,6 +58,7 @@ _PROTOS = {
     "fedb200_copy_flagged": (i32, [vp, vp, sz, sz, vp, u32, vp]),
     "fedb200_set_flags": (i32, [vp, u32, i32, vp]),
     "fedb200_fedavg_reduce_ex": (i32, [vp, vp, vp, vp, i32, i32, sz, f32, f32, u32, i32, i32, i32, vp]),
+    "fedb200_fedavg_reduce_nvls": (i32, [vp, vp, vp, vp, vp, i32, i32, sz, f32, f32, u32, i32, i32, vp]),
     "fedb200_peer_exchange": (i32, [vp, vp, i32, i32, i32, u32, i32, vp]),
     "fedb200_peer_barrier": (i32, [vp, i32, i32, u32, i32, vp]),
     "fedb200_flag_set": (i32, [vp, u32, vp]),

@@ -28,8 +28,10 @@ class _RawCuda:
 
 
 class SymmetricBuffer:
-    def __init__(self, name: str, tensor: torch.Tensor, ptrs: List[int], nbytes: int):
+    def __init__(self, name: str, tensor: torch.Tensor, ptrs: List[int], nbytes: int, mc_ptr: int = 0, keep=None):
         self.name, self.tensor, self.ptrs, self.nbytes = name, tensor, ptrs, nbytes
+        self.mc_ptr = mc_ptr            # multicast (NVLS) address of the same buffer, 0 if it is not bound to a multicast object
+        self._keep = keep               # allocator handles that must outlive the buffer
 
     def table(self, byte_offset: int = 0):
         arr = (C.c_void_p * len(self.ptrs))(*[p + byte_offset for p in self.ptrs])
@@ -86,9 +88,38 @@ class PeerComm(Comm):
         dist.barrier()
         return buf
 
-    def alloc(self, name: str, numel: int, dtype=torch.float32) -> torch.Tensor:
+    def _alloc_multicast(self, name: str, nbytes: int) -> SymmetricBuffer:
+        """Symmetric buffer bound to an NVLS multicast object.  Allocation, handle exchange and the multicast binding
+        (CUDA VMM: cuMemCreate / cuMulticastCreate / AddDevice / BindMem) are host-side plumbing done by torch's
+        symmetric-memory allocator; what comes back — every rank's unicast pointer and ONE multicast pointer — is what the
+        kernels of this library consume.  Raises if the box exposes no multicast."""
+        import torch.distributed._symmetric_memory as symm
+        nbytes = (nbytes + 255) // 256 * 256
+        t = symm.empty(nbytes, dtype=torch.uint8, device=self.device)
+        t.zero_()
+        h = symm.rendezvous(t, dist.group.WORLD)
+        if int(h.multicast_ptr) == 0:
+            raise RuntimeError("this box does not expose NVLS multicast (multicast_ptr == 0)")
+        buf = SymmetricBuffer(name, t, [int(p) for p in h.buffer_ptrs], nbytes, int(h.multicast_ptr), keep=h)
+        while name in self.bufs:
+            name += "'"
+        self.bufs[name] = buf
+        torch.cuda.synchronize()
+        dist.barrier()
+        return buf
+
+    def nvls_available(self) -> bool:
+        if getattr(self, "_nvls_ok", None) is None:
+            try:
+                self._alloc_multicast("__nvls_probe__", 4096)
+                self._nvls_ok = True
+            except Exception:
+                self._nvls_ok = False
+        return self._nvls_ok
+
+    def alloc(self, name: str, numel: int, dtype=torch.float32, multicast: bool = False) -> torch.Tensor:
         esz = torch.empty(0, dtype=dtype).element_size()
-        buf = self._alloc_symmetric(name, numel * esz)
+        buf = self._alloc_multicast(name, numel * esz) if multicast else self._alloc_symmetric(name, numel * esz)
         view = buf.tensor[: numel * esz].view(dtype)
         self._by_ptr[view.data_ptr()] = (buf, 0)
         return view
@@ -151,12 +182,26 @@ class PeerComm(Comm):
 
     # ---- collectives ---------------------------------------------------------------------------------------------
     def weighted_mean(self, acc: torch.Tensor, weight: float, out: torch.Tensor, shadow: Optional[torch.Tensor] = None,
-                      inv_total: float = 0.0, oneshot: Optional[bool] = None, max_ctas: int = 0) -> None:
+                      inv_total: float = 0.0, oneshot: Optional[bool] = None, max_ctas: int = 0, nvls: bool = False) -> None:
         """Fused FedAvg over peer memory.  ``oneshot`` (default: payloads <= 64 KB) reads every peer's whole buffer and
         writes only the local ``out``; otherwise two-shot reduce-scatter + push.  ``max_ctas`` caps the grid for overlap
-        with compute on a side stream."""
+        with compute on a side stream.  ``nvls``: both buffers were allocated with ``multicast=True`` — the reduction is
+        done inside the NVSwitch (``multimem.ld_reduce`` / ``multimem.st``), no bf16 shadow in that form."""
         ab, ao = self._locate(acc)
         ob, oo = self._locate(out)
+        if nvls:
+            if not (ab.mc_ptr and ob.mc_ptr):
+                raise ValueError("nvls=True needs buffers allocated with comm.alloc(..., multicast=True)")
+            if shadow is not None:
+                raise ValueError("the NVLS form writes no bf16 shadow")
+            self.epoch += 1
+            call("fedb200_fedavg_reduce_nvls", C.cast(ab.table(ao), C.c_void_p), C.cast(ob.table(oo), C.c_void_p),
+                 ab.mc_ptr + ao, ob.mc_ptr + oo, C.cast(self.flags.table(), C.c_void_p), self.rank, self.world, acc.numel(),
+                 float(weight), float(inv_total), self.epoch, self.timeout_ms, int(max_ctas),
+                 torch.cuda.current_stream().cuda_stream)
+            count()
+            self.launches += 1
+            return
         sh = None
         if shadow is not None:
             sb, so = self._locate(shadow)
@@ -285,5 +330,6 @@ class PeerComm(Comm):
             for p in self._own:
                 _lib.lib().fedb200_peer_free(C.c_void_p(p))
             self._own.clear()
+            self.bufs.clear()                      # multicast buffers: tensors + handles released with their references
         except Exception:
             pass

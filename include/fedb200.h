@@ -206,6 +206,14 @@ int fedb200_fedavg_reduce_ex(const float* const* acc_ptrs, float* const* out_ptr
                              unsigned int* const* flag_ptrs, int rank, int world, size_t n, float my_weight,
                              float inv_total_weight, unsigned int epoch, int timeout_ms, int oneshot, int max_ctas,
                              void* stream);
+/* K1, NVLS form: the buffers are bound to a multicast object (host-side CUDA VMM set-up; fedb200/parallel/peer_mem.py uses
+ * torch's symmetric-memory allocator for it); mc_acc / mc_out are the MULTICAST addresses, acc_ptrs / out_ptrs the unicast peer
+ * pointers of the same buffers (scalar tail only).  The sum is formed inside the NVSwitch (multimem.ld_reduce) and the result is
+ * written to every replica with one multimem.st, so each GPU receives D / world reduced elements instead of (world - 1) D /
+ * world operands.  Same barriers, weights, masked / timed-out behaviour and epoch sequence as the two-shot P2P form. */
+int fedb200_fedavg_reduce_nvls(const float* const* acc_ptrs, float* const* out_ptrs, const float* mc_acc, float* mc_out,
+                               unsigned int* const* flag_ptrs, int rank, int world, size_t n, float my_weight,
+                               float inv_total_weight, unsigned int epoch, int timeout_ms, int max_ctas, void* stream);
 /* Slot exchange (device-side all-gather of small per-round records): `table_ptrs` are the `world` peer-mapped copies of a
  * [world, slot_bytes] table; this rank's slot is pushed into every peer's copy, then a cross-rank barrier.  Replaces the host
  * all_gather_object of roots / counts / metrics (no counterpart in the reference, which has no communication layer). */

@@ -66,6 +66,21 @@ def main():
         rs /= world
         torch.testing.assert_close(so, rs, rtol=1e-5, atol=1e-6)
         comm.weighted_mean(acc, 1.0, out)                   # a two-shot call in between must not disturb the epochs
+    # NVLS form (reduction inside the NVSwitch via multimem.ld_reduce / multimem.st) where the box exposes multicast
+    if comm.nvls_available():
+        na, no = comm.alloc("t_nv_acc", n, multicast=True), comm.alloc("t_nv_out", n, multicast=True)
+        for it in range(2):
+            na.copy_(x * (w + it))
+            torch.cuda.synchronize(); dist.barrier()
+            comm.weighted_mean(na, w + it, no, nvls=True)
+            ref = (x * (w + it)).clone()
+            dist.all_reduce(ref)
+            ref /= sum(r + 1 + it for r in range(world))
+            torch.testing.assert_close(no, ref, rtol=1e-5, atol=1e-6)
+        keep_nv = no.clone()
+        comm.weighted_mean(na, 0.0, no, nvls=True)            # all masked: untouched
+        torch.testing.assert_close(no, keep_nv, rtol=0, atol=0)
+        comm.check_errors()
     # slot exchange: device-side all-gather of small per-rank records
     tab = comm.alloc("t_tab", world * 48, torch.int32).view(world, 48)
     for it in range(2):
