@@ -14,6 +14,7 @@
 #include "common.cuh"
 #include "peer_flags.cuh"
 #include <string.h>
+#include <stdlib.h>
 
 namespace fedb {
 
@@ -120,6 +121,7 @@ __device__ __forceinline__ void multimem_st(float* mc, const float4& v) {
                  ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
+template <int U>
 __global__ void __launch_bounds__(512) fedavg_reduce_nvls_kernel(const PeerTable t, const float* __restrict__ mc_acc,
                                                                  float* __restrict__ mc_out, int rank, int world, size_t n,
                                                                  float my_weight, float inv_w_arg, unsigned int epoch,
@@ -142,12 +144,12 @@ __global__ void __launch_bounds__(512) fedavg_reduce_nvls_kernel(const PeerTable
         const size_t lo = per * rank, hi = lo + per < n4 ? lo + per : n4;
         const size_t stride = (size_t)gridDim.x * blockDim.x;
         size_t i = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-        for (; i + 3 * stride < hi; i += 4 * stride) {                 // four switch reductions in flight per thread
-            float4 v[4];
+        for (; i + (U - 1) * stride < hi; i += U * stride) {           // U switch reductions in flight per thread
+            float4 v[U];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) v[u] = multimem_ld_reduce_add(mc_acc + 4 * (i + u * stride));
+            for (int u = 0; u < U; ++u) v[u] = multimem_ld_reduce_add(mc_acc + 4 * (i + u * stride));
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < U; ++u) {
                 v[u].x *= inv_w; v[u].y *= inv_w; v[u].z *= inv_w; v[u].w *= inv_w;
                 multimem_st(mc_out + 4 * (i + u * stride), v[u]);
             }
@@ -303,8 +305,14 @@ extern "C" int fedb200_fedavg_reduce_nvls(const float* const* acc_ptrs, float* c
     const int cap = max_ctas > 0 ? max_ctas : sm_count();
     if (grid > cap) grid = cap;
     if (grid < 1) grid = 1;
-    fedavg_reduce_nvls_kernel<<<grid, 512, 0, (cudaStream_t)stream>>>(t, mc_acc, mc_out, rank, world, n, my_weight, inv_total_weight,
-                                                                     epoch, timeout_to_cycles(timeout_ms));
+    // measured at 8 x B200, 433 MB: 4 reductions in flight per thread 0.98 ms, 8 in flight 1.03 ms; a 32-CTA grid 0.95 ms
+    static const int unroll = [] { const char* e = getenv("FEDB200_NVLS_UNROLL"); return e ? atoi(e) : 4; }();
+    if (unroll >= 8)
+        fedavg_reduce_nvls_kernel<8><<<grid, 512, 0, (cudaStream_t)stream>>>(t, mc_acc, mc_out, rank, world, n, my_weight,
+                                                                            inv_total_weight, epoch, timeout_to_cycles(timeout_ms));
+    else
+        fedavg_reduce_nvls_kernel<4><<<grid, 512, 0, (cudaStream_t)stream>>>(t, mc_acc, mc_out, rank, world, n, my_weight,
+                                                                            inv_total_weight, epoch, timeout_to_cycles(timeout_ms));
     FEDB_LAUNCH_CHECK();
     return 0;
 }

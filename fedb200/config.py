@@ -133,6 +133,7 @@ class FedConfig:
     ignore_mismatched_sizes: bool = False   # server_noniid_medical_transcriptions.py:146-148
     vocab_path: Optional[str] = None   # vocab.txt (or its directory) for the WordPiece tokenizer; default: init_checkpoint
     deterministic: bool = False        # bit-reproducible training (ordered split-K wgrad reduction): ledger roots re-derivable
+    nvls: bool = False                 # FedAvg reduce inside the NVSwitch (multimem) where the box exposes multicast
     aggregate_ctas: int = 32           # grid of the fused FedAvg reduce when it overlaps the local evaluation (side stream)
     placement: str = "balanced"        # balanced (token-count LPT) | block (contiguous id blocks)
     checkpoint_dir: Optional[str] = None
@@ -186,6 +187,7 @@ def build_parser(defaults: Optional[FedConfig] = None, description: str = "") ->
     p.add_argument("--inject-kind", default=d.inject_kind)
     p.add_argument("--ledger", action="store_true", default=d.ledger)
     p.add_argument("--verify-updates", action="store_true", default=d.verify_updates)
+    p.add_argument("--nvls", action="store_true", default=d.nvls, help="switch-side FedAvg reduction (NVLS multicast)")
     p.add_argument("--init-checkpoint", default=d.init_checkpoint,
                    help="local HF checkpoint directory to fine-tune from (from_pretrained equivalent)")
     p.add_argument("--ignore-mismatched-sizes", action="store_true", default=d.ignore_mismatched_sizes)
@@ -239,6 +241,6 @@ def config_from_args(args: argparse.Namespace, defaults: Optional[FedConfig] = N
     cfg.anomaly_detector, cfg.inject_anomalies, cfg.inject_kind = (
         args.anomaly_detector, args.inject_anomalies, args.inject_kind)
     cfg.ledger, cfg.checkpoint_dir, cfg.checkpoint_every = args.ledger, args.checkpoint_dir, args.checkpoint_every
-    cfg.verify_updates = args.verify_updates
+    cfg.verify_updates, cfg.nvls = args.verify_updates, args.nvls
     cfg.resume, cfg.metrics_path, cfg.seed = args.resume, args.metrics_path, args.seed
     return cfg

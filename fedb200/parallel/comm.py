@@ -52,8 +52,12 @@ class Comm:
         self.device = torch.device(device)
 
     # -- memory -----------------------------------------------------------------------------
-    def alloc(self, name: str, numel: int, dtype=torch.float32) -> torch.Tensor:
-        """Buffer every rank allocates identically (peer-mapped on the peer backend)."""
+    def nvls_available(self) -> bool:
+        return False
+
+    def alloc(self, name: str, numel: int, dtype=torch.float32, multicast: bool = False) -> torch.Tensor:
+        """Buffer every rank allocates identically (peer-mapped on the peer backend; ``multicast``: also bound to an NVLS
+        multicast object there)."""
         return torch.zeros(numel, dtype=dtype, device=self.device)
 
     def delta_buffer(self, rows: int, D: int, dtype=torch.float32) -> torch.Tensor:

@@ -64,10 +64,11 @@ class FedRuntime:
         self.runner = make_runner(cfg, self.device, cfg.seed)
         self.D = self.runner.flat.numel()
         self.nbytes = self.D * 4
-        self.global_flat = self.comm.alloc("global", self.D)
+        self.nvls = bool(cfg.nvls) and self.world > 1 and self.comm.nvls_available()
+        self.global_flat = self.comm.alloc("global", self.D, multicast=self.nvls)
         self.global_flat.copy_(self.runner.flat)
-        self.slots = self.comm.alloc("slots", self.P * self.D).view(self.P, self.D)
-        self.acc = self.comm.alloc("acc", self.D)
+        self.slots = self.comm.alloc("slots", self.P * self.D, multicast=self.nvls).view(self.P, self.D)
+        self.acc = self.comm.alloc("acc", self.D, multicast=self.nvls)
         self.deltas = None
         self.timer = PhaseTimer(self.device.type == "cuda")
         self.readback = HostReadback(self.device)
@@ -374,6 +375,8 @@ class FedRuntime:
             side.wait_stream(torch.cuda.current_stream())
         with (torch.cuda.stream(side) if side is not None else _nullctx()):
             kw = {"max_ctas": self.cfg.aggregate_ctas} if side is not None else {}
+            if self.nvls:
+                kw["nvls"] = True
             if self.P == 1 and self.N == self.world and not self.masked:
                 # one peer per GPU and nobody masked anywhere: the slot IS the rank's accumulator.  Every rank must take
                 # the same branch — the fused reduce reads the SAME symmetric buffer on all peers.

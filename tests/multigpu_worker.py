@@ -200,6 +200,20 @@ def main():
     dist.all_gather_object(heads, (rt1.ledger.head.hex(), res1["last"]["local_accuracy"]))
     assert len(set(h[0] for h in heads)) == 1 and all(h[1] == heads[0][1] for h in heads), "records diverged across ranks"
     assert len(heads[0][1]) == 2 * world
+    # ---- the same round with the switch-side (NVLS) aggregate: --nvls allocates slots / global model on a multicast object ------
+    if comm.nvls_available():
+        import copy
+        cfgn = copy.deepcopy(cfg1)
+        cfgn.nvls, cfgn.num_clients = True, world
+        rtn = FedRuntime(cfgn, echo=False, comm=comm)
+        assert rtn.nvls
+        rtn.run()
+        torch.cuda.synchronize()
+        comm.check_errors()
+        mine = rtn.slots[0].clone()
+        dist.all_reduce(mine)
+        torch.testing.assert_close(rtn.global_flat, mine / world, rtol=1e-5, atol=1e-6)
+        assert rtn.ledger.validate() == -1
     # ---- asynchronous gossip across GPUs: schedule-driven executor, device-side pub/done flags ---------------------
     cfg2 = FedConfig(mode="serverless", num_clients=2 * world, num_rounds=3, device="cuda", backend="fused", comm="peer",
                      asynchronous=True, ledger=True, topology="full")
