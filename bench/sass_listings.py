@@ -18,7 +18,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "fedb200", "lib", "libfedb200.so")
 OUT = os.path.join(ROOT, "docs", "sass")
 KEY = re.compile(r"\b(UTCHMMA|UTCQMMA|UTCBAR|UTCCP|LDTM|STTM|UTMALDG|UTMASTG|UTMAPF|UBLKCP|SYNCS|HMMA|REDG|RED|ATOMG|ATOM|MUFU|"
-                 r"LDG|STG|LD|ST|MEMBAR|ERRBAR|CCTL|NANOSLEEP|ACQBULK|UCGABAR|BAR)\b")
+                 r"LDGMC|STGMC|REDGMC|LDG|STG|LD|ST|MEMBAR|ERRBAR|CCTL|NANOSLEEP|ACQBULK|UCGABAR|BAR)\b")
 FULL_IF = ("UTCHMMA", "UTMALDG", "UTMASTG", "LDTM", "UBLKCP")
 MAX_FULL_LINES = 12000
 
