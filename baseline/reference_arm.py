@@ -55,6 +55,9 @@ SCRIPT = os.path.join("src", "Serverlesscase", "serverless_IID_IMDB.py")
 def _verify_unmodified() -> str:
     path = os.path.join(REF_ROOT, SCRIPT)
     sums = os.path.join(REF_ROOT, "SHA256SUMS")
+    if not (os.path.exists(path) and os.path.exists(sums)) and os.path.isdir("/root/reference/src"):
+        import subprocess                      # first use on a machine that has the reference mounted: stage it now
+        subprocess.run([os.path.join(HERE, "install_reference.sh")], check=False, capture_output=True)
     if not (os.path.exists(path) and os.path.exists(sums)):
         raise FileNotFoundError("baseline/_ref is not staged (run baseline/install_reference.sh)")
     want = {l.split()[1]: l.split()[0] for l in open(sums) if l.strip()}
