@@ -336,7 +336,7 @@ __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __
 // blockDim = (32, 8): a warp-row covers 64 contiguous columns, the 8 rows of threads stride over the sequence's tokens.
 __global__ void __launch_bounds__(256) attn_bwd_finish_kernel(const __nv_bfloat16* __restrict__ dq_part, __nv_bfloat16* __restrict__ dqkv,
                                                               float* __restrict__ dbias, const int* __restrict__ cu_seqlens,
-                                                              int T, int H) {
+                                                              int T, int H, float* __restrict__ part) {
     pdl_sync();
     // blockDim = (8, 32): 8 threads x 8 columns = one 64-column slab, 32 token rows per sweep; one block per
     // (slab, sequence) so each bias-gradient column receives one atomic per sequence
@@ -379,7 +379,8 @@ __global__ void __launch_bounds__(256) attn_bwd_finish_kernel(const __nv_bfloat1
         float sum = 0.f;
 #pragma unroll 8
         for (int y = 0; y < 32; ++y) sum += red[y][t];
-        atomicAdd(dbias + blockIdx.x * 64 + t, sum);
+        if (part != nullptr) part[(size_t)blockIdx.y * 3 * H + blockIdx.x * 64 + t] = sum;   // reproducible mode: per-sequence partials
+        else atomicAdd(dbias + blockIdx.x * 64 + t, sum);
     }
 }
 
@@ -717,7 +718,13 @@ extern "C" int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dc
                                                    scale, scale * LOG2E, seed, dropout_thresh16(dropout_p),
                                                    1.0f / (1.0f - dropout_p), dropout_p > 0.f, (const uint32_t*)drop_bits,
                                                    (max_seqlen + 31) / 32));
+    float* part = nullptr;
+    if (det_enabled() && dbias_qkv != nullptr && B > 1) {
+        part = det_workspace((size_t)B * 3 * H * sizeof(float));
+        FEDB_REQUIRE(part != nullptr, "attn_bwd: deterministic workspace too small");
+    }
     FEDB_CHECK(launch_pdl(attn_bwd_finish_kernel, dim3((3 * H + 63) / 64, B), dim3(8, 32), 0, s, (const __nv_bfloat16*)dq_accum,
-                          (__nv_bfloat16*)dqkv, dbias_qkv, cu_seqlens, T, H));
+                          (__nv_bfloat16*)dqkv, dbias_qkv, cu_seqlens, T, H, part));
+    if (part != nullptr) FEDB_TRY(det_ordered_colsum(part, B, (size_t)3 * H, 3 * H, 1, dbias_qkv, nullptr, nullptr, nullptr, s));
     return 0;
 }

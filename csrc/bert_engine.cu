@@ -36,7 +36,6 @@ static int wgrad_splits(int out_rows, int out_cols, int tokens, int sms) {
 
 using namespace fedb;
 
-#define FEDB_TRY(expr) do { int _rc = (expr); if (_rc) return _rc; } while (0)
 
 extern "C" int fedb200_bert_forward(const fedb200_bert_plan* p, int T, int B, int max_len, int train,
                                     unsigned long long step_seed, int sm_count_hint, void* stream) {

@@ -35,8 +35,19 @@ void set_last_error(const char* fmt, ...);
     } while (0)
 
 #define FEDB_LAUNCH_CHECK() FEDB_CHECK(cudaGetLastError())
+#define FEDB_TRY(expr) do { int _rc = (expr); if (_rc) return _rc; } while (0)
 
 int sm_count();   // cached multiprocessor count of the current device
+
+// determinism.cu: reproducible-reduction mode.  When a workspace is registered (fedb200_set_deterministic) the training
+// kernels store their per-CTA / per-split partials there and these helpers add them up in a fixed order.
+bool det_enabled();
+size_t det_capacity();
+float* det_workspace(size_t need_bytes, size_t offset_bytes = 0);     // null when off or too small
+int det_ordered_colsum(const float* part, int nparts, size_t stride, int seg, int nseg, float* o0, float* o1, float* o2, float* o3,
+                       cudaStream_t s);
+int det_ordered_split_sum(const float* ws, int splits, size_t stride, size_t n, float* out, cudaStream_t s);
+int det_scatter_rows(const int* keys, const float* dz, int T, int H, int min_key, float* out, cudaStream_t s);
 
 // ---------------------------------------------------------------------------------------------
 // programmatic dependent launch (PDL)

@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(256) mix_n_kernel(MixArgs a, float* __restrict
 // out[n] += sum_m x[m, n]   (x bf16 row-major with leading dimension ld).  blockDim = (32, 8):
 // a warp-row covers 64 contiguous columns (bf16x2 per lane); rows are strided over y and blockIdx.y.
 __global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out,
-                                                          int M, int N, int ld, int rows_per_block) {
+                                                          int M, int N, int ld, int rows_per_block, float* __restrict__ part) {
     pdl_sync();
     __shared__ float2 red[8][32];
     const int col = (blockIdx.x * 32 + threadIdx.x) * 2;
@@ -132,8 +132,13 @@ __global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* _
     if (threadIdx.y == 0 && col < N) {
 #pragma unroll
         for (int y = 1; y < 8; ++y) { acc.x += red[y][threadIdx.x].x; acc.y += red[y][threadIdx.x].y; }
-        atomicAdd(out + col, acc.x);
-        atomicAdd(out + col + 1, acc.y);
+        if (part != nullptr) {                       // reproducible mode: row-block partials, summed in order afterwards
+            part[(size_t)blockIdx.y * N + col] = acc.x;
+            part[(size_t)blockIdx.y * N + col + 1] = acc.y;
+        } else {
+            atomicAdd(out + col, acc.x);
+            atomicAdd(out + col + 1, acc.y);
+        }
     }
 }
 
@@ -224,8 +229,14 @@ extern "C" int fedb200_colsum_bf16(const void* x, float* out, int M, int N, int 
     if (row_blocks > (M + 63) / 64) row_blocks = (M + 63) / 64;
     if (row_blocks < 1) row_blocks = 1;
     const int rpb = (M + row_blocks - 1) / row_blocks;
+    float* part = nullptr;
+    if (det_enabled() && row_blocks > 1) {
+        part = det_workspace((size_t)row_blocks * N * sizeof(float));
+        FEDB_REQUIRE(part != nullptr, "colsum: deterministic workspace too small");
+    }
     FEDB_CHECK(launch_pdl(colsum_bf16_kernel, dim3(dim3(col_blocks, row_blocks)), dim3(dim3(32, 8)), 0, (cudaStream_t)stream, 
-        (const __nv_bfloat16*)x, out, M, N, ld, rpb));
+        (const __nv_bfloat16*)x, out, M, N, ld, rpb, part));
+    if (part != nullptr) FEDB_TRY(det_ordered_colsum(part, row_blocks, (size_t)N, N, 1, out, nullptr, nullptr, nullptr, (cudaStream_t)stream));
     return 0;
 }
 

@@ -77,7 +77,9 @@ __global__ void __launch_bounds__(EM_WARPS * 32) embed_bwd_kernel(
     const float* __restrict__ typew, const float* __restrict__ gamma, const float* __restrict__ mean_in,
     const float* __restrict__ rstd_in, float* __restrict__ gword, float* __restrict__ gpos, float* __restrict__ gtype,
     float* __restrict__ dgamma, float* __restrict__ dbeta, int T, int H, uint64_t seed, uint32_t keep_thresh,
-    float inv_keep, int use_dropout) {
+    float inv_keep, int use_dropout, float* __restrict__ dz_out, float* __restrict__ part) {
+    // reproducible mode (dz_out / part given): the per-token gradient rows go to dz_out [T, H] and are scattered into the
+    // tables by an ordered kernel afterwards; the four block-reduced quantities go to part [blocks][4][H]
     pdl_sync();
     extern __shared__ float red[];        // [EM_WARPS][H]
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, nvec = H / 8;
@@ -123,11 +125,15 @@ __global__ void __launch_bounds__(EM_WARPS * 32) embed_bwd_kernel(
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
                     const float dzv = rstd * (dxh[i][k] - c1 - xh[i][k] * c2);
-                    atomicAdd(gword + (size_t)id * H + v * 8 + k, dzv);
-                    atomicAdd(gpos + (size_t)ps * H + v * 8 + k, dzv);
+                    if (dz_out != nullptr) {
+                        dz_out[(size_t)row * H + v * 8 + k] = dzv;
+                    } else {
+                        atomicAdd(gword + (size_t)id * H + v * 8 + k, dzv);
+                        atomicAdd(gpos + (size_t)ps * H + v * 8 + k, dzv);
+                    }
                     if (ty == 0) t0[i][k] += dzv;
                     else if (ty == 1) t1[i][k] += dzv;
-                    else atomicAdd(gtype + (size_t)ty * H + v * 8 + k, dzv);
+                    else if (dz_out == nullptr) atomicAdd(gtype + (size_t)ty * H + v * 8 + k, dzv);
                 }
             }
         }
@@ -149,7 +155,8 @@ __global__ void __launch_bounds__(EM_WARPS * 32) embed_bwd_kernel(
             float s = 0.f;
 #pragma unroll
             for (int w2 = 0; w2 < EM_WARPS; ++w2) s += red[w2 * H + c];
-            if (s != 0.f) atomicAdd(outs[q] + c, s);
+            if (part != nullptr) part[((size_t)blockIdx.x * 4 + q) * H + c] = s;
+            else if (s != 0.f) atomicAdd(outs[q] + c, s);
         }
     }
 }
@@ -194,8 +201,23 @@ extern "C" int fedb200_embed_bwd(const void* dx, const int* ids, const int* pos,
     int blocks = (T + EM_WARPS - 1) / EM_WARPS;
     const int cap = sm_count() * 2;
     if (blocks > cap) blocks = cap;
+    float* dz = nullptr;
+    float* part = nullptr;
+    if (det_enabled()) {
+        const size_t dz_bytes = (((size_t)T * H * sizeof(float)) + 255) & ~(size_t)255;
+        dz = det_workspace(dz_bytes);
+        part = det_workspace((size_t)blocks * 4 * H * sizeof(float), dz_bytes);
+        FEDB_REQUIRE(dz != nullptr && part != nullptr, "embed_bwd: deterministic workspace too small");
+    }
     FEDB_CHECK(launch_pdl(embed_bwd_kernel, dim3(blocks), dim3(EM_WARPS * 32), EM_WARPS * H * sizeof(float), (cudaStream_t)stream, 
         (const __nv_bfloat16*)dx, ids, pos, tt, word, posw, typew, gamma, mean, rstd, gword, gpos, gtype, dgamma,
-        dbeta, T, H, seed, th, ik, dropout_p > 0.f));
+        dbeta, T, H, seed, th, ik, dropout_p > 0.f, dz, part));
+    if (dz != nullptr) {
+        cudaStream_t s = (cudaStream_t)stream;
+        FEDB_TRY(det_ordered_colsum(part, blocks, (size_t)4 * H, H, 4, dgamma, dbeta, gtype, gtype + H, s));
+        FEDB_TRY(det_scatter_rows(ids, dz, T, H, 0, gword, s));
+        FEDB_TRY(det_scatter_rows(pos, dz, T, H, 0, gpos, s));
+        FEDB_TRY(det_scatter_rows(tt, dz, T, H, 2, gtype, s));            // token types 0 / 1 went through the block partials
+    }
     return 0;
 }

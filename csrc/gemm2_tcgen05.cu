@@ -160,7 +160,7 @@ __global__ void __launch_bounds__(G2_THREADS, 1) gemm2_tcgen05_kernel(const __gr
             const int row = m_blk * 2 * G2_BM + (int)rank * G2_BM + quad * 32 + lane;
             gemm_epilogue_tile_tma<BN, EPI>(p, &tmC, &tmC2, &tmAux, stage, slot_it, aux_bar[warp - 2], aux_phase,
                                             tmem_base + ((uint32_t)(quad * 32) << 16) + buf * BN, row, n_blk * BN, half, has_k,
-                                            &acc_full[buf], (local >> 1) & 1u);
+                                            &acc_full[buf], (local >> 1) & 1u, split);
             tc_fence_before_sync();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(&acc_empty[buf], 0);        // the leader's MMA warp owns this barrier

@@ -21,6 +21,7 @@ struct GemmParams {
     float inv_keep;
     int use_dropout;
     int tma_store;          // pair kernel: stage bf16 outputs through smem + TMA store (0 = direct row-per-thread stores)
+    long long split_stride; // EPI_ATOMIC: split s accumulates into out + s * split_stride (elements); 0 = all splits share `out`
 };
 
 __device__ __forceinline__ void store_bf16x32(__nv_bfloat16* dst, const float (&v)[32], int ncols_valid) {
@@ -56,7 +57,7 @@ __device__ __forceinline__ void load_bf16x32(const __nv_bfloat16* src, float (&v
 // residual chunk can be prefetched while the MMAs are still running.
 template <int BN, int EPI = -1>
 __device__ __forceinline__ void gemm_epilogue_tile(const GemmParams& p, uint32_t tmem_acc, int row, int col_base, int half,
-                                                   bool has_k, uint64_t* acc_full, uint32_t parity) {
+                                                   bool has_k, uint64_t* acc_full, uint32_t parity, int split = 0) {
     constexpr int N_CHUNKS = BN / 32;
     const int epi = EPI >= 0 ? EPI : p.epi;      // compile-time in the specialised kernels: the dispatch below folds away
     const bool needs_aux = p.aux != nullptr && (epi == FEDB200_EPI_BIAS_DROP_RES || epi == FEDB200_EPI_MUL_GELU_GRAD ||
@@ -108,7 +109,8 @@ __device__ __forceinline__ void gemm_epilogue_tile(const GemmParams& p, uint32_t
             if (epi == FEDB200_EPI_DISCARD) {
                 if (v[0] == 123456.789f) reinterpret_cast<float*>(p.out)[0] = v[1];      // never true: keeps the loads alive
             } else if (epi == FEDB200_EPI_ATOMIC_F32) {
-                float* o = reinterpret_cast<float*>(p.out) + (size_t)row * p.ldo + col0;
+                // reproducible mode: every split owns a private [M, ldo] partial (one writer per element), summed afterwards
+                float* o = reinterpret_cast<float*>(p.out) + (size_t)split * (size_t)p.split_stride + (size_t)row * p.ldo + col0;
 #pragma unroll
                 for (int q = 0; q < 8; ++q)
                     if (q * 4 < nvalid)
@@ -185,10 +187,10 @@ __device__ __forceinline__ void gemm_epilogue_tile_tma(const GemmParams& p, cons
                                                        const CUtensorMap* tm_out2, const CUtensorMap* tm_aux, uint32_t stage,
                                                        uint32_t& slot_it, uint64_t* aux_bar, uint32_t& aux_phase,
                                                        uint32_t tmem_acc, int row, int col_base, int half, bool has_k,
-                                                       uint64_t* acc_full, uint32_t parity) {
+                                                       uint64_t* acc_full, uint32_t parity, int split = 0) {
     const int epi = EPI >= 0 ? EPI : p.epi;      // compile-time in the specialised kernels: the dispatch below folds away
     if (epi == FEDB200_EPI_ATOMIC_F32 || epi == FEDB200_EPI_DISCARD || !p.tma_store) {
-        gemm_epilogue_tile<BN, EPI>(p, tmem_acc, row, col_base, half, has_k, acc_full, parity);
+        gemm_epilogue_tile<BN, EPI>(p, tmem_acc, row, col_base, half, has_k, acc_full, parity, split);
         return;
     }
     constexpr int N_CHUNKS = BN / 32;

@@ -141,7 +141,7 @@ __global__ void __launch_bounds__(GM_THREADS, 1) gemm_tcgen05_kernel(const __gri
             const bool has_k = split * kb_per_split < k_blocks;
             const int row = m_blk * GM_BM + quad * 32 + lane;
             gemm_epilogue_tile<BN>(p, tmem_base + ((uint32_t)(quad * 32) << 16) + buf * BN, row, n_blk * BN, half, has_k,
-                                   &acc_full[buf], (local >> 1) & 1u);
+                                   &acc_full[buf], (local >> 1) & 1u, split);
             tc_fence_before_sync();
             __syncwarp();
             if (lane == 0) mbar_arrive(&acc_empty[buf]);
@@ -199,10 +199,10 @@ static int gemm_mode() {
 // layout: 0 = NT (A [M,K] K-major, B [N,K] K-major)           forward
 //         1 = NN (A [M,K] K-major, B [K,N] row-major)          dgrad
 //         2 = TN (A [K,M] row-major, B [K,N] row-major)        wgrad (use epi = ATOMIC_F32, splits >= 1)
-extern "C" int fedb200_gemm_bf16(int layout, const void* A, int lda, const void* B, int ldb, int M, int N, int K,
-                                 int epi, void* out, void* out2, int ldo, const float* bias, const void* aux,
-                                 int ld_aux, int act, unsigned long long seed, float dropout_p, int splits,
-                                 int max_ctas, void* stream) {
+static int gemm_bf16_impl(int layout, const void* A, int lda, const void* B, int ldb, int M, int N, int K,
+                          int epi, void* out, void* out2, int ldo, const float* bias, const void* aux,
+                          int ld_aux, int act, unsigned long long seed, float dropout_p, int splits,
+                          int max_ctas, void* stream, long long split_stride) {
     FEDB_REQUIRE(layout >= 0 && layout <= 2, "gemm: layout %d", layout);
     FEDB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
     FEDB_REQUIRE(N % 8 == 0 && ldo % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0, "gemm: N, ldo, lda, ldb must be multiples of 8");
@@ -225,6 +225,7 @@ extern "C" int fedb200_gemm_bf16(int layout, const void* A, int lda, const void*
         // CTA-pair kernel: 256 x BN tile per two SMs, each SM loads half of B
         GemmParams pp;
         pp.M = M; pp.N = N; pp.K = K; pp.splits = splits; pp.epi = epi; pp.out = out; pp.out2 = out2; pp.ldo = ldo;
+        pp.split_stride = split_stride;
         pp.bias = bias; pp.aux = (const __nv_bfloat16*)aux; pp.ld_aux = ld_aux; pp.act = act; pp.seed = seed;
         pp.keep_thresh = dropout_thresh16(dropout_p);
         pp.inv_keep = 1.0f / (1.0f - dropout_p);
@@ -243,6 +244,7 @@ extern "C" int fedb200_gemm_bf16(int layout, const void* A, int lda, const void*
 
     GemmParams p;
     p.M = M; p.N = N; p.K = K; p.splits = splits; p.epi = epi; p.out = out; p.out2 = out2; p.ldo = ldo;
+    p.split_stride = split_stride;
     p.bias = bias; p.aux = (const __nv_bfloat16*)aux; p.ld_aux = ld_aux; p.act = act; p.seed = seed;
     p.keep_thresh = dropout_thresh16(dropout_p);
     p.inv_keep = 1.0f / (1.0f - dropout_p);
@@ -257,4 +259,31 @@ extern "C" int fedb200_gemm_bf16(int layout, const void* A, int lda, const void*
 #undef FEDB_GEMM_CASE
     FEDB_REQUIRE(false, "gemm: no kernel for layout %d BN %d", layout, BN);
     return 0;
+}
+
+extern "C" int fedb200_gemm_bf16(int layout, const void* A, int lda, const void* B, int ldb, int M, int N, int K,
+                                 int epi, void* out, void* out2, int ldo, const float* bias, const void* aux,
+                                 int ld_aux, int act, unsigned long long seed, float dropout_p, int splits,
+                                 int max_ctas, void* stream) {
+    if (epi == FEDB200_EPI_ATOMIC_F32 && splits > 1 && det_enabled() && M > 0 && N > 0 && K > 0) {
+        // Reproducible mode (determinism.cu): split s accumulates into its own [M, ldo] partial in the workspace (one writer
+        // per element, so the atomic add onto the zeroed partial is exact), and the partials are added to `out` in split order.
+        const int k_blocks = (K + GM_BK - 1) / GM_BK;
+        if (splits > k_blocks) splits = k_blocks;
+        const size_t stride = (size_t)M * (size_t)ldo;
+        const size_t fit = det_capacity() / (stride * sizeof(float));
+        if ((size_t)splits > fit) splits = (int)fit;                       // a smaller split factor is slower, not different in kind
+        if (splits > 1) {
+            while (splits > 1 && (splits - 1) * ((k_blocks + splits - 1) / splits) >= k_blocks) --splits;   // as the kernel will see it
+            float* ws = det_workspace((size_t)splits * stride * sizeof(float));
+            FEDB_REQUIRE(ws != nullptr, "gemm: deterministic workspace unavailable");
+            FEDB_CHECK(cudaMemsetAsync(ws, 0, (size_t)splits * stride * sizeof(float), (cudaStream_t)stream));
+            const int e = gemm_bf16_impl(layout, A, lda, B, ldb, M, N, K, epi, ws, out2, ldo, bias, aux, ld_aux, act, seed, dropout_p,
+                                         splits, max_ctas, stream, (long long)stride);
+            if (e) return e;
+            return det_ordered_split_sum(ws, splits, stride, stride, reinterpret_cast<float*>(out), (cudaStream_t)stream);
+        }
+    }
+    return gemm_bf16_impl(layout, A, lda, B, ldb, M, N, K, epi, out, out2, ldo, bias, aux, ld_aux, act, seed, dropout_p, splits,
+                          max_ctas, stream, 0);
 }

@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(LN_WARPS * 32, (NV <= 2) ? 2 : 1) ln_bwd_kerne
     const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ z, const float* __restrict__ mean_in,
     const float* __restrict__ rstd_in, const float* __restrict__ gamma, __nv_bfloat16* __restrict__ dz,
     __nv_bfloat16* __restrict__ df, float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dbias,
-    int T, int H, uint64_t seed, uint32_t keep_thresh, float inv_keep) {
+    int T, int H, uint64_t seed, uint32_t keep_thresh, float inv_keep, float* __restrict__ part) {
     pdl_sync();
     extern __shared__ float red[];        // [LN_WARPS][H]
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, nvec = H / 8;
@@ -208,7 +208,8 @@ __global__ void __launch_bounds__(LN_WARPS * 32, (NV <= 2) ? 2 : 1) ln_bwd_kerne
             float s = 0.f;
 #pragma unroll
             for (int w = 0; w < LN_WARPS; ++w) s += red[w * H + c];
-            atomicAdd(outs[q] + c, s);
+            if (part != nullptr) part[((size_t)blockIdx.x * 3 + q) * H + c] = s;      // reproducible mode: summed in block order afterwards
+            else atomicAdd(outs[q] + c, s);
         }
     }
 }
@@ -254,9 +255,15 @@ extern "C" int fedb200_layernorm_bwd(const void* dy, const void* z, const float*
     cudaError_t le;
 #define FEDB_LN_BWD(NVV) le = launch_pdl(ln_bwd_kernel<NVV>, dim3(blocks), dim3(LN_WARPS * 32), LN_WARPS * H * sizeof(float), \
         (cudaStream_t)stream, (const __nv_bfloat16*)dy, (const __nv_bfloat16*)z, mean, rstd, gamma, (__nv_bfloat16*)dz, \
-        (__nv_bfloat16*)df, dgamma, dbeta, dbias, T, H, seed, thresh, 1.0f / keep)
+        (__nv_bfloat16*)df, dgamma, dbeta, dbias, T, H, seed, thresh, 1.0f / keep, part)
+    float* part = nullptr;
+    if (det_enabled()) {
+        part = det_workspace((size_t)blocks * 3 * H * sizeof(float));
+        FEDB_REQUIRE(part != nullptr, "layernorm_bwd: deterministic workspace too small");
+    }
     if (nv == 1) FEDB_LN_BWD(1); else if (nv == 2) FEDB_LN_BWD(2); else if (nv == 3) FEDB_LN_BWD(3); else FEDB_LN_BWD(4);
 #undef FEDB_LN_BWD
     FEDB_CHECK(le);
+    if (part != nullptr) FEDB_TRY(det_ordered_colsum(part, blocks, (size_t)3 * H, H, 3, dgamma, dbeta, dbias, nullptr, (cudaStream_t)stream));
     return 0;
 }

@@ -187,6 +187,25 @@ class FusedRunner:
         self.use_engine = True                  # native step executor (csrc/bert_engine.cu); False = Python twin
         self._plan = self._build_plan()
         self._sms = torch.cuda.get_device_properties(self.device).multi_processor_count
+        self.det_ws: Optional[torch.Tensor] = None
+        if fed.deterministic:
+            self.set_deterministic(True)
+
+    def set_deterministic(self, on: bool, workspace_mb: int = 256) -> None:
+        """Bit-reproducible training (``--deterministic``, csrc/determinism.cu): split-K weight gradients, bias / LayerNorm
+        column sums and the embedding-table scatter store per-split / per-CTA partials in a workspace and add them in a
+        fixed order instead of with fp32 atomics.  Two runs from the same seed, data and SM count then end with the same
+        bytes, so a ledger's Merkle roots can be re-derived by an auditor.  The switch is process-wide (one trainer per
+        process / GPU is the deployment model); the workspace belongs to this runner."""
+        from ..ops import _lib
+        if on:
+            need = max(int(workspace_mb) << 20, self.max_tokens * max(self.E, self.H) * 4 + (64 << 20))
+            self.det_ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+            _lib.call("fedb200_set_deterministic", self.det_ws.data_ptr(), need)
+        else:
+            torch.cuda.synchronize(self.device)      # nothing in flight may still use the workspace
+            _lib.call("fedb200_set_deterministic", None, 0)
+            self.det_ws = None
 
     def _build_plan(self):
         """Fill the C plan with raw device pointers (valid for the life of the runner: nothing is reallocated)."""
@@ -343,7 +362,7 @@ class FusedRunner:
         from ..ops import _lib
         _lib.call("fedb200_bert_backward", self._plan_ref, T, B, max_len, self._step_seed(), self._sms,
                   torch.cuda.current_stream().cuda_stream)
-        _lib.count(4 + 16 * self.L)
+        _lib.count(4 + 16 * self.L + ((4 + 8 * self.L) if self.det_ws is not None else 0))   # + the ordered-sum kernels
 
     def _step_seed(self) -> int:
         return (self.base_seed * 0x100000001B3 + self.step_count) & 0x7FFFFFFFFFFFFFFF

@@ -20,6 +20,8 @@ _PROTOS = {
     "fedb200_abi_version": (i32, []),
     "fedb200_sm_count": (i32, []),
     "fedb200_set_pdl": (i32, [i32]),
+    "fedb200_set_deterministic": (i32, [vp, sz]),
+    "fedb200_get_deterministic": (i32, []),
     "fedb200_adamw_flat": (i32, [vp, vp, vp, vp, vp, sz, i32, f32, f32, f32, f32, f32, f32, i32, vp]),
     "fedb200_mix_n": (i32, [vp, vp, i32, vp, vp, sz, vp]),
     "fedb200_colsum_bf16": (i32, [vp, vp, i32, i32, i32, vp]),

@@ -34,6 +34,12 @@ int fedb200_abi_version(void);
 int fedb200_sm_count(void);
 /* programmatic dependent launch between this library's kernels (default on; FEDB200_PDL=0 also disables) */
 int fedb200_set_pdl(int on);
+/* Reproducible-reduction mode (csrc/determinism.cu): with a workspace registered (256-byte aligned device memory owned by
+ * the caller, >= 1 MiB; 256 MiB covers BERT-large), split-K weight gradients, bias / LayerNorm column sums and the
+ * embedding scatter store partials there and add them in a fixed order instead of with fp32 atomics, so a training step
+ * is bit-reproducible for a given input, seed and SM count.  ws == NULL switches it off (the default). */
+int fedb200_set_deterministic(void* ws, size_t bytes);
+int fedb200_get_deterministic(void);
 /* TMA tensor maps are memoised per (pointer, shape, box): counters of the per-thread cache (host pointers, may be NULL). */
 int fedb200_tmap_cache_stats(unsigned long long* hits, unsigned long long* misses);
 

@@ -172,6 +172,35 @@ def test_runtime_receiver_verification_uses_static_root(cuda_lib):
     rt.close()
 
 
+def test_deterministic_rounds_give_the_same_ledger_roots(cuda_lib):
+    """--deterministic: two federated runs from the same seed write the same Merkle roots into their ledgers, so an auditor
+    can re-derive an entry by re-running the round (the default, atomic-reduction mode gives different low bits every run)."""
+    from fedb200.config import FedConfig, ModelConfig
+    from fedb200.runtime import FedRuntime
+
+    def roots():
+        cfg = FedConfig(mode="serverless", num_clients=3, num_rounds=2, device="cuda", backend="fused", comm="loopback",
+                        ledger=True, deterministic=True)
+        cfg.model = ModelConfig.preset("bert-mini", num_labels=2)
+        cfg.data.population, cfg.data.train_per_client, cfg.data.test_per_client = 600, 48, 32
+        cfg.data.max_seq_len, cfg.data.batch_size = 160, 16
+        cfg.lr = 1e-3
+        rt = FedRuntime(cfg, echo=False)
+        try:
+            for r in range(2):
+                rt.round_serverless(r)
+            torch.cuda.synchronize()
+            assert rt.ledger.validate() == -1
+            return [b.update_root for b in rt.ledger.blocks], rt.runner.flat.clone()
+        finally:
+            rt.runner.set_deterministic(False)
+            rt.close()
+    (r1, w1), (r2, w2) = roots(), roots()
+    assert len(r1) >= 6 and r1 == r2, [a.hex()[:12] + " / " + b.hex()[:12] for a, b in zip(r1, r2) if a != b]
+    assert torch.equal(w1, w2)
+    assert len(set(r1)) > 1                       # the roots are of different updates, not a constant
+
+
 # ---- the fused multi-GPU kernels in their one-rank form (the box that runs `-m gpu` has a single GPU; the 2-8 GPU versions
 # ---- of these checks live in tests/multigpu_worker.py) ----------------------------------------------------------------------
 def _arr(xs):

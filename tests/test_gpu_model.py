@@ -193,6 +193,48 @@ def test_native_engine_matches_python_twin(cuda_lib):
     torch.testing.assert_close(grads[0][0], grads[1][0], rtol=1e-3, atol=1e-5)
 
 
+def _three_steps(fed, arch_seed, batches, deterministic):
+    from fedb200.models.fused_bert import FusedRunner
+    fed.deterministic = deterministic
+    run = FusedRunner(fed.model, fed, "cuda", seed=arch_seed)
+    try:
+        run.train_step(batches[0], optimizer_step=False)
+        torch.cuda.synchronize()
+        g = run.grads.flat.clone()
+        run.grads.flat.zero_()
+        run.opt.lr = 1e-3
+        for b in batches:
+            run.train_step(b)
+        torch.cuda.synchronize()
+        return g, run.flat.clone()
+    finally:
+        if deterministic:
+            run.set_deterministic(False)
+
+
+@pytest.mark.parametrize("name", ["bert-mini", "albert-mini", "bert-wide"])
+def test_deterministic_mode_is_bit_reproducible_and_matches_default(cuda_lib, name):
+    """``--deterministic`` (csrc/determinism.cu): ordered reductions instead of fp32 atomics.  Two runs from the same seed
+    must end with the SAME BYTES after three optimizer steps with dropout on, and the gradients must equal the default
+    (atomic) path's up to summation order.  ``bert-wide`` (H 768, 2 layers) goes through the CTA-pair GEMM with split-K."""
+    from fedb200.config import ModelConfig
+    if name == "bert-wide":
+        fed = _mini_cfg(0.1)
+        fed.model = ModelConfig.preset("bert-base", num_labels=3, num_layers=2, vocab_size=2000)
+        fed.data.batch_size, fed.data.max_seq_len = 8, 512
+    else:
+        fed = _mini_cfg(0.1, name=name)
+    lens = [[40, 90, 130, 20, 64, 200, 33, 77], [12, 256, 256, 31, 8, 100, 190, 5], [300, 64, 64, 64, 17, 90, 41, 111]]
+    batches = [_batch(fed.model.vocab_size, l, 3, seed=20 + i)[0] for i, l in enumerate(lens)]
+    g1, w1 = _three_steps(fed, 7, batches, True)
+    g2, w2 = _three_steps(fed, 7, batches, True)
+    assert torch.equal(g1, g2), f"gradients differ between two deterministic runs: {(g1 != g2).sum().item()} elements"
+    assert torch.equal(w1, w2), f"weights differ between two deterministic runs: {(w1 != w2).sum().item()} elements"
+    g0, _ = _three_steps(fed, 7, batches, False)
+    torch.testing.assert_close(g1, g0, rtol=1e-3, atol=2e-5)
+    assert float(g1.abs().max()) > 0
+
+
 def test_fused_bert_training_reduces_loss(cuda_lib):
     from fedb200.models.fused_bert import FusedRunner
     fed = _mini_cfg(0.1)
