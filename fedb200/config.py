@@ -132,7 +132,8 @@ class FedConfig:
     init_checkpoint: Optional[str] = None
     ignore_mismatched_sizes: bool = False   # server_noniid_medical_transcriptions.py:146-148
     vocab_path: Optional[str] = None   # vocab.txt (or its directory) for the WordPiece tokenizer; default: init_checkpoint
-    deterministic: bool = False        # bit-reproducible training (ordered split-K wgrad reduction): ledger roots re-derivable
+    deterministic: bool = False        # bit-reproducible training (csrc/determinism.cu: ordered reductions instead of fp32 atomics;
+                                       # +~10 % step time): the ledger's Merkle roots can be re-derived by re-running a round
     nvls: bool = False                 # FedAvg reduce inside the NVSwitch (multimem) where the box exposes multicast
     aggregate_ctas: int = 32           # grid of the fused FedAvg reduce when it overlaps the local evaluation (side stream)
     placement: str = "balanced"        # balanced (token-count LPT) | block (contiguous id blocks)
