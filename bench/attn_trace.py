@@ -35,6 +35,20 @@ for p in (0.1, 0.0):
     first = t[:, 3] - t[:, 2]
     print(f"  launch->after pdl/setup {setup.mean():.0f} clk, setup->first s_full {first.mean():.0f} clk")
     ph = {"arrive->s_full(next)": [], "pass1": [], "wait_o(after pass1)": [], "fold": [], "pass2": []}
+    if os.environ.get("FEDB200_ATTN_FWD", "4") == "4":
+        # four-thread kernel: stamps 3+5j after s_full, 4+5j after max pass + exchange, 6+5j after rescale decision / o_full wait,
+        # 5+5j after the probability pass and the p_ready arrive
+        ph = {"arrive->s_full(next)": [], "pass1+xchg": [], "rescale/wait_o": [], "pass2": []}
+        for row in t:
+            for j in range(int(row[29])):
+                b = 3 + 5 * j
+                ph["pass1+xchg"].append(row[b + 1] - row[b])
+                ph["rescale/wait_o"].append(row[b + 3] - row[b + 1])
+                ph["pass2"].append(row[b + 2] - row[b + 3])
+                if j > 0:
+                    ph["arrive->s_full(next)"].append(row[b] - row[b - 5 + 2])
+        print("  per kv tile (clk):", {k: int(np.mean(v)) for k, v in ph.items() if v}, "tiles", len(ph["pass1+xchg"]))
+        t = t[:0]
     for row in t:
         n = int(row[29])
         for j in range(n):
@@ -48,7 +62,10 @@ for p in (0.1, 0.0):
                 ph["pass2"].append(row[b + 2] - row[pb + 4])
             else:
                 ph["pass2"].append(row[b + 2] - row[b + 1])
-    print("  per kv tile (clk):", {k: int(np.mean(v)) for k, v in ph.items() if v}, "tiles", len(ph["pass1"]))
+    if len(t):
+        print("  per kv tile (clk):", {k: int(np.mean(v)) for k, v in ph.items() if v}, "tiles", len(ph["pass1"]))
+    t = trace.cpu().numpy().reshape(-1, 32)
+    t = t[t[:, 30] > 0]
     # CTAs per SM and the busy span per SM
     sm = t[:, 31]
     per_sm = [(t[sm == s, 30].max() - t[sm == s, 0].min(), (sm == s).sum(), dur[sm == s].sum()) for s in np.unique(sm)]

@@ -305,6 +305,292 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attn_fwd_kernel(const __grid_co
     if (warp == 1) tmem_dealloc(tmem_slot, 256);
 }
 
+// -------------------------------------------------------------------------------------------------
+// forward, four threads per q row (the default; FEDB200_ATTN_FWD=2 selects the kernel above)
+//
+// What the two-thread kernel measured (profiles/attn_fwd_trace.md): per kv tile the softmax warps wait 840 clk for S
+// (one S buffer, re-issued only after P was written), spend 836 clk on a max pass and 3 790 clk on the probability pass,
+// and then fold the P V product into 32 output registers — all of it latency-bound with 16 softmax warps per SM.  Here:
+//   * 16 softmax warps per CTA (32 per SM): thread (row, quarter) owns 32 kv columns of its row.  It reads them from TMEM
+//     ONCE into registers and releases the S buffer at once (`s_free`), so Q K_{j+1}^T runs under the softmax of tile j;
+//     the maximum, the exponentials, the dropout decisions and the bf16 packing all happen on those 32 registers.
+//   * the running output stays in TMEM: P_j V_j accumulates onto it, and it is rescaled (tcgen05.ld / st of the thread's
+//     16 head-dim columns) only when some row of the warp raised its maximum by more than 2^8 — otherwise the stale
+//     maximum keeps being used, which changes nothing in the result (numerator and denominator carry the same factor).
+// -------------------------------------------------------------------------------------------------
+constexpr int AT4_SOFTMAX_WARPS = 16;
+constexpr int AT4_SOFTMAX_THREADS = AT4_SOFTMAX_WARPS * 32;
+constexpr int AT4_THREADS = 64 + AT4_SOFTMAX_THREADS;      // warp 0 TMA, warp 1 MMA, warps 2-17 softmax
+constexpr float AT4_RESCALE_LOG2 = 8.f;
+
+template <bool TRACE>
+__global__ void __launch_bounds__(AT4_THREADS, 2) attn_fwd4_kernel(const __grid_constant__ CUtensorMap tm_qkv,
+                                                                  __nv_bfloat16* __restrict__ ctx, float* __restrict__ lse,
+                                                                  const int* __restrict__ cu_seqlens, int T, int H,
+                                                                  float scale_log2, uint64_t seed, uint32_t keep_thresh,
+                                                                  float inv_keep, int use_dropout,
+                                                                  uint32_t* __restrict__ drop_bits, int bits_stride,
+                                                                  long long* __restrict__ trace, int diag) {
+    // diag (TRACE build only; bench/attn_trace.py): 1 = no exp2 (p = its argument), 2 = no TMEM loads in the sweep, 4 = no P stores
+    const bool d_noexp = TRACE && (diag & 1), d_nold = TRACE && (diag & 2), d_nost = TRACE && (diag & 4);
+    long long* tr = (TRACE && trace) ? trace + ((size_t)(blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 32 : nullptr;
+    const bool tracer = TRACE && tr != nullptr && threadIdx.x == 64;
+    if (tracer) { tr[0] = clock64(); unsigned sm; asm volatile("mov.u32 %0, %%smid;" : "=r"(sm)); tr[31] = sm; }
+    pdl_sync();
+    if (tracer) tr[1] = clock64();
+    const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * 128;
+    const int tok0 = cu_seqlens[b], len = cu_seqlens[b + 1] - tok0;
+    if (q0 >= len) return;
+    const int n_kv = (len + 127) / 128;
+
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* sQ = smem;
+    uint8_t* sK = sQ + AT_TILE;
+    uint8_t* sV = sK + AT_TILE;              // (P lives in TMEM: three 16 KB tiles per CTA)
+    __shared__ __align__(8) uint64_t q_full, k_full, v_full, k_empty, v_empty, s_full, s_free, p_ready, o_full;
+    __shared__ uint32_t tmem_slot;
+    __shared__ float s_xchg[2][4][128];      // [tile parity][column quarter][row]: row maxima, at the end the row sums
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tm_qkv);
+        mbar_init(&q_full, 1);
+        mbar_init(&k_full, 1); mbar_init(&v_full, 1); mbar_init(&k_empty, 1); mbar_init(&v_empty, 1);
+        mbar_init(&s_full, 1); mbar_init(&s_free, AT4_SOFTMAX_WARPS); mbar_init(&p_ready, AT4_SOFTMAX_WARPS);
+        mbar_init(&o_full, 1);
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc(&tmem_slot, 256);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_s = tmem_slot, tmem_o = tmem_slot + 128, tmem_p = tmem_slot + 192;   // S 128 | O 64 | P 64 (bf16 pairs)
+
+    if (warp == 0) {
+        if (elect_one()) {
+            mbar_expect_tx(&q_full, AT_TILE);
+            tma_load_2d(sQ, &tm_qkv, &q_full, h * 64, tok0 + q0);
+        }
+        __syncwarp();
+        for (int j = 0; j < n_kv; ++j) {
+            const uint32_t ph = ((uint32_t)j & 1u) ^ 1u;
+            mbar_wait(&k_empty, ph);
+            if (elect_one()) {
+                mbar_expect_tx(&k_full, AT_TILE);
+                tma_load_2d(sK, &tm_qkv, &k_full, H + h * 64, tok0 + j * 128);
+            }
+            __syncwarp();
+            mbar_wait(&v_empty, ph);
+            if (elect_one()) {
+                mbar_expect_tx(&v_full, AT_TILE);
+                tma_load_2d(sV, &tm_qkv, &v_full, 2 * H + h * 64, tok0 + j * 128);
+            }
+            __syncwarp();
+        }
+    } else if (warp == 1) {
+        constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
+        constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);
+        const uint32_t aQ = smem_u32(sQ);
+        const uint32_t aK = smem_u32(sK), aV = smem_u32(sV);
+        mbar_wait(&q_full, 0);
+        mbar_wait(&k_full, 0);
+        tc_fence_after_sync();
+        if (elect_one()) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) umma_bf16(tmem_s, desc_kmajor(aQ, k), desc_kmajor(aK, k), idesc_s, k > 0);
+            umma_commit(&s_full);
+            umma_commit(&k_empty);
+        }
+        __syncwarp();
+        for (int j = 0; j < n_kv; ++j) {
+            if (j + 1 < n_kv) {
+                mbar_wait(&k_full, (uint32_t)(j + 1) & 1u);
+                mbar_wait(&s_free, (uint32_t)j & 1u);             // every softmax thread holds its part of S(j) in registers
+                tc_fence_after_sync();
+                if (elect_one()) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) umma_bf16(tmem_s, desc_kmajor(aQ, k), desc_kmajor(aK, k), idesc_s, k > 0);
+                    umma_commit(&s_full);
+                    umma_commit(&k_empty);
+                }
+                __syncwarp();
+            }
+            mbar_wait(&v_full, (uint32_t)j & 1u);
+            mbar_wait(&p_ready, (uint32_t)j & 1u);                // P(j) is in shared memory, O carries the right scale
+            tc_fence_after_sync();
+            if (elect_one()) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k)        // A = P(j) from TMEM: 16 k-elements = 8 packed columns per step
+                    umma_bf16_ts(tmem_o, tmem_p + k * 8, desc_mnmajor(aV, k, 8192), idesc_o, (j > 0 || k > 0) ? 1u : 0u);
+                umma_commit(&o_full);
+                umma_commit(&v_empty);
+            }
+            __syncwarp();
+        }
+    } else {
+        const int quad = warp & 3;                            // TMEM lane quadrant this warp may touch
+        const int quarter = (warp - 2) >> 2;                  // kv columns quarter*32 .. +31 of every tile; head-dim columns quarter*16 .. +15
+        const int r = quad * 32 + lane;                       // row within the q tile == TMEM lane
+        const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+        const int q_tok = tok0 + q0 + r;
+        const bool q_ok = q0 + r < len;
+        const uint32_t drop_row = (uint32_t)(h * T + q_tok);
+        const uint32_t drop_key = dropout_key(seed);
+        const float log2_inv_keep = use_dropout ? log2f(inv_keep) : 0.f;
+        const bool keep_all = keep_thresh >= 65536u;
+        const uint32_t thr_hi = keep_thresh << 16;
+        // The row maximum starts as a GUESS (0): the probabilities of a tile are computed against the maximum known so far while
+        // the tile's own maximum is collected in the same sweep, so S is read from TMEM once per tile (TMEM reads run at
+        // 64 B/clk per SM — a second sweep over the 64 KB tile costs ~1 000 clk).  If the tile then turns out to exceed the
+        // reference by more than 2^8 (or, on the first tile, to lie more than 2^8 below the guess) the sweep is repeated
+        // against the true maximum.  Any reference value gives the same result as long as nothing over- or underflows:
+        // numerator, row sum and lse all carry it.
+        float m_run = 0.f, l_part = 0.f;
+        if (tracer) tr[2] = clock64();
+        for (int j = 0; j < n_kv; ++j) {
+            mbar_wait(&s_full, (uint32_t)j & 1u);
+            tc_fence_after_sync();
+            if (tracer) tr[3 + 5 * j] = clock64();
+            const int kv_valid = min(128, len - j * 128) - quarter * 32;      // valid columns among this thread's 32 (may be <= 0)
+            const bool full = kv_valid >= 32;                 // warp-uniform
+            const int chunk = j * 4 + quarter;                // 32-column dropout chunk == this thread's columns
+            const uint32_t base = use_dropout ? attn_drop_base(drop_key, drop_row, (uint32_t)chunk) : 0u;
+            if (tracer) tr[6 + 5 * j] = clock64();
+            float rs, mx;
+            uint32_t bits;
+            uint32_t pk[16];                                  // this thread's 32 probabilities as bf16 pairs: 16 TMEM columns of P
+            // one sweep over this thread's 32 columns, 16 at a time: raw maximum, probabilities against `m_eff` (the survivors'
+            // dropout scale 1/(1-p) is folded into it: every p[i], and so the row sum, carries that factor; it cancels in O / l
+            // and is subtracted from lse at the end), keep decisions, P packed to bf16 pairs in registers
+            auto sweep = [&](const float m_eff) {
+                rs = 0.f; mx = -INFINITY; bits = 0u;
+#pragma unroll
+                for (int sub = 0; sub < 2; ++sub) {
+                    uint32_t raw[16];
+                    if (!d_nold) {
+                        tmem_ld_32x16(tmem_s + lane_addr + quarter * 32 + sub * 16, raw);
+                        tmem_ld_wait();
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) raw[i] = (uint32_t)(i + lane) << 20;
+                    }
+                    if (tracer && j == 1) { tr[23 + sub * 2] = clock64() + (__uint_as_float(raw[0]) == 1.2345f ? 1 : 0); }   // data of this half has landed
+                    float p[16];
+                    if (full) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            mx = fmaxf(mx, __uint_as_float(raw[i]));
+                            const float arg = fmaf(__uint_as_float(raw[i]), scale_log2, -m_eff);
+                            p[i] = d_noexp ? arg : exp2f(arg);
+                            rs += p[i];
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const bool ok = sub * 16 + i < kv_valid;
+                            if (ok) mx = fmaxf(mx, __uint_as_float(raw[i]));
+                            p[i] = ok ? exp2f(fmaf(__uint_as_float(raw[i]), scale_log2, -m_eff)) : 0.f;
+                            rs += p[i];
+                        }
+                    }
+                    if (use_dropout) {
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) {
+                            const int kk = sub * 8 + k;
+                            const uint32_t w = attn_drop_word(base, (uint32_t)kk);
+                            const bool keep_lo = (w << 16) < thr_hi || keep_all;     // (w & 0xFFFF) < thresh16
+                            const bool keep_hi = w < thr_hi || keep_all;             // (w >> 16)   < thresh16
+                            if (keep_lo) bits |= 1u << (2 * kk); else p[2 * k] = 0.f;
+                            if (keep_hi) bits |= 2u << (2 * kk); else p[2 * k + 1] = 0.f;
+                        }
+                    }
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) pk[sub * 8 + q] = pack_bf16x2(p[2 * q], p[2 * q + 1]);
+                    if (tracer && j == 1) tr[24 + sub * 2] = clock64();     // this half is packed
+                }
+            };
+            sweep(m_run - log2_inv_keep);
+            s_xchg[j & 1][quarter][r] = mx;
+            if (tracer && j == 1) tr[27] = clock64();
+            asm volatile("bar.sync 1, %0;" ::"n"(AT4_SOFTMAX_THREADS) : "memory");
+            const float mrow = fmaxf(fmaxf(s_xchg[j & 1][0][r], s_xchg[j & 1][1][r]), fmaxf(s_xchg[j & 1][2][r], s_xchg[j & 1][3][r])) *
+                               scale_log2;
+            if (tracer) tr[4 + 5 * j] = clock64();
+            // decided per warp (the TMEM accesses are warp-collective); the four warps that share these 32 rows see the same
+            // maxima and take the same branch
+            const bool redo = mrow > m_run + AT4_RESCALE_LOG2 || (j == 0 && mrow < m_run - AT4_RESCALE_LOG2);
+            bool waited_o = false;
+            if (__any_sync(0xffffffffu, redo)) {
+                const float m_new = j == 0 ? mrow : fmaxf(m_run, mrow);
+                if (j > 0) {                                  // bring the row sum and the running output (TMEM) to the new reference
+                    mbar_wait(&o_full, (uint32_t)(j - 1) & 1u);
+                    tc_fence_after_sync();
+                    waited_o = true;
+                    const float alpha = exp2f(m_run - m_new);
+                    l_part *= alpha;
+                    uint32_t o[16];
+                    tmem_ld_32x16(tmem_o + lane_addr + quarter * 16, o);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                    tmem_st_32x16(tmem_o + lane_addr + quarter * 16, o);
+                    tmem_st_wait();
+                }
+                m_run = m_new;
+                sweep(m_run - log2_inv_keep);
+            }
+            l_part += rs;
+            if (use_dropout && drop_bits != nullptr && q_ok && chunk < bits_stride)     // chunks past max_seqlen are fully masked
+                drop_bits[((size_t)h * T + q_tok) * bits_stride + chunk] = bits;
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s_free);              // S(j+1) may overwrite the buffer: its MMAs run under the rest of this tile
+            // P(j) goes to TMEM, where P(j) V(j) reads it as its A operand: no shared-memory round trip (P was 64 KB of the
+            // 144 KB of shared-memory traffic per tile).  The columns are free once P(j-1) V(j-1) has completed — issued a
+            // whole sweep ago, so this wait is short
+            if (j > 0 && !waited_o) {
+                mbar_wait(&o_full, (uint32_t)(j - 1) & 1u);
+                tc_fence_after_sync();
+            }
+            if (!d_nost) {
+                tmem_st_32x16(tmem_p + lane_addr + quarter * 16, pk);
+                tmem_st_wait();
+            }
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&p_ready);             // P(j) is in TMEM, O carries the right reference
+            if (tracer) tr[5 + 5 * j] = clock64();
+        }
+        mbar_wait(&o_full, (uint32_t)(n_kv - 1) & 1u);
+        tc_fence_after_sync();
+        s_xchg[n_kv & 1][quarter][r] = l_part;
+        asm volatile("bar.sync 1, %0;" ::"n"(AT4_SOFTMAX_THREADS) : "memory");
+        const float l_run = (s_xchg[n_kv & 1][0][r] + s_xchg[n_kv & 1][1][r]) + (s_xchg[n_kv & 1][2][r] + s_xchg[n_kv & 1][3][r]);
+        uint32_t o[16];
+        tmem_ld_32x16(tmem_o + lane_addr + quarter * 16, o);
+        tmem_ld_wait();
+        if (q_ok) {
+            const float inv = (use_dropout ? inv_keep : 1.f) / l_run;      // l_run carries the folded 1/(1-p): true sum = l_run * (1-p)
+            __nv_bfloat16* dst = ctx + (size_t)q_tok * H + h * 64 + quarter * 16;
+#pragma unroll
+            for (int g = 0; g < 2; ++g) {
+                uint4 pk;
+                pk.x = pack_bf16x2(__uint_as_float(o[g * 8 + 0]) * inv, __uint_as_float(o[g * 8 + 1]) * inv);
+                pk.y = pack_bf16x2(__uint_as_float(o[g * 8 + 2]) * inv, __uint_as_float(o[g * 8 + 3]) * inv);
+                pk.z = pack_bf16x2(__uint_as_float(o[g * 8 + 4]) * inv, __uint_as_float(o[g * 8 + 5]) * inv);
+                pk.w = pack_bf16x2(__uint_as_float(o[g * 8 + 6]) * inv, __uint_as_float(o[g * 8 + 7]) * inv);
+                *reinterpret_cast<uint4*>(dst + g * 8) = pk;
+            }
+            if (quarter == 0) lse[(size_t)h * T + q_tok] = m_run + log2f(l_run) - log2_inv_keep;   // true lse (l carries 1/(1-p))
+        }
+        if (tracer) { tr[29] = n_kv; tr[30] = clock64(); }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_slot, 256);
+}
+
 // =================================================================================================
 // backward
 // =================================================================================================
@@ -668,6 +954,8 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
 using namespace fedb;
 
 static long long* g_attn_trace = nullptr;
+static int g_attn_diag = 0;          // diagnostics of the traced forward (see the kernel); bench/attn_trace.py
+static int g_attn_smem_pad = 0;      // extra dynamic shared memory: > 30 KB leaves room for only one CTA per SM
 
 extern "C" int fedb200_attn_fwd(const void* qkv, void* ctx, float* lse, const int* cu_seqlens, int B, int T, int heads,
                                 int max_seqlen, float scale, unsigned long long seed, float dropout_p, void* drop_bits,
@@ -679,11 +967,23 @@ extern "C" int fedb200_attn_fwd(const void* qkv, void* ctx, float* lse, const in
     if (e) return e;
     const size_t smem = 5 * AT_TILE + 1024;
     static bool configured = false;
+    static int variant = 2;
     if (!configured) {
         FEDB_CHECK(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        FEDB_CHECK(cudaFuncSetAttribute(attn_fwd4_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        FEDB_CHECK(cudaFuncSetAttribute(attn_fwd4_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem + 64 * 1024));
+        const char* v = getenv("FEDB200_ATTN_FWD");
+        if (v != nullptr && (v[0] == '2' || v[0] == '4')) variant = v[0] - '0';
         configured = true;
     }
     dim3 grid((max_seqlen + 127) / 128, heads, B);
+    if (variant == 4) {
+        auto kern = g_attn_trace != nullptr ? attn_fwd4_kernel<true> : attn_fwd4_kernel<false>;
+        FEDB_CHECK(launch_pdl(kern, dim3(grid), dim3(AT4_THREADS), (size_t)(3 * AT_TILE + 1024) + (size_t)g_attn_smem_pad, (cudaStream_t)stream,
+            tm, (__nv_bfloat16*)ctx, lse, cu_seqlens, T, H, scale * LOG2E, seed, dropout_thresh16(dropout_p),
+            1.0f / (1.0f - dropout_p), dropout_p > 0.f, (uint32_t*)drop_bits, (max_seqlen + 31) / 32, g_attn_trace, g_attn_diag));
+        return 0;
+    }
     FEDB_CHECK(launch_pdl(attn_fwd_kernel, dim3(grid), dim3(AT_THREADS), smem, (cudaStream_t)stream, 
         tm, (__nv_bfloat16*)ctx, lse, cu_seqlens, T, H, scale * LOG2E, seed, dropout_thresh16(dropout_p),
         1.0f / (1.0f - dropout_p), dropout_p > 0.f, (uint32_t*)drop_bits, (max_seqlen + 31) / 32, g_attn_trace));
@@ -693,6 +993,12 @@ extern "C" int fedb200_attn_fwd(const void* qkv, void* ctx, float* lse, const in
 // Diagnostics: when set, every attention-forward CTA writes 32 clock64() stamps (see the kernel) at trace[cta * 32 ...];
 // the buffer must hold ceil(max_seqlen / 128) * heads * B * 32 int64.  NULL switches tracing off.
 extern "C" int fedb200_attn_set_trace(void* trace) { g_attn_trace = (long long*)trace; return 0; }
+extern "C" int fedb200_attn_set_diag(int diag, int smem_pad_bytes) {
+    FEDB_REQUIRE(smem_pad_bytes >= 0 && smem_pad_bytes <= 64 * 1024, "attn_set_diag: pad %d", smem_pad_bytes);
+    g_attn_diag = diag;
+    g_attn_smem_pad = smem_pad_bytes;
+    return 0;
+}
 
 extern "C" int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dctx, const float* lse, float* delta,
                                 void* dqkv, float* dq_accum, float* dbias_qkv, const int* cu_seqlens, int B, int T,

@@ -37,6 +37,7 @@ _PROTOS = {
     "fedb200_head_fwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, f32, u64, f32, vp]),
     "fedb200_head_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, u64, f32, vp]),
     "fedb200_attn_set_trace": (i32, [vp]),
+    "fedb200_attn_set_diag": (i32, [i32, i32]),
     "fedb200_attn_fwd": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, f32, u64, f32, vp, vp]),
     "fedb200_attn_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, u64, f32, vp, vp]),
     "fedb200_gram_bf16": (i32, [vp, i32, i32, sz, sz, sz, sz, vp, i32, vp]),
