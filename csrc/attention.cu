@@ -967,7 +967,7 @@ extern "C" int fedb200_attn_fwd(const void* qkv, void* ctx, float* lse, const in
     if (e) return e;
     const size_t smem = 5 * AT_TILE + 1024;
     static bool configured = false;
-    static int variant = 2;
+    static int variant = 4;
     if (!configured) {
         FEDB_CHECK(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         FEDB_CHECK(cudaFuncSetAttribute(attn_fwd4_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
