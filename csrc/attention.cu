@@ -4,12 +4,16 @@
 // qkv is [T, 3H] bf16 (Q | K | V column blocks, head h at columns h*64), cu_seqlens gives each sequence's
 // token range, so the padding mask of the reference becomes "kv index < sequence length".
 //
-// forward, one CTA per (128-row q tile, head, sequence); 192 threads:
+// forward (`attn_fwd4_kernel`, the default), one CTA per (128-row q tile, head, sequence), two CTAs per SM; 576 threads:
 //   warp 0 TMA   : Q tile once, then K_j / V_j tiles (single stage each; two CTAs per SM overlap instead)
-//   warp 1 MMA   : S = Q K_j^T  (M128 N128 K64, both K-major) -> TMEM;  O_j = P_j V_j (A = P from smem,
-//                  B = V tile read MN-major, so V is never transposed)
-//   warps 2-5    : (two CTAs per SM) one thread per q row: two passes over S in TMEM (row max, then exp2 / row sum / dropout),
-//                  P written as bf16 into the 128B-swizzled K-major layout, running O kept in registers
+//   warp 1 MMA   : S = Q K_j^T  (M128 N128 K64, both operands K-major from smem) -> TMEM;
+//                  O += P_j V_j with the A operand P_j read FROM TMEM (bf16 pairs) and B = V tile MN-major from smem
+//   warps 2-17   : four threads per q row, 32 kv columns each: one sweep over S per tile (row maximum, exp2 against the
+//                  reference maximum known so far, row sum, dropout decisions), P packed to bf16 and stored back to TMEM.
+//                  The running output never leaves TMEM; it is rescaled only when a row moves its reference by > 2^8.
+//   TMEM per CTA : S 128 | O 64 | P 64 columns.  Shared memory carries only Q, K, V (profiles/attn_fwd_trace.md: the P round
+//                  trip through shared memory was the bottleneck of the two-thread kernel, which is kept as
+//                  `attn_fwd_kernel`, FEDB200_ATTN_FWD=2, for comparison).
 // backward, one CTA per (128-row kv tile, head, sequence), looping over q tiles:
 //   S^T = K Q_i^T and dP^T = V dO_i^T land in TMEM with the kv index on the lanes, so the thread that owns a kv
 //   row produces its rows of P^T and dS^T directly in the A-operand layout; the same dS^T buffer is read
@@ -308,15 +312,17 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attn_fwd_kernel(const __grid_co
 // -------------------------------------------------------------------------------------------------
 // forward, four threads per q row (the default; FEDB200_ATTN_FWD=2 selects the kernel above)
 //
-// What the two-thread kernel measured (profiles/attn_fwd_trace.md): per kv tile the softmax warps wait 840 clk for S
-// (one S buffer, re-issued only after P was written), spend 836 clk on a max pass and 3 790 clk on the probability pass,
-// and then fold the P V product into 32 output registers — all of it latency-bound with 16 softmax warps per SM.  Here:
-//   * 16 softmax warps per CTA (32 per SM): thread (row, quarter) owns 32 kv columns of its row.  It reads them from TMEM
-//     ONCE into registers and releases the S buffer at once (`s_free`), so Q K_{j+1}^T runs under the softmax of tile j;
-//     the maximum, the exponentials, the dropout decisions and the bf16 packing all happen on those 32 registers.
+// What the two-thread kernel measured (profiles/attn_fwd_trace.md): per kv tile 144 KB of shared-memory traffic per CTA
+// (MMA operand reads 80 KB, P stores 32 KB, TMA writes 32 KB) on a 128 B/clk port shared by two CTAs, two TMEM sweeps over S
+// and a fold of the P V product into 32 output registers.  Here:
+//   * 16 softmax warps per CTA (32 per SM): thread (row, quarter) owns 32 kv columns of its row and sweeps them ONCE per tile,
+//     8 columns at a time with the next eight in flight: maximum, exponentials against the reference maximum known so far,
+//     dropout decisions and bf16 packing in one pass.  If a row then turns out to exceed the reference by more than 2^8 the
+//     warp repeats the sweep against the true maximum (S is released only after that decision), so the result is exact.
+//   * P goes back to TMEM (one tcgen05.st per thread) and P_j V_j takes it from there as its A operand: no shared-memory
+//     round trip, no proxy fence, and the P buffer (32 KB) is gone.
 //   * the running output stays in TMEM: P_j V_j accumulates onto it, and it is rescaled (tcgen05.ld / st of the thread's
-//     16 head-dim columns) only when some row of the warp raised its maximum by more than 2^8 — otherwise the stale
-//     maximum keeps being used, which changes nothing in the result (numerator and denominator carry the same factor).
+//     16 head-dim columns) only on that same rare path.
 // -------------------------------------------------------------------------------------------------
 constexpr int AT4_SOFTMAX_WARPS = 16;
 constexpr int AT4_SOFTMAX_THREADS = AT4_SOFTMAX_WARPS * 32;
@@ -465,21 +471,28 @@ __global__ void __launch_bounds__(AT4_THREADS, 2) attn_fwd4_kernel(const __grid_
             // and is subtracted from lse at the end), keep decisions, P packed to bf16 pairs in registers
             auto sweep = [&](const float m_eff) {
                 rs = 0.f; mx = -INFINITY; bits = 0u;
+                // 8 columns at a time, the next eight in flight while these are processed (the loads' latency, ~250-400 clk under
+                // two CTAs, was fully exposed with 16-column chunks; wider prefetching does not fit the 56 registers)
+                uint32_t buf[2][8];
+                const uint32_t s_addr = tmem_s + lane_addr + quarter * 32;
+                if (!d_nold) {
+                    tmem_ld_32x8(s_addr, buf[0]);
+                    tmem_ld_wait();
+                }
 #pragma unroll
-                for (int sub = 0; sub < 2; ++sub) {
-                    uint32_t raw[16];
-                    if (!d_nold) {
-                        tmem_ld_32x16(tmem_s + lane_addr + quarter * 32 + sub * 16, raw);
-                        tmem_ld_wait();
-                    } else {
+                for (int c = 0; c < 4; ++c) {
+                    uint32_t (&raw)[8] = buf[c & 1];
+                    if (d_nold) {
 #pragma unroll
-                        for (int i = 0; i < 16; ++i) raw[i] = (uint32_t)(i + lane) << 20;
+                        for (int i = 0; i < 8; ++i) raw[i] = (uint32_t)(i + lane) << 20;
+                    } else if (c < 3) {
+                        tmem_ld_32x8(s_addr + (c + 1) * 8, buf[(c + 1) & 1]);
                     }
-                    if (tracer && j == 1) { tr[23 + sub * 2] = clock64() + (__uint_as_float(raw[0]) == 1.2345f ? 1 : 0); }   // data of this half has landed
-                    float p[16];
+                    if (tracer && j == 1 && (c & 1) == 0) { tr[23 + c] = clock64() + (__uint_as_float(raw[0]) == 1.2345f ? 1 : 0); }
+                    float p[8];
                     if (full) {
 #pragma unroll
-                        for (int i = 0; i < 16; ++i) {
+                        for (int i = 0; i < 8; ++i) {
                             mx = fmaxf(mx, __uint_as_float(raw[i]));
                             const float arg = fmaf(__uint_as_float(raw[i]), scale_log2, -m_eff);
                             p[i] = d_noexp ? arg : exp2f(arg);
@@ -487,8 +500,8 @@ __global__ void __launch_bounds__(AT4_THREADS, 2) attn_fwd4_kernel(const __grid_
                         }
                     } else {
 #pragma unroll
-                        for (int i = 0; i < 16; ++i) {
-                            const bool ok = sub * 16 + i < kv_valid;
+                        for (int i = 0; i < 8; ++i) {
+                            const bool ok = c * 8 + i < kv_valid;
                             if (ok) mx = fmaxf(mx, __uint_as_float(raw[i]));
                             p[i] = ok ? exp2f(fmaf(__uint_as_float(raw[i]), scale_log2, -m_eff)) : 0.f;
                             rs += p[i];
@@ -496,8 +509,8 @@ __global__ void __launch_bounds__(AT4_THREADS, 2) attn_fwd4_kernel(const __grid_
                     }
                     if (use_dropout) {
 #pragma unroll
-                        for (int k = 0; k < 8; ++k) {
-                            const int kk = sub * 8 + k;
+                        for (int k = 0; k < 4; ++k) {
+                            const int kk = c * 4 + k;
                             const uint32_t w = attn_drop_word(base, (uint32_t)kk);
                             const bool keep_lo = (w << 16) < thr_hi || keep_all;     // (w & 0xFFFF) < thresh16
                             const bool keep_hi = w < thr_hi || keep_all;             // (w >> 16)   < thresh16
@@ -506,8 +519,9 @@ __global__ void __launch_bounds__(AT4_THREADS, 2) attn_fwd4_kernel(const __grid_
                         }
                     }
 #pragma unroll
-                    for (int q = 0; q < 8; ++q) pk[sub * 8 + q] = pack_bf16x2(p[2 * q], p[2 * q + 1]);
-                    if (tracer && j == 1) tr[24 + sub * 2] = clock64();     // this half is packed
+                    for (int q = 0; q < 4; ++q) pk[c * 4 + q] = pack_bf16x2(p[2 * q], p[2 * q + 1]);
+                    if (!d_nold && c < 3) tmem_ld_wait();
+                    if (tracer && j == 1 && (c & 1) == 1) tr[23 + c] = clock64();
                 }
             };
             sweep(m_run - log2_inv_keep);
