@@ -16,7 +16,8 @@
 //                  `attn_fwd_kernel`, FEDB200_ATTN_FWD=2, for comparison).
 // backward, one CTA per (128-row kv tile, head, sequence), looping over q tiles:
 //   S^T = K Q_i^T and dP^T = V dO_i^T land in TMEM with the kv index on the lanes, so the thread that owns a kv
-//   row produces its rows of P^T and dS^T directly in the A-operand layout; the same dS^T buffer is read
+//   row produces its rows of P^T and dS^T directly in the A-operand layout: P^T goes back to TMEM as bf16 pairs and is
+//   the TMEM A operand of dV += P^T dO_i; dS^T goes to shared memory, where the same buffer is read
 //   K-major for dK += dS^T Q_i and MN-major for dQ_i = dS K (no transposes anywhere).  dV/dK accumulate in
 //   TMEM across the q loop; every kv CTA stores its dQ partial into slot `kv tile` of `dq_accum` (scratch,
 //   [ceil(max_seqlen/128), T, H] bf16, no initialisation needed) and the finishing kernel sums the slots in fp32.
@@ -688,6 +689,7 @@ constexpr int ATB_CWARPS = 16;            // compute warps: four per TMEM lane q
 constexpr int ATB_CTHREADS = ATB_CWARPS * 32;
 constexpr int ATB_THREADS = 64 + ATB_CTHREADS;   // warp 0 TMA, warp 1 MMA, warps 2-17 compute
 
+template <bool PT_TMEM>
 __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv,
                                                                  const __grid_constant__ CUtensorMap tm_do,
                                                                  const float* __restrict__ lse, const float* __restrict__ delta,
@@ -708,9 +710,12 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
     uint8_t* sV = sK + AT_TILE;
     uint8_t* sQ = sV + AT_TILE;              // 2 stages
     uint8_t* sdO = sQ + 2 * AT_TILE;         // 2 stages
-    uint8_t* sP = sdO + 2 * AT_TILE;         // Pd^T : 2 buffers x 2 tiles (q 0-63 | 64-127), rows = kv
-    uint8_t* sdS = sP + 4 * AT_TILE;         // dS^T : 2 buffers x 2 tiles
-    __shared__ __align__(8) uint64_t kv_full, qdo_full[2], qdo_empty[2], sdp_full, pds_ready, dq_full, dq_empty, dkv_full, sdp_free;
+    // PT_TMEM: Pd^T lives in TMEM (64 columns of bf16 pairs, written with tcgen05.st and read by the dV MMA as its A operand)
+    // instead of two shared-memory buffers: 64 KB less shared-memory traffic per q tile and 64 KB less shared memory
+    uint8_t* sdS = sdO + 2 * AT_TILE;        // dS^T : 2 buffers x 2 tiles (q 0-63 | 64-127), rows = kv
+    uint8_t* sP = sdS + 4 * AT_TILE;         // Pd^T : 2 buffers x 2 tiles (only when it is not kept in TMEM)
+    __shared__ __align__(8) uint64_t kv_full, qdo_full[2], qdo_empty[2], sdp_full, pds_ready, dq_full, dq_empty, dkv_full, sdp_free,
+        dv_done;
     __shared__ uint32_t tmem_slot;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -720,7 +725,7 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
         mbar_init(&kv_full, 1);
         for (int s = 0; s < 2; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_empty[s], 1); }
         mbar_init(&sdp_full, 1); mbar_init(&pds_ready, ATB_CTHREADS); mbar_init(&dq_full, 1); mbar_init(&dq_empty, ATB_CTHREADS);
-        mbar_init(&dkv_full, 1); mbar_init(&sdp_free, ATB_CTHREADS);
+        mbar_init(&dkv_full, 1); mbar_init(&sdp_free, ATB_CTHREADS); mbar_init(&dv_done, 1);
         mbar_fence_init();
     }
     if (warp == 1) tmem_alloc(&tmem_slot, 512);
@@ -728,7 +733,7 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tm_st = tmem_slot, tm_dpt = tmem_slot + 128, tm_dv = tmem_slot + 256, tm_dk = tmem_slot + 320,
-                   tm_dq = tmem_slot + 384;
+                   tm_dq = tmem_slot + 384, tm_pt = tmem_slot + 448;
 
     if (warp == 0) {
         // warp-uniform loops, one elected lane issues (operands stay in uniform registers; see gemm2_tcgen05.cu)
@@ -792,8 +797,11 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
             tc_fence_after_sync();
             if (elect_one()) {
 #pragma unroll
-                for (int k = 0; k < 8; ++k)      // dV += Pd^T dO_i   (reduction over q)
-                    umma_bf16(tm_dv, desc_kmajor(aPb + (k >> 2) * AT_TILE, k & 3), desc_mnmajor(aO, k, 8192), idesc_kmn, (i | k) != 0);
+                for (int k = 0; k < 8; ++k) {    // dV += Pd^T dO_i   (reduction over q)
+                    if (PT_TMEM) umma_bf16_ts(tm_dv, tm_pt + k * 8, desc_mnmajor(aO, k, 8192), idesc_kmn, (i | k) != 0);
+                    else umma_bf16(tm_dv, desc_kmajor(aPb + (k >> 2) * AT_TILE, k & 3), desc_mnmajor(aO, k, 8192), idesc_kmn, (i | k) != 0);
+                }
+                if (PT_TMEM) umma_commit(&dv_done);      // Pd^T(i) has been consumed: the compute warps may store tile i+1's
 #pragma unroll
                 for (int k = 0; k < 8; ++k)      // dK += dS^T Q_i
                     umma_bf16(tm_dk, desc_kmajor(aSb + (k >> 2) * AT_TILE, k & 3), desc_mnmajor(aQ, k, 8192), idesc_kmn, (i | k) != 0);
@@ -924,12 +932,23 @@ __global__ void __launch_bounds__(ATB_THREADS, 1) attn_bwd_kernel(const __grid_c
                     else if (drop_mode == 0) elems(I0{}, std::false_type{});
                     else elems(I2{}, std::false_type{});
                 }
+                if (PT_TMEM) {
+                    uint32_t pk[8];
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) pk[q] = pack_bf16x2(pd[2 * q], pd[2 * q + 1]);
+                    if (hc == 0 && i > 0) {      // the dV product of tile i-1 has read its Pd^T (issued a whole tile ago)
+                        mbar_wait(&dv_done, (uint32_t)(i - 1) & 1u);
+                        tc_fence_after_sync();
+                    }
+                    tmem_st_32x8(tm_pt + lane_addr + cg * 16 + hc * 8, pk);
+                }
 #pragma unroll
                 for (int g = 0; g < 2; ++g) {
-                    st_swizzled_chunk(tp, r, (cg & 1) * 4 + hc * 2 + g, pd + g * 8);
+                    if (!PT_TMEM) st_swizzled_chunk(tp, r, (cg & 1) * 4 + hc * 2 + g, pd + g * 8);
                     st_swizzled_chunk(td, r, (cg & 1) * 4 + hc * 2 + g, ds + g * 8);
                 }
             }
+            if (PT_TMEM) tmem_st_wait();
             fence_async_smem();
             tc_fence_before_sync();
             mbar_arrive(&pds_ready);
@@ -1027,14 +1046,19 @@ extern "C" int fedb200_attn_bwd(const void* qkv, const void* ctx, const void* dc
     e = make_tmap_bf16_2d(&tmdo, dctx, (uint64_t)T, (uint64_t)H, (uint64_t)H, 128, 64);
     if (e) return e;
     FEDB_CHECK(launch_pdl(attn_delta_kernel, dim3((T * heads + 255) / 256), dim3(256), 0, s, (const __nv_bfloat16*)ctx, (const __nv_bfloat16*)dctx, delta, T, heads));
-    const size_t smem = 14 * AT_TILE + 1024;
     static bool configured = false;
+    static int pt_tmem = 1;                 // Pd^T kept in TMEM (A operand of the dV product); FEDB200_ATTN_BWD_PT=smem: through shared memory
     if (!configured) {
-        FEDB_CHECK(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        FEDB_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 14 * AT_TILE + 1024));
+        FEDB_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 10 * AT_TILE + 1024));
+        const char* v = getenv("FEDB200_ATTN_BWD_PT");
+        if (v != nullptr) pt_tmem = (v[0] == 't');
         configured = true;
     }
+    const size_t smem = (size_t)(pt_tmem ? 10 : 14) * AT_TILE + 1024;
+    auto bwd = pt_tmem ? attn_bwd_kernel<true> : attn_bwd_kernel<false>;
     dim3 grid((max_seqlen + 127) / 128, heads, B);
-    FEDB_CHECK(launch_pdl(attn_bwd_kernel, dim3(grid), dim3(ATB_THREADS), smem, s, tm, tmdo, lse, delta, (__nv_bfloat16*)dqkv, dq_accum, cu_seqlens, T, H,
+    FEDB_CHECK(launch_pdl(bwd, dim3(grid), dim3(ATB_THREADS), smem, s, tm, tmdo, lse, delta, (__nv_bfloat16*)dqkv, dq_accum, cu_seqlens, T, H,
                                                    scale, scale * LOG2E, seed, dropout_thresh16(dropout_p),
                                                    1.0f / (1.0f - dropout_p), dropout_p > 0.f, (const uint32_t*)drop_bits,
                                                    (max_seqlen + 31) / 32));
