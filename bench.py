@@ -304,7 +304,14 @@ def main():
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", "29511", os.path.abspath(__file__)] + sys.argv[1:]
         raise SystemExit(subprocess.call(cmd))
+    # stdout carries the ONE JSON line and nothing else: library banners written to file descriptor 1 from C code (NCCL prints
+    # "NCCL version ..." there on the first communicator) are sent to stderr; Python's sys.stdout keeps the real stdout
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w", buffering=1)
     (run_fedb200 if args.impl == "fedb200" else run_torch_baseline)(args)
+    sys.stdout.flush()
 
 
 if __name__ == "__main__":
