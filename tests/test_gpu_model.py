@@ -65,6 +65,36 @@ def test_attention_fwd_bwd_no_dropout(cuda_lib, lens, heads):
         assert e < 3e-2 * max(scale_ref, 1.0) + 2e-2, f"{name} max err {e} (ref max {scale_ref})"
 
 
+def test_attention_fwd_large_scores_take_the_resweep_path(cuda_lib):
+    """Scores far from the forward's initial reference maximum (|s| of several tens in log2 units, and growing from one kv tile
+    to the next) force its exact re-sweep and the rescale of the TMEM-resident output; output and lse must still match fp32."""
+    ops = _ops()
+    torch.manual_seed(3)
+    lens, heads = [512, 300, 129, 128, 64, 7], 2
+    H, T, B = heads * 64, sum(lens), len(lens)
+    cu = torch.tensor([0] + list(np.cumsum(lens)), dtype=torch.int32, device="cuda")
+    qkv = torch.randn(T, 3 * H, device="cuda") * 3.0
+    ramp = torch.cat([torch.linspace(0.5, 2.0, n) for n in lens]).cuda()          # later keys score higher: the maximum keeps moving
+    qkv[:, H:2 * H] *= ramp[:, None]
+    qkv = qkv.bfloat16()
+    ctx = torch.zeros(T, H, dtype=torch.bfloat16, device="cuda")
+    lse = torch.zeros(heads * T, device="cuda")
+    ops.attn_fwd(qkv, ctx, lse, cu, B, heads, max(lens), 0.125)
+    torch.cuda.synchronize()
+    f = qkv.float()
+    for b in range(B):
+        s, e = int(cu[b]), int(cu[b + 1])
+        for h in range(heads):
+            q, k, v = f[s:e, h * 64:(h + 1) * 64], f[s:e, H + h * 64:H + (h + 1) * 64], f[s:e, 2 * H + h * 64:2 * H + (h + 1) * 64]
+            sc = (q @ k.T) * 0.125
+            ref = torch.softmax(sc, -1) @ v
+            got = ctx[s:e, h * 64:(h + 1) * 64].float()
+            rel = ((got - ref).norm() / ref.norm()).item()
+            assert rel < 8e-3, (b, h, rel)
+            l2 = torch.logsumexp(sc, -1) * 1.4426950408889634
+            assert (lse[h * T + s:h * T + e] - l2).abs().max().item() < 2e-3 * max(1.0, l2.abs().max().item())
+
+
 def test_attention_dropout_exact_mask(cuda_lib):
     from fedb200.ops.rng import attn_dropout_scale as dropout_scale
     ops = _ops()
