@@ -24,7 +24,7 @@ names = {0: "full kernel", 1: "no exp2", 2: "no TMEM loads in the sweep", 4: "no
 for pad in (0, 48 * 1024):
     for p in (0.0, 0.1):
         for diag in (0, 1, 2, 4, 7):
-            _lib.call("fedb200_attn_set_diag", diag, pad)
+            _lib.call("fedb200_attn_set_diag", diag | 8, pad)
             ts = []
             for it in range(8):
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -45,5 +45,5 @@ for pad in (0, 48 * 1024):
             print(f"CTAs/SM {1 if pad else 2} dropout {p} {names[diag]:28s}: {np.median(ts):6.1f} us  sweep+xchg {np.mean(sweep):5.0f}  "
                   f"wait S {np.mean(swait):4.0f}  wait O {np.mean(owait):4.0f} clk | tile 1: ld0 {det[0]} math0 {det[1]} ld1 {det[2]} math1 {det[3]} "
                   f"sts {det[4]} bar {det[5]}")
-_lib.call("fedb200_attn_set_diag", 0, 0)
+_lib.call("fedb200_attn_set_diag", 8, 0)
 _lib.call("fedb200_attn_set_trace", None)
