@@ -37,6 +37,8 @@ class TorchRunner:
                  module: Optional[torch.nn.Module] = None):
         fed = fed or FedConfig()
         self.cfg, self.fed, self.device = model_cfg, fed, torch.device(device)
+        if fed.deterministic:               # --deterministic on the PyTorch path: ask torch for its reproducible kernels
+            torch.use_deterministic_algorithms(True, warn_only=True)
         self.module = module if module is not None else build_model(
             model_cfg, self.device, seed, checkpoint=fed.init_checkpoint, ignore_mismatched_sizes=fed.ignore_mismatched_sizes)
         self.arena = FlatArena.adopt(self.module, self.device)

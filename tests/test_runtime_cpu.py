@@ -297,3 +297,22 @@ def test_receiver_verifies_published_update_against_recorded_root():
     with pytest.raises(RuntimeError, match="does not hash to the Merkle root"):
         rt.round_serverless(1)
     rt.close()
+
+
+def test_deterministic_flag_parses_and_cpu_rounds_reproduce_their_ledger_roots():
+    """--deterministic reaches the config, and two runs from the same seed record the same Merkle roots (on the CPU / PyTorch
+    path that is torch's deterministic mode; the sm_100a path has tests/test_gpu_fed.py::test_deterministic_rounds_...)."""
+    from fedb200.config import build_parser, config_from_args
+    cfg = config_from_args(build_parser().parse_args(["--deterministic", "--clients", "3"]))
+    assert cfg.deterministic is True and cfg.num_clients == 3
+
+    def roots():
+        rt = FedRuntime(_cfg(ledger=True, deterministic=True), echo=False)
+        try:
+            rt.run()
+            return [b.update_root for b in rt.ledger.blocks], rt.runner.flat.clone()
+        finally:
+            rt.close()
+            torch.use_deterministic_algorithms(False)
+    (r1, w1), (r2, w2) = roots(), roots()
+    assert len(r1) == 6 and r1 == r2 and torch.equal(w1, w2)
