@@ -1,0 +1,20 @@
+"""The cross-GPU flag protocol (csrc/peer_flags.cuh) explored exhaustively as a state machine: safety and progress for every
+interleaving, with and without co-resident CTAs; broken variants must be caught (fedb200/utils/protocol_check.py)."""
+import pytest
+
+from fedb200.utils.protocol_check import check, check_broken_variant
+
+
+@pytest.mark.parametrize("ranks,ctas,launches,resident", [(2, 2, 2, 1), (2, 2, 2, 2), (2, 3, 1, 1)])
+def test_flag_protocol_is_safe_and_live_for_every_interleaving(ranks, ctas, launches, resident):
+    out = check(ranks, ctas, launches, resident)
+    assert out["final_states"] == 1 and out["states"] > 1000
+
+
+def test_checker_catches_broken_protocols():
+    with pytest.raises(AssertionError, match="end safety"):
+        check(2, 2, 2, 1, mutation="no_end_wait")
+    with pytest.raises(AssertionError, match="weight of epoch"):
+        check(2, 2, 2, 1, mutation="epoch_before_weight")
+    # the round-1 start barrier (block 0 releases the other blocks) hangs when the grid is not co-resident
+    assert check_broken_variant().startswith("stuck")
