@@ -142,6 +142,12 @@ def run_async_observed(rt) -> Dict:
                 slot = outbox[li, e % R]
                 comm.flag_set(pub, li, e)                                   # publish STARTED: consumers may pick version e
                 if on_gpu:
+                    if e > R:
+                        # the slot still holds version e - R with landing flags that say so: retire the flags BEFORE its bytes
+                        # change, so a reader that is still on that version finds the mismatch in its post-read check (without
+                        # this a read lapped in the middle of a chunk would go unnoticed: utils/protocol_check.py::check_ring)
+                        cuda_ops.set_flags(cflags[li, e % R], 0, n_chunks)
+                        comm.launches += 1
                     if ledger_on:
                         cuda_ops.sha256_leaves(state[li], slot, rt.ledger.chunk_bytes, leaves_ws)
                         cuda_ops.merkle_root(leaves_ws, scratch_ws, root_table[row])

@@ -162,8 +162,69 @@ def check_broken_variant() -> str:
     return ""
 
 
+def check_ring(ring: int = 2, chunks: int = 2, versions: int = 4, invalidate: bool = True) -> Dict[str, int]:
+    """The asynchronous outbox ring (p2p/observed.py + csrc/gossip.cu): a producer publishes versions 1..V into slot v % R,
+    chunk by chunk (bytes, then the chunk's landing flag = v, release order); a reader picks a published version, and per chunk
+    waits for flag >= v, reads the bytes, and re-reads the flag: a value other than v counts the chunk as torn (the mix is then
+    discarded).  Property: a chunk the reader ACCEPTS holds exactly the bytes of version v.  With ``invalidate`` the producer
+    first retires the slot's flags (0) before it overwrites the bytes of version v - R, as the runtime does; without it the
+    exploration finds the lapped read that goes unnoticed."""
+    R, C, V = ring, chunks, versions
+    # producer: (version being published, phase, chunk): phase 0 = retire flags (per chunk), 1 = write bytes, 2 = set flag
+    # memory:   data[slot][chunk] = version of the bytes, "mid" while half written (tuple (old, new)); flag[slot][chunk]
+    # reader:   (version chosen or 0, chunk, phase): 0 = choose, 1 = wait flag, 2 = read bytes (value latched), 3 = re-check
+    init = ((1, 0 if invalidate else 1, 0), tuple(tuple(0 for _ in range(C)) for _ in range(R)),
+            tuple(tuple(0 for _ in range(C)) for _ in range(R)), 0, (0, 0, 0, None))
+    seen, todo = {init}, deque([init])
+    accepted = torn = 0
+    while todo:
+        prod, data, flag, pub, rd = todo.popleft()
+        nxt = []
+        v, ph, c = prod
+        if v <= V:
+            sl = v % R
+            if ph == 0:                                   # retire the landing flag of chunk c (only if the slot was used before)
+                nf = tuple(tuple(0 if (i == sl and j == c and v > R) else flag[i][j] for j in range(C)) for i in range(R))
+                nxt.append((((v, 0, c + 1) if c + 1 < C else (v, 1, 0)), data, nf, max(pub, v), rd))      # `pub` = v was stored first
+            elif ph == 1:                                 # the bytes of chunk c change (first half, then second half)
+                cur = data[sl][c]
+                new = (cur, v) if not isinstance(cur, tuple) else v
+                nd = tuple(tuple(new if (i == sl and j == c) else data[i][j] for j in range(C)) for i in range(R))
+                nxt.append(((v, 1, c) if isinstance(new, tuple) else (v, 2, c), nd, flag, max(pub, v), rd))
+            else:                                         # flag[c] = v, release
+                nf = tuple(tuple(v if (i == sl and j == c) else flag[i][j] for j in range(C)) for i in range(R))
+                nxt.append((((v, 1, c + 1) if c + 1 < C else (v + 1, 0 if invalidate else 1, 0)), data, nf, pub, rd))
+        rv, rc, rph, latched = rd
+        if rph == 0:
+            if pub > 0:
+                nxt.append((prod, data, flag, pub, (pub, 0, 1, None)))          # the version decision (logged for replay)
+        elif rph == 1:
+            if flag[rv % R][rc] >= rv:
+                nxt.append((prod, data, flag, pub, (rv, rc, 2, None)))
+        elif rph == 2:
+            nxt.append((prod, data, flag, pub, (rv, rc, 3, data[rv % R][rc])))
+        elif rph == 3:
+            if flag[rv % R][rc] == rv:                    # accepted
+                assert latched == rv, (f"undetected torn read: version {rv} chunk {rc} accepted with bytes {latched} "
+                                       f"(ring {R}, producer at version {v})")
+                accepted += 1
+            else:
+                torn += 1
+            nxt.append((prod, data, flag, pub, (rv, rc + 1, 1, None) if rc + 1 < C else (0, 0, 0, None)))
+        for t in nxt:
+            if t not in seen:
+                seen.add(t)
+                todo.append(t)
+    return {"states": len(seen), "accepted_reads": accepted, "torn_reads_detected": torn, "ring": R, "chunks": C, "versions": V}
+
+
 if __name__ == "__main__":
     import json
     for cfg in ((2, 2, 2, 1), (2, 2, 2, 2), (3, 1, 2, 1), (2, 3, 1, 1)):
         print(json.dumps(check(*cfg)))
     print("round-1 design under one resident CTA:", check_broken_variant())
+    print(json.dumps(check_ring(2, 2, 4, True)))
+    try:
+        check_ring(2, 2, 4, False)
+    except AssertionError as ex:
+        print("ring without retiring the flags first:", ex)
