@@ -2,6 +2,9 @@
 import hashlib
 
 import numpy as np
+import pytest
+
+pytest.importorskip("hypothesis")
 from hypothesis import given, settings, strategies as st
 
 from fedb200.ledger.merkle import LEAF_TAG, NODE_TAG, leaf_digests, merkle_root, reduce_level, root_from_leaves
