@@ -324,6 +324,7 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attn_fwd_kernel(const __grid_co
 //     round trip, no proxy fence, and the P buffer (32 KB) is gone.
 //   * the running output stays in TMEM: P_j V_j accumulates onto it, and it is rescaled (tcgen05.ld / st of the thread's
 //     16 head-dim columns) only on that same rare path.
+// fedb200/ops/attn_model.py restates the reference-maximum rule in NumPy (tests/test_attention_algorithm_cpu.py).
 // -------------------------------------------------------------------------------------------------
 constexpr int AT4_SOFTMAX_WARPS = 16;
 constexpr int AT4_SOFTMAX_THREADS = AT4_SOFTMAX_WARPS * 32;
